@@ -1,0 +1,230 @@
+// FP32 CUDA-core operators: implicit-GEMM convolution / linear, pooling, BN + residual, mean,
+// and the softmax/argmax label kernel.  See generic_ops.cuh.
+#include "generic_ops.cuh"
+
+namespace honk {
+
+namespace {
+
+constexpr int BM = 64, BN = 64, BK = 16, TM = 4, TN = 4;
+
+// C[M,N] = A[M,K] * W[N,K]^T with A gathered on the fly from the NCHW input (im2col never
+// materialised).  M = B*Ho*Wo, N = Cout, K = Cin*KH*KW.  64x64x16 tiles, 4x4 per thread.
+__global__ void __launch_bounds__(256) conv_gemm_f32_kernel(const float* __restrict__ in,
+                                                            const float* __restrict__ w,
+                                                            const float* __restrict__ bias,
+                                                            float* __restrict__ out, ConvGeom g, int relu) {
+  __shared__ float As[BK][BM + 4];
+  __shared__ float Bs[BK][BN + 4];
+  const long long M = static_cast<long long>(g.B) * g.Ho * g.Wo;
+  const int N = g.Cout, K = g.Cin * g.KH * g.KW, KHW = g.KH * g.KW;
+  const int tid = threadIdx.x;
+  const long long m0 = static_cast<long long>(blockIdx.x) * BM;
+  const int n0 = blockIdx.y * BN;
+
+  // A-load role: one m per thread, 4 k's
+  const int la_m = tid % BM, la_k = tid / BM;           // la_k in 0..3
+  const long long gm = m0 + la_m;
+  const bool m_ok = gm < M;
+  int hi0 = 0, wi0 = 0;
+  const float* in_b = in;
+  if (m_ok) {
+    const int wo = static_cast<int>(gm % g.Wo);
+    const long long r = gm / g.Wo;
+    const int ho = static_cast<int>(r % g.Ho);
+    const long long b = r / g.Ho;
+    hi0 = ho * g.sh - g.ph;
+    wi0 = wo * g.sw - g.pw;
+    in_b = in + b * g.Cin * g.H * g.W;
+  }
+  // B-load role: k fastest
+  const int lb_k = tid % BK, lb_n = tid / BK;            // lb_n in 0..15
+
+  const int tm = (tid % 16) * TM, tn = (tid / 16) * TN;
+  float acc[TM][TN];
+#pragma unroll
+  for (int i = 0; i < TM; ++i)
+#pragma unroll
+    for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+
+  for (int k0 = 0; k0 < K; k0 += BK) {
+#pragma unroll
+    for (int i = 0; i < BK / 4; ++i) {
+      const int kk = la_k + 4 * i, k = k0 + kk;
+      float v = 0.f;
+      if (m_ok && k < K) {
+        const int ci = k / KHW, rem = k - ci * KHW;
+        const int kh = rem / g.KW, kw = rem - kh * g.KW;
+        const int hi = hi0 + kh * g.dh, wi = wi0 + kw * g.dw;
+        if (hi >= 0 && hi < g.H && wi >= 0 && wi < g.W)
+          v = __ldg(in_b + (static_cast<long long>(ci) * g.H + hi) * g.W + wi);
+      }
+      As[kk][la_m] = v;
+    }
+#pragma unroll
+    for (int i = 0; i < BN / 16; ++i) {
+      const int nn = lb_n + 16 * i, n = n0 + nn, k = k0 + lb_k;
+      Bs[lb_k][nn] = (n < N && k < K) ? __ldg(w + static_cast<long long>(n) * K + k) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < BK; ++kk) {
+      float a[TM], b[TN];
+#pragma unroll
+      for (int i = 0; i < TM; ++i) a[i] = As[kk][tm + i];
+#pragma unroll
+      for (int j = 0; j < TN; ++j) b[j] = Bs[kk][tn + j];
+#pragma unroll
+      for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+
+  const long long HWo = static_cast<long long>(g.Ho) * g.Wo;
+#pragma unroll
+  for (int i = 0; i < TM; ++i) {
+    const long long m = m0 + tm + i;
+    if (m >= M) continue;
+    const long long b = m / HWo, pos = m - b * HWo;
+#pragma unroll
+    for (int j = 0; j < TN; ++j) {
+      const int n = n0 + tn + j;
+      if (n >= N) continue;
+      float v = acc[i][j] + (bias ? __ldg(bias + n) : 0.f);
+      if (relu) v = fmaxf(v, 0.f);
+      out[(b * N + n) * HWo + pos] = v;
+    }
+  }
+}
+
+__global__ void pool2d_f32_kernel(const float* __restrict__ in, float* __restrict__ out, long long total, int H,
+                                  int W, int Ho, int Wo, int kh, int kw, int is_max) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int wo = static_cast<int>(i % Wo);
+  const long long r = i / Wo;
+  const int ho = static_cast<int>(r % Ho);
+  const long long bc = r / Ho;
+  const float* p = in + (bc * H + static_cast<long long>(ho) * kh) * W + static_cast<long long>(wo) * kw;
+  float acc = is_max ? -INFINITY : 0.f;
+  for (int y = 0; y < kh; ++y)
+    for (int x = 0; x < kw; ++x) {
+      const float v = __ldg(p + y * W + x);
+      acc = is_max ? fmaxf(acc, v) : acc + v;
+    }
+  out[i] = is_max ? acc : acc / static_cast<float>(kh * kw);
+}
+
+__global__ void bn_residual_f32_kernel(const float* __restrict__ y, const float* __restrict__ res,
+                                       float* __restrict__ res_out, float* __restrict__ out,
+                                       const float* __restrict__ mean, const float* __restrict__ scale,
+                                       long long total, int C, int HW) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int c = static_cast<int>((i / HW) % C);
+  float x = y[i];
+  if (res) x += res[i];
+  if (res_out) res_out[i] = x;
+  out[i] = (x - __ldg(mean + c)) * __ldg(scale + c);
+}
+
+__global__ void mean_hw_f32_kernel(const float* __restrict__ in, float* __restrict__ out, int HW) {
+  const long long bc = blockIdx.x;
+  const float* p = in + bc * HW;
+  float s = 0.f;
+  for (int i = threadIdx.x; i < HW; i += blockDim.x) s += p[i];
+  __shared__ float red[32];
+  for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    s = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
+    for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (threadIdx.x == 0) out[bc] = s / static_cast<float>(HW);
+  }
+}
+
+// softmax -> (argmax, max prob); one warp per clip (service.py:103-104)
+__global__ void label_kernel(const float* __restrict__ logits, long long n, int L, int* __restrict__ labels,
+                             float* __restrict__ probs) {
+  const long long clip = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (clip >= n) return;
+  const float* z = logits + clip * L;
+  float best = -INFINITY;
+  int arg = 0x7fffffff;
+  for (int i = lane; i < L; i += 32) {
+    const float v = z[i];
+    if (v > best) { best = v; arg = i; }
+  }
+  for (int o = 16; o; o >>= 1) {
+    const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+    if (ob > best || (ob == best && oa < arg)) { best = ob; arg = oa; }
+  }
+  float sum = 0.f;
+  for (int i = lane; i < L; i += 32) sum += expf(z[i] - best);
+  for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if (lane == 0) {
+    if (labels) labels[clip] = arg;
+    if (probs) probs[clip] = 1.f / sum;
+  }
+}
+
+}  // namespace
+
+int conv2d_f32(const float* in, const float* w, const float* bias, float* out, const ConvGeom& g, bool relu,
+               cudaStream_t s) {
+  const long long M = static_cast<long long>(g.B) * g.Ho * g.Wo;
+  if (M == 0) return HONK_OK;
+  HONK_CHECK(g.Ho > 0 && g.Wo > 0, HONK_ERR_INVALID, "convolution output is empty");
+  dim3 grid(static_cast<unsigned>((M + BM - 1) / BM), ceil_div(g.Cout, BN));
+  conv_gemm_f32_kernel<<<grid, 256, 0, s>>>(in, w, bias, out, g, relu ? 1 : 0);
+  HONK_LAUNCH_CHECK();
+  return HONK_OK;
+}
+
+int pool2d_f32(const float* in, float* out, int BC, int H, int W, int kh, int kw, bool is_max, cudaStream_t s) {
+  const int Ho = H / kh, Wo = W / kw;
+  const long long total = static_cast<long long>(BC) * Ho * Wo;
+  if (total == 0) return HONK_OK;
+  pool2d_f32_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, s>>>(in, out, total, H, W, Ho, Wo, kh,
+                                                                              kw, is_max ? 1 : 0);
+  HONK_LAUNCH_CHECK();
+  return HONK_OK;
+}
+
+int bn_residual_f32(const float* y, const float* res, float* res_out, float* out, const float* mean,
+                    const float* scale, int B, int C, int HW, cudaStream_t s) {
+  const long long total = static_cast<long long>(B) * C * HW;
+  if (total == 0) return HONK_OK;
+  bn_residual_f32_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, s>>>(y, res, res_out, out, mean,
+                                                                                   scale, total, C, HW);
+  HONK_LAUNCH_CHECK();
+  return HONK_OK;
+}
+
+int mean_hw_f32(const float* in, float* out, int BC, int HW, cudaStream_t s) {
+  if (BC == 0) return HONK_OK;
+  mean_hw_f32_kernel<<<BC, 256, 0, s>>>(in, out, HW);
+  HONK_LAUNCH_CHECK();
+  return HONK_OK;
+}
+
+}  // namespace honk
+
+using namespace honk;
+
+extern "C" int honk_label_from_logits(const float* d_logits, int64_t n_clips, int32_t n_labels, int32_t* d_labels,
+                                      float* d_probs, void* stream) {
+  HONK_CHECK(n_clips >= 0 && n_labels >= 1, HONK_ERR_INVALID, "bad n_clips/n_labels");
+  if (n_clips == 0) return HONK_OK;
+  HONK_CHECK(d_logits, HONK_ERR_INVALID, "null logits");
+  const long long threads = n_clips * 32;
+  label_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      d_logits, n_clips, n_labels, d_labels, d_probs);
+  HONK_LAUNCH_CHECK();
+  return HONK_OK;
+}

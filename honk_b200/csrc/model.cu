@@ -1,0 +1,347 @@
+// Model handle: strict state_dict validation (load_state_dict semantics, utils/model.py:79-80),
+// the all-FP32 CUDA-core forward for every architecture, and the C ABI.
+#include "model.cuh"
+
+#include <cmath>
+
+using namespace honk;
+
+namespace {
+
+constexpr int64_t kChunkF32 = 512;   // clips per pass on the FP32 path (bounds the workspace)
+
+struct Expect {
+  std::string name;
+  std::vector<int64_t> dims;
+};
+
+int conv_out(int n, int k, int s) { return (n - k) / s + 1; }
+
+// Key names and shapes of the reference modules (model.py:85-102 and 126-184).
+int expected_keys(const honk_model_config& c, std::vector<Expect>& out, std::vector<std::string>& ignorable) {
+  if (c.family == HONK_FAMILY_RES) {
+    const int C = c.n_feature_maps, L = c.n_labels;
+    HONK_CHECK(C >= 1 && C <= 512 && L >= 1 && c.n_layers >= 1 && c.n_layers <= 64, HONK_ERR_INVALID,
+               "bad res config (maps=%d labels=%d layers=%d)", C, L, c.n_layers);
+    out.push_back({"conv0.weight", {C, 1, 3, 3}});
+    for (int i = 1; i <= c.n_layers; ++i) {
+      const std::string s = std::to_string(i);
+      out.push_back({"bn" + s + ".running_mean", {C}});
+      out.push_back({"bn" + s + ".running_var", {C}});
+      ignorable.push_back("bn" + s + ".num_batches_tracked");
+      out.push_back({"conv" + s + ".weight", {C, C, 3, 3}});
+    }
+    out.push_back({"output.weight", {L, C}});
+    out.push_back({"output.bias", {L}});
+    return HONK_OK;
+  }
+  HONK_CHECK(c.family == HONK_FAMILY_CNN, HONK_ERR_INVALID, "unknown model family %d", c.family);
+  HONK_CHECK(c.n_feature_maps1 >= 1 && c.conv1_size[0] >= 1 && c.conv1_size[1] >= 1 && c.conv1_stride[0] >= 1 &&
+                 c.conv1_stride[1] >= 1 && c.conv1_pool[0] >= 1 && c.conv1_pool[1] >= 1 && c.n_labels >= 1,
+             HONK_ERR_INVALID, "bad cnn config");
+  int H = c.height, W = c.width, C = c.n_feature_maps1;
+  HONK_CHECK(H >= c.conv1_size[0] && W >= c.conv1_size[1], HONK_ERR_INVALID, "conv1 larger than the input");
+  out.push_back({"conv1.weight", {C, 1, c.conv1_size[0], c.conv1_size[1]}});
+  out.push_back({"conv1.bias", {C}});
+  H = conv_out(H, c.conv1_size[0], c.conv1_stride[0]) / c.conv1_pool[0];
+  W = conv_out(W, c.conv1_size[1], c.conv1_stride[1]) / c.conv1_pool[1];
+  if (c.has_conv2) {
+    HONK_CHECK(c.n_feature_maps2 >= 1 && c.conv2_size[0] >= 1 && c.conv2_size[1] >= 1 && c.conv2_stride[0] >= 1 &&
+                   c.conv2_stride[1] >= 1 && c.conv2_pool[0] >= 1 && c.conv2_pool[1] >= 1,
+               HONK_ERR_INVALID, "bad conv2 config");
+    HONK_CHECK(H >= c.conv2_size[0] && W >= c.conv2_size[1], HONK_ERR_INVALID, "conv2 larger than its input");
+    out.push_back({"conv2.weight", {c.n_feature_maps2, C, c.conv2_size[0], c.conv2_size[1]}});
+    out.push_back({"conv2.bias", {c.n_feature_maps2}});
+    H = conv_out(H, c.conv2_size[0], c.conv2_stride[0]) / c.conv2_pool[0];
+    W = conv_out(W, c.conv2_size[1], c.conv2_stride[1]) / c.conv2_pool[1];
+    C = c.n_feature_maps2;
+  }
+  HONK_CHECK(H >= 1 && W >= 1, HONK_ERR_INVALID, "feature map vanished");
+  const int64_t flat = static_cast<int64_t>(C) * H * W;
+  int64_t last = flat;
+  if (!c.tf_variant) {
+    out.push_back({"lin.weight", {32, flat}});
+    out.push_back({"lin.bias", {32}});
+  }
+  if (c.dnn1_size > 0) {
+    out.push_back({"dnn1.weight", {c.dnn1_size, c.tf_variant ? flat : 32}});
+    out.push_back({"dnn1.bias", {c.dnn1_size}});
+    last = c.dnn1_size;
+    if (c.dnn2_size > 0) {
+      out.push_back({"dnn2.weight", {c.dnn2_size, c.dnn1_size}});
+      out.push_back({"dnn2.bias", {c.dnn2_size}});
+      last = c.dnn2_size;
+    }
+  }
+  out.push_back({"output.weight", {c.n_labels, last}});
+  out.push_back({"output.bias", {c.n_labels}});
+  return HONK_OK;
+}
+
+int upload(honk_model* m, const std::vector<float>& h, float** d) {
+  void* p = nullptr;
+  HONK_CUDA(cudaMalloc(&p, std::max<size_t>(h.size(), 1) * sizeof(float)));
+  m->owned.push_back(p);
+  HONK_CUDA(cudaMemcpy(p, h.data(), h.size() * sizeof(float), cudaMemcpyHostToDevice));
+  *d = static_cast<float*>(p);
+  return HONK_OK;
+}
+
+int res_dilation(const honk_model_config& c, int i) {   // conv_i, i >= 1 (model.py:94-98)
+  return c.use_dilation ? (1 << ((i - 1) / 3)) : 1;
+}
+
+// per-clip float count of the largest activation on the FP32 path
+int64_t f32_act_elems(const honk_model* m) {
+  const honk_model_config& c = m->cfg;
+  if (c.family == HONK_FAMILY_RES) return static_cast<int64_t>(c.n_feature_maps) * m->H0 * m->W0;
+  int H = conv_out(c.height, c.conv1_size[0], c.conv1_stride[0]);
+  int W = conv_out(c.width, c.conv1_size[1], c.conv1_stride[1]);
+  int64_t mx = static_cast<int64_t>(c.n_feature_maps1) * H * W;
+  H /= c.conv1_pool[0];
+  W /= c.conv1_pool[1];
+  if (c.has_conv2) {
+    H = conv_out(H, c.conv2_size[0], c.conv2_stride[0]);
+    W = conv_out(W, c.conv2_size[1], c.conv2_stride[1]);
+    mx = std::max(mx, static_cast<int64_t>(c.n_feature_maps2) * H * W);
+  }
+  return std::max<int64_t>(mx, 512);
+}
+
+int64_t f32_workspace(const honk_model* m, int64_t n) {
+  const int64_t chunk = std::min(n, kChunkF32);
+  Arena a(nullptr, 0);
+  for (int i = 0; i < 4; ++i) a.take<float>(f32_act_elems(m) * chunk);
+  return align_up(a.off, 256);
+}
+
+int forward_res_f32(const honk_model* m, const float* x, int B, float* logits, Arena& ar, cudaStream_t s) {
+  const honk_model_config& c = m->cfg;
+  const int C = c.n_feature_maps;
+  const int64_t per = f32_act_elems(m) * B;
+  float* b0 = ar.take<float>(per);
+  float* b1 = ar.take<float>(per);
+  float* b2 = ar.take<float>(per);
+  float* b3 = ar.take<float>(per);
+  ConvGeom g{B, 1, m->H0, m->W0, C, 3, 3, 1, 1, 1, 1, 1, 1, 0, 0};
+  conv_out_dims(g);
+  float* xin = b1;      // normalised conv input
+  float* old = b2;      // raw residual stream
+  if (c.res_pool[0] > 0) {
+    HONK_TRY(conv2d_f32(x, m->dev.at("conv0.weight"), nullptr, b0, g, true, s));
+    HONK_TRY(pool2d_f32(b0, old, B * C, m->H0, m->W0, c.res_pool[0], c.res_pool[1], false, s));
+  } else {
+    HONK_TRY(conv2d_f32(x, m->dev.at("conv0.weight"), nullptr, old, g, true, s));
+  }
+  const float* cur = old;   // conv1 reads the un-normalised conv0 output (there is no bn0)
+  const int HW = m->Hr * m->Wr;
+  for (int i = 1; i <= c.n_layers; ++i) {
+    const int d = res_dilation(c, i);
+    ConvGeom gi{B, C, m->Hr, m->Wr, C, 3, 3, 1, 1, d, d, d, d, 0, 0};
+    conv_out_dims(gi);
+    const std::string si = std::to_string(i);
+    HONK_TRY(conv2d_f32(cur, m->dev.at("conv" + si + ".weight"), nullptr, b0, gi, true, s));
+    float* dst = (cur == xin) ? b3 : xin;
+    const bool add = (i % 2 == 0);
+    HONK_TRY(bn_residual_f32(b0, add ? old : nullptr, add ? old : nullptr, dst,
+                             m->dev.at("bn" + si + ".running_mean"), m->bn_scale[i - 1], B, C, HW, s));
+    if (dst == b3) std::swap(xin, b3);
+    cur = xin;
+  }
+  HONK_TRY(mean_hw_f32(cur, b0, B * C, HW, s));
+  ConvGeom gl{B, C, 1, 1, c.n_labels, 1, 1, 1, 1, 0, 0, 1, 1, 1, 1};
+  return conv2d_f32(b0, m->dev.at("output.weight"), m->dev.at("output.bias"), logits, gl, false, s);
+}
+
+int linear_f32(const honk_model* m, const char* name, const float* in, float* out, int B, bool relu, cudaStream_t s) {
+  const HostTensor& w = m->host.at(std::string(name) + ".weight");
+  ConvGeom g{B, static_cast<int>(w.dims[1]), 1, 1, static_cast<int>(w.dims[0]), 1, 1, 1, 1, 0, 0, 1, 1, 1, 1};
+  return conv2d_f32(in, m->dev.at(std::string(name) + ".weight"), m->dev.at(std::string(name) + ".bias"), out, g,
+                    relu, s);
+}
+
+int forward_cnn_f32(const honk_model* m, const float* x, int B, float* logits, Arena& ar, cudaStream_t s) {
+  const honk_model_config& c = m->cfg;
+  const int64_t per = f32_act_elems(m) * B;
+  float* a = ar.take<float>(per);
+  float* b = ar.take<float>(per);
+  ConvGeom g{B, 1, c.height, c.width, c.n_feature_maps1, c.conv1_size[0], c.conv1_size[1],
+             c.conv1_stride[0], c.conv1_stride[1], 0, 0, 1, 1, 0, 0};
+  conv_out_dims(g);
+  HONK_TRY(conv2d_f32(x, m->dev.at("conv1.weight"), m->dev.at("conv1.bias"), a, g, true, s));
+  int C = g.Cout, H = g.Ho, W = g.Wo;
+  float* cur = a;
+  float* nxt = b;
+  if (c.conv1_pool[0] != 1 || c.conv1_pool[1] != 1) {
+    HONK_TRY(pool2d_f32(cur, nxt, B * C, H, W, c.conv1_pool[0], c.conv1_pool[1], true, s));
+    std::swap(cur, nxt);
+    H /= c.conv1_pool[0];
+    W /= c.conv1_pool[1];
+  }
+  if (c.has_conv2) {
+    ConvGeom g2{B, C, H, W, c.n_feature_maps2, c.conv2_size[0], c.conv2_size[1],
+                c.conv2_stride[0], c.conv2_stride[1], 0, 0, 1, 1, 0, 0};
+    conv_out_dims(g2);
+    HONK_TRY(conv2d_f32(cur, m->dev.at("conv2.weight"), m->dev.at("conv2.bias"), nxt, g2, true, s));
+    std::swap(cur, nxt);
+    C = g2.Cout; H = g2.Ho; W = g2.Wo;
+    if (c.conv2_pool[0] != 1 || c.conv2_pool[1] != 1) {
+      HONK_TRY(pool2d_f32(cur, nxt, B * C, H, W, c.conv2_pool[0], c.conv2_pool[1], true, s));
+      std::swap(cur, nxt);
+      H /= c.conv2_pool[0];
+      W /= c.conv2_pool[1];
+    }
+  }
+  // flatten is a no-op in NCHW (x.view(B, -1), model.py:195)
+  if (!c.tf_variant) {
+    HONK_TRY(linear_f32(m, "lin", cur, nxt, B, false, s));
+    std::swap(cur, nxt);
+  }
+  if (c.dnn1_size > 0) {
+    HONK_TRY(linear_f32(m, "dnn1", cur, nxt, B, !c.tf_variant, s));
+    std::swap(cur, nxt);
+    if (c.dnn2_size > 0) {
+      HONK_TRY(linear_f32(m, "dnn2", cur, nxt, B, false, s));
+      std::swap(cur, nxt);
+    }
+  }
+  return linear_f32(m, "output", cur, logits, B, false, s);
+}
+
+}  // namespace
+
+extern "C" int honk_model_create(const honk_model_config* cfg, const honk_tensor* tensors, int32_t n_tensors,
+                                 int device, honk_model** out) {
+  HONK_CHECK(cfg && out && (tensors || n_tensors == 0), HONK_ERR_INVALID, "honk_model_create: null argument");
+  HONK_TRY(honk_device_check(device));
+  std::vector<Expect> exp;
+  std::vector<std::string> ignorable;
+  HONK_TRY(expected_keys(*cfg, exp, ignorable));
+  std::unique_ptr<honk_model, int (*)(honk_model*)> m(new honk_model(), honk_model_destroy);
+  m->cfg = *cfg;
+  m->device = device;
+  m->H0 = cfg->height > 0 ? cfg->height : 101;
+  m->W0 = cfg->width > 0 ? cfg->width : 40;
+  m->cfg.height = m->H0;
+  m->cfg.width = m->W0;
+  m->Hr = m->H0;
+  m->Wr = m->W0;
+  if (cfg->family == HONK_FAMILY_RES && cfg->res_pool[0] > 0) {
+    HONK_CHECK(cfg->res_pool[1] > 0, HONK_ERR_INVALID, "bad res_pool");
+    m->Hr = m->H0 / cfg->res_pool[0];
+    m->Wr = m->W0 / cfg->res_pool[1];
+    HONK_CHECK(m->Hr >= 1 && m->Wr >= 1, HONK_ERR_INVALID, "res_pool larger than the input");
+  }
+  // strict key check, like load_state_dict
+  for (int i = 0; i < n_tensors; ++i) {
+    const honk_tensor& t = tensors[i];
+    HONK_CHECK(t.name, HONK_ERR_KEY, "tensor %d has no name", i);
+    const std::string name(t.name);
+    bool ign = false;
+    for (auto& s : ignorable) ign |= (s == name);
+    if (ign) continue;
+    const Expect* e = nullptr;
+    for (auto& x : exp)
+      if (x.name == name) e = &x;
+    HONK_CHECK(e, HONK_ERR_KEY, "unexpected key \"%s\" in state_dict", t.name);
+    HONK_CHECK(!m->host.count(name), HONK_ERR_KEY, "duplicate key \"%s\"", t.name);
+    bool same = t.ndim == static_cast<int>(e->dims.size()) && t.h_data != nullptr;
+    for (int d = 0; same && d < t.ndim; ++d) same = t.dims[d] == e->dims[d];
+    HONK_CHECK(same, HONK_ERR_KEY, "size mismatch for \"%s\"", t.name);
+    HostTensor h;
+    h.dims = e->dims;
+    h.data.assign(static_cast<const float*>(t.h_data), static_cast<const float*>(t.h_data) + h.numel());
+    m->host.emplace(name, std::move(h));
+  }
+  for (auto& x : exp) HONK_CHECK(m->host.count(x.name), HONK_ERR_KEY, "missing key \"%s\" in state_dict", x.name.c_str());
+
+  HONK_CUDA(cudaSetDevice(device));
+  m->n_sms = num_sms(device);
+  for (auto& kv : m->host) {
+    float* d = nullptr;
+    HONK_TRY(upload(m.get(), kv.second.data, &d));
+    m->dev[kv.first] = d;
+  }
+  if (cfg->family == HONK_FAMILY_RES) {
+    for (int i = 1; i <= cfg->n_layers; ++i) {
+      const HostTensor& var = m->host.at("bn" + std::to_string(i) + ".running_var");
+      std::vector<float> sc(var.data.size());
+      // nn.BatchNorm2d(affine=False) in eval mode, eps = 1e-5 (model.py:100)
+      for (size_t k = 0; k < sc.size(); ++k) sc[k] = 1.0f / std::sqrt(var.data[k] + 1e-5f);
+      float* d = nullptr;
+      HONK_TRY(upload(m.get(), sc, &d));
+      m->bn_scale.push_back(d);
+    }
+    if (cfg->precision == 0) {
+      HONK_TRY(res_tc_plan_create(m.get()));
+      if (m->tc) m->path = "tcgen05-f16";
+    }
+  }
+  *out = m.release();
+  return HONK_OK;
+}
+
+extern "C" int honk_model_destroy(honk_model* m) {
+  if (!m) return HONK_OK;
+  if (m->tc) res_tc_plan_free(m->tc);
+  for (void* p : m->owned) cudaFree(p);
+  delete m;
+  return HONK_OK;
+}
+
+extern "C" const char* honk_model_path(const honk_model* m) { return m ? m->path.c_str() : ""; }
+
+extern "C" int64_t honk_model_workspace_bytes(const honk_model* m, int64_t n_clips) {
+  if (!m || n_clips <= 0) return 0;
+  return m->tc ? res_tc_workspace_bytes(m, n_clips) : f32_workspace(m, n_clips);
+}
+
+extern "C" int honk_model_forward(const honk_model* m, const float* d_mfcc, int64_t n_clips, float* d_logits,
+                                  void* d_workspace, int64_t workspace_bytes, void* stream) {
+  HONK_CHECK(m, HONK_ERR_INVALID, "honk_model_forward: null model");
+  HONK_CHECK(n_clips >= 0, HONK_ERR_INVALID, "negative n_clips");
+  if (n_clips == 0) return HONK_OK;
+  HONK_CHECK(d_mfcc && d_logits, HONK_ERR_INVALID, "honk_model_forward: null buffer");
+  HONK_CHECK(d_workspace && workspace_bytes >= honk_model_workspace_bytes(m, n_clips), HONK_ERR_WORKSPACE,
+             "workspace too small: %lld < %lld bytes", static_cast<long long>(workspace_bytes),
+             static_cast<long long>(honk_model_workspace_bytes(m, n_clips)));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (m->tc) return res_tc_forward(m, d_mfcc, n_clips, d_logits, d_workspace, workspace_bytes, s);
+  const int64_t in_per = static_cast<int64_t>(m->H0) * m->W0;
+  for (int64_t c0 = 0; c0 < n_clips; c0 += kChunkF32) {
+    const int B = static_cast<int>(std::min(kChunkF32, n_clips - c0));
+    Arena ar(d_workspace, workspace_bytes);
+    const float* x = d_mfcc + c0 * in_per;
+    float* y = d_logits + c0 * m->cfg.n_labels;
+    if (m->cfg.family == HONK_FAMILY_RES) HONK_TRY(forward_res_f32(m, x, B, y, ar, s));
+    else HONK_TRY(forward_cnn_f32(m, x, B, y, ar, s));
+    HONK_CHECK(ar.ok(), HONK_ERR_WORKSPACE, "internal: workspace overrun");
+  }
+  return HONK_OK;
+}
+
+extern "C" int64_t honk_model_workspace_bytes_pcm(const honk_model* m, const honk_frontend* fe, int64_t n_clips,
+                                                  int64_t n_samples) {
+  if (!m || !fe || n_clips <= 0) return 0;
+  const int64_t mf = align_up(n_clips * honk_frontend_num_frames(fe, n_samples) * m->W0 * 4, 256);
+  return mf + honk_model_workspace_bytes(m, n_clips);
+}
+
+extern "C" int honk_model_forward_pcm(const honk_model* m, const honk_frontend* fe, const void* d_pcm, int dtype,
+                                      int64_t n_clips, int64_t n_samples, int64_t clip_stride, float* d_logits,
+                                      void* d_workspace, int64_t workspace_bytes, void* stream) {
+  HONK_CHECK(m && fe, HONK_ERR_INVALID, "honk_model_forward_pcm: null handle");
+  if (n_clips == 0) return HONK_OK;
+  HONK_CHECK(honk_frontend_num_frames(fe, n_samples) == m->H0, HONK_ERR_INVALID,
+             "front end yields %lld frames but the model expects %d",
+             static_cast<long long>(honk_frontend_num_frames(fe, n_samples)), m->H0);
+  HONK_CHECK(fe_n_dct(fe) == m->W0, HONK_ERR_INVALID, "front end yields %d coefficients but the model expects %d",
+             fe_n_dct(fe), m->W0);
+  HONK_CHECK(d_workspace && workspace_bytes >= honk_model_workspace_bytes_pcm(m, fe, n_clips, n_samples),
+             HONK_ERR_WORKSPACE, "workspace too small");
+  const int64_t mf = align_up(n_clips * static_cast<int64_t>(m->H0) * m->W0 * 4, 256);
+  float* mfcc = static_cast<float*>(d_workspace);
+  HONK_TRY(honk_frontend_mfcc(fe, d_pcm, dtype, n_clips, n_samples, clip_stride, mfcc, stream));
+  return honk_model_forward(m, mfcc, n_clips, d_logits, static_cast<char*>(d_workspace) + mf,
+                            workspace_bytes - mf, stream);
+}

@@ -1,0 +1,53 @@
+// Model handle shared by the FP32 CUDA-core path (model.cu) and the tcgen05 path (res_tc.cu).
+#pragma once
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "generic_ops.cuh"
+
+namespace honk {
+
+struct HostTensor {
+  std::vector<int64_t> dims;
+  std::vector<float> data;
+  int64_t numel() const {
+    int64_t n = 1;
+    for (auto d : dims) n *= d;
+    return n;
+  }
+};
+
+struct ResTcPlan;   // res_tc.cu
+void res_tc_plan_free(ResTcPlan*);
+
+}  // namespace honk
+
+struct honk_model {
+  honk_model_config cfg{};
+  int device = 0;
+  int n_sms = 148;
+  std::map<std::string, honk::HostTensor> host;      // validated state_dict (float32)
+  std::map<std::string, float*> dev;                 // same tensors on the device (FP32 path)
+  std::vector<float*> bn_scale;                      // [n_layers] 1/sqrt(var + 1e-5), device
+  std::vector<void*> owned;                          // every cudaMalloc of this handle
+  honk::ResTcPlan* tc = nullptr;                     // non-null => tcgen05 path is used
+  std::string path = "cuda-core-f32";
+  // geometry derived from cfg
+  int H0 = 101, W0 = 40;                             // input
+  int Hr = 101, Wr = 40;                             // res*: map size after the optional pool
+};
+
+namespace honk {
+
+// res_tc.cu: builds the tensor-core plan when the architecture has one (res* models).
+// Returns HONK_OK with m->tc == nullptr when it does not apply.
+int fe_n_dct(const honk_frontend* fe);   // frontend.cu
+int res_tc_plan_create(honk_model* m);
+int64_t res_tc_workspace_bytes(const honk_model* m, int64_t n_clips);
+int res_tc_forward(const honk_model* m, const float* d_mfcc, int64_t n_clips, float* d_logits, void* ws,
+                   int64_t ws_bytes, cudaStream_t s);
+
+}  // namespace honk

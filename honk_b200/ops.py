@@ -1,0 +1,94 @@
+"""torch custom ops (``torch.ops.honk_b200.*``) over the C ABI.
+
+PyTorch is plumbing here: it allocates the output/workspace tensors and supplies the
+current CUDA stream; the arithmetic happens in libhonk_b200.so.  Handles travel as
+Python ints (the opaque pointers of include/honk_b200.h).
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _native as N
+
+
+def _prep_pcm(pcm):
+    N.require_cuda(pcm, "pcm")
+    if pcm.dim() != 2:
+        raise ValueError("honk_b200: pcm must be [n_clips, n_samples]")
+    if pcm.stride(1) != 1:
+        pcm = pcm.contiguous()
+    return pcm
+
+
+@torch.library.custom_op("honk_b200::frontend_mfcc", mutates_args=(), device_types="cuda")
+def frontend_mfcc(pcm: torch.Tensor, frontend: int, n_frames: int, n_dct: int) -> torch.Tensor:
+    pcm = _prep_pcm(pcm)
+    out = torch.empty((pcm.shape[0], n_frames, n_dct), dtype=torch.float32, device=pcm.device)
+    with torch.cuda.device(pcm.device):
+        N.check(N.lib().honk_frontend_mfcc(frontend, pcm.data_ptr(), N.pcm_dtype_code(pcm), pcm.shape[0],
+                                           pcm.shape[1], pcm.stride(0), out.data_ptr(),
+                                           N.stream_ptr(pcm.device)))
+    return out
+
+
+@frontend_mfcc.register_fake
+def _(pcm, frontend, n_frames, n_dct):
+    return pcm.new_empty((pcm.shape[0], n_frames, n_dct), dtype=torch.float32)
+
+
+@torch.library.custom_op("honk_b200::model_forward", mutates_args=(), device_types="cuda")
+def model_forward(mfcc: torch.Tensor, model: int, n_labels: int) -> torch.Tensor:
+    N.require_cuda(mfcc, "model input")
+    x = mfcc.to(torch.float32).contiguous()          # inputs may arrive Fortran-ordered (manage_audio.py:41)
+    B = x.shape[0]
+    out = torch.empty((B, n_labels), dtype=torch.float32, device=x.device)
+    L = N.lib()
+    ws_bytes = int(L.honk_model_workspace_bytes(model, B))
+    ws = torch.empty((max(ws_bytes, 1),), dtype=torch.uint8, device=x.device)
+    with torch.cuda.device(x.device):
+        N.check(L.honk_model_forward(model, x.data_ptr(), B, out.data_ptr(), ws.data_ptr(), ws_bytes,
+                                     N.stream_ptr(x.device)))
+    return out
+
+
+@model_forward.register_fake
+def _(mfcc, model, n_labels):
+    return mfcc.new_empty((mfcc.shape[0], n_labels), dtype=torch.float32)
+
+
+@torch.library.custom_op("honk_b200::model_forward_pcm", mutates_args=(), device_types="cuda")
+def model_forward_pcm(pcm: torch.Tensor, model: int, frontend: int, n_labels: int) -> torch.Tensor:
+    pcm = _prep_pcm(pcm)
+    B = pcm.shape[0]
+    out = torch.empty((B, n_labels), dtype=torch.float32, device=pcm.device)
+    L = N.lib()
+    ws_bytes = int(L.honk_model_workspace_bytes_pcm(model, frontend, B, pcm.shape[1]))
+    ws = torch.empty((max(ws_bytes, 1),), dtype=torch.uint8, device=pcm.device)
+    with torch.cuda.device(pcm.device):
+        N.check(L.honk_model_forward_pcm(model, frontend, pcm.data_ptr(), N.pcm_dtype_code(pcm), B, pcm.shape[1],
+                                         pcm.stride(0), out.data_ptr(), ws.data_ptr(), ws_bytes,
+                                         N.stream_ptr(pcm.device)))
+    return out
+
+
+@model_forward_pcm.register_fake
+def _(pcm, model, frontend, n_labels):
+    return pcm.new_empty((pcm.shape[0], n_labels), dtype=torch.float32)
+
+
+@torch.library.custom_op("honk_b200::label_from_logits", mutates_args=(), device_types="cuda")
+def label_from_logits(logits: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
+    N.require_cuda(logits, "logits")
+    z = logits.to(torch.float32).contiguous()
+    labels = torch.empty((z.shape[0],), dtype=torch.int32, device=z.device)
+    probs = torch.empty((z.shape[0],), dtype=torch.float32, device=z.device)
+    with torch.cuda.device(z.device):
+        N.check(N.lib().honk_label_from_logits(z.data_ptr(), z.shape[0], z.shape[1], labels.data_ptr(),
+                                               probs.data_ptr(), N.stream_ptr(z.device)))
+    return labels, probs
+
+
+@label_from_logits.register_fake
+def _(logits):
+    return (logits.new_empty((logits.shape[0],), dtype=torch.int32),
+            logits.new_empty((logits.shape[0],), dtype=torch.float32))

@@ -1,0 +1,170 @@
+/*
+ * honk_b200.h - C ABI of libhonk_b200.so, the B200 (sm_100a) implementation of Honk's
+ * batched keyword-spotting inference path.
+ *
+ * The reference (ljj7975/honk) is pure Python and has no FFI; this header IS the boundary
+ * a maintainer binds (ctypes stub in INTEGRATION.md).  Each entry point names the
+ * reference interface it replaces (paths relative to the reference tree).
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative honk_status; the message for the
+ *     calling thread's last failure is honk_last_error().  Nothing throws across the ABI.
+ *   - pointers named d_* are DEVICE pointers owned by the caller (PyTorch tensors in the
+ *     Python shim); h_* are HOST pointers.  The library owns only model handles.
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it and nothing
+ *     synchronises, so calls are re-entrant across streams/threads (a model handle is
+ *     immutable after creation; scratch memory is the caller-provided workspace).
+ *   - there is NO CPU fallback: a missing/unsupported GPU is an error (HONK_ERR_DEVICE).
+ */
+#ifndef HONK_B200_H_
+#define HONK_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HONK_B200_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define HONK_API __attribute__((visibility("default")))
+#else
+#define HONK_API
+#endif
+
+typedef enum honk_status {
+  HONK_OK = 0,
+  HONK_ERR_INVALID = -1,   /* bad argument (shape, dtype, null pointer)            */
+  HONK_ERR_KEY = -2,       /* state_dict key missing / unexpected / wrong shape    */
+  HONK_ERR_DEVICE = -3,    /* no CUDA device or not sm_100                         */
+  HONK_ERR_CUDA = -4,      /* a CUDA runtime/driver call failed                    */
+  HONK_ERR_WORKSPACE = -5, /* caller workspace too small                           */
+  HONK_ERR_UNSUPPORTED = -6
+} honk_status;
+
+typedef enum honk_pcm_dtype {
+  HONK_PCM_I16 = 0,        /* int16 wire format, scaled by 1/32768 (service.py:98) */
+  HONK_PCM_F32 = 1,        /* float32 in [-1,1]  (model.py:295-303)                */
+  HONK_PCM_F64 = 2         /* float64 in [-1,1]  (service.py:98 result)            */
+} honk_pcm_dtype;
+
+HONK_API int honk_abi_version(void);
+HONK_API const char* honk_last_error(void);
+
+/* Verifies that `device` is a CUDA device of compute capability 10.x. */
+HONK_API int honk_device_check(int device);
+
+/* ------------------------------------------------------------------------------------------
+ * Front end.  Replaces AudioPreprocessor.__init__ / compute_mfccs
+ * (utils/manage_audio.py:19-28, 30-42) and the per-clip loop of SpeechDataset.collate_fn
+ * (utils/model.py:253-265).
+ * ---------------------------------------------------------------------------------------- */
+typedef struct honk_frontend_config {
+  int32_t sr;              /* 16000 */
+  int32_t n_fft;           /* 480   (multiple of 4, <= 512)        */
+  int32_t hop_length;      /* 160   = sr / 1000 * hop_ms           */
+  int32_t n_mels;          /* 40    (<= 64)                        */
+  int32_t n_dct_filters;   /* 40    (<= 64)                        */
+  float f_min;             /* 20    */
+  float f_max;             /* 4000  */
+} honk_frontend_config;
+
+typedef struct honk_frontend honk_frontend;
+
+/* Builds the window / DFT / mel / DCT tables in float64 on the host exactly as
+ * librosa 0.6 does and uploads them to `device`. */
+HONK_API int honk_frontend_create(const honk_frontend_config* cfg, int device, honk_frontend** out);
+HONK_API int honk_frontend_destroy(honk_frontend* fe);
+/* frames produced for n_samples input samples: 1 + n_samples / hop_length (centre=True) */
+HONK_API int64_t honk_frontend_num_frames(const honk_frontend* fe, int64_t n_samples);
+/* host copies of the tables: dct [n_dct, n_mels], mel [n_mels, 1 + n_fft/2], float64 */
+HONK_API int honk_frontend_get_dct(const honk_frontend* fe, double* h_out);
+HONK_API int honk_frontend_get_mel(const honk_frontend* fe, double* h_out);
+
+/* d_pcm: [n_clips, clip_stride] elements of `dtype`, first n_samples of each row used.
+ * d_mfcc: float32 [n_clips, n_frames, n_dct_filters] (time-major, the layout
+ * collate_fn's reshape(1,-1,40) and service.py's squeeze(2) give the model). */
+HONK_API int honk_frontend_mfcc(const honk_frontend* fe, const void* d_pcm, int dtype, int64_t n_clips,
+                       int64_t n_samples, int64_t clip_stride, float* d_mfcc, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Models.  Replaces SpeechResModel / SpeechModel construction, load_state_dict and forward
+ * (utils/model.py:72-80, 82-121, 123-205) for every entry of _configs (model.py:381-414).
+ * ---------------------------------------------------------------------------------------- */
+typedef enum honk_family { HONK_FAMILY_RES = 0, HONK_FAMILY_CNN = 1 } honk_family;
+
+/* Plain-integer mirror of a find_config() dict (model.py:59-62, 381-414).  Absent optional
+ * keys are 0. */
+typedef struct honk_model_config {
+  int32_t family;            /* honk_family: name.startswith("res") (model.py:51-57)        */
+  int32_t n_labels;
+  int32_t height, width;     /* input frames x coefficients: 101 x 40                       */
+  /* res* (model.py:85-102) */
+  int32_t n_feature_maps;
+  int32_t n_layers;
+  int32_t use_dilation;
+  int32_t res_pool[2];       /* {0,0} when the config has no "res_pool"                     */
+  /* cnn-* (model.py:126-184) */
+  int32_t n_feature_maps1;
+  int32_t conv1_size[2], conv1_pool[2], conv1_stride[2];
+  int32_t has_conv2;
+  int32_t n_feature_maps2;
+  int32_t conv2_size[2], conv2_pool[2], conv2_stride[2];
+  int32_t tf_variant;        /* 0 => "lin" layer (-> 32) present, dnn1 followed by ReLU      */
+  int32_t dnn1_size, dnn2_size;  /* 0 when absent                                           */
+  /* build options (extensions, default 0) */
+  int32_t precision;         /* 0 = f16 tensor-core operands + f32 accumulate where a tcgen05
+                                path exists; 1 = force the all-f32 CUDA-core path           */
+} honk_model_config;
+
+/* One state_dict entry under the reference's key name (model.py:85-102). */
+typedef struct honk_tensor {
+  const char* name;          /* e.g. "conv3.weight", "bn3.running_var", "output.bias"       */
+  const void* h_data;        /* host, contiguous, float32 (int64 for num_batches_tracked)   */
+  int32_t ndim;
+  int64_t dims[4];
+} honk_tensor;
+
+typedef struct honk_model honk_model;
+
+/* Strict load (like load_state_dict, model.py:79-80): every expected key must be present
+ * with the right shape and no unknown key may appear (num_batches_tracked is accepted and
+ * ignored).  BatchNorm statistics are folded and weights repacked for the kernels here. */
+HONK_API int honk_model_create(const honk_model_config* cfg, const honk_tensor* tensors, int32_t n_tensors,
+                      int device, honk_model** out);
+HONK_API int honk_model_destroy(honk_model* m);
+
+/* Scratch bytes honk_model_forward* needs for a batch of n_clips (256-byte aligned). */
+HONK_API int64_t honk_model_workspace_bytes(const honk_model* m, int64_t n_clips);
+
+/* d_mfcc float32 [n_clips, height, width] -> d_logits float32 [n_clips, n_labels]
+ * (pre-softmax, like forward(); model.py:104-121, 186-205). */
+HONK_API int honk_model_forward(const honk_model* m, const float* d_mfcc, int64_t n_clips, float* d_logits,
+                       void* d_workspace, int64_t workspace_bytes, void* stream);
+
+/* Fused path: PCM -> front end -> CNN without materialising MFCCs for the caller.
+ * Same semantics as honk_frontend_mfcc followed by honk_model_forward. */
+HONK_API int honk_model_forward_pcm(const honk_model* m, const honk_frontend* fe, const void* d_pcm, int dtype,
+                           int64_t n_clips, int64_t n_samples, int64_t clip_stride, float* d_logits,
+                           void* d_workspace, int64_t workspace_bytes, void* stream);
+HONK_API int64_t honk_model_workspace_bytes_pcm(const honk_model* m, const honk_frontend* fe, int64_t n_clips,
+                                       int64_t n_samples);
+
+/* softmax + argmax + max-prob per clip: the tail of TorchLabelService.label
+ * (service.py:103-104) and print_eval's argmax (utils/train.py:41-46).
+ * d_labels int32 [n_clips], d_probs float32 [n_clips] (either may be NULL). */
+HONK_API int honk_label_from_logits(const float* d_logits, int64_t n_clips, int32_t n_labels, int32_t* d_labels,
+                           float* d_probs, void* stream);
+
+/* Number of kernels the library has launched in this process (for bench.py's gpu_launches). */
+HONK_API int64_t honk_launch_count(void);
+
+/* Name of the code path honk_model_forward takes: "tcgen05-f16" or "cuda-core-f32". */
+HONK_API const char* honk_model_path(const honk_model* m);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HONK_B200_H_ */

@@ -22,7 +22,8 @@ EXPORTS = [
     "honk_frontend_destroy", "honk_frontend_num_frames", "honk_frontend_get_dct", "honk_frontend_get_mel",
     "honk_frontend_mfcc", "honk_model_create", "honk_model_destroy", "honk_model_workspace_bytes",
     "honk_model_forward", "honk_model_forward_pcm", "honk_model_workspace_bytes_pcm",
-    "honk_label_from_logits", "honk_launch_count", "honk_model_path",
+    "honk_label_from_logits", "honk_launch_count", "honk_model_path", "honk_profile_enable",
+    "honk_profile_reset", "honk_profile_get",
 ]
 
 
@@ -85,6 +86,8 @@ def lib():
         L.honk_label_from_logits.argtypes = [vp, i64, i32, vp, vp, vp]
         L.honk_launch_count.restype = i64
         L.honk_model_path.argtypes = [vp]
+        L.honk_profile_enable.argtypes = [C.c_int]
+        L.honk_profile_get.argtypes = [C.c_char_p, C.POINTER(C.c_double), C.POINTER(i64)]
         L.honk_model_path.restype = C.c_char_p
         if L.honk_abi_version() != 1:
             raise RuntimeError("honk_b200: ABI version mismatch")
@@ -123,3 +126,18 @@ def pcm_dtype_code(t):
     if t.dtype == torch.float64:
         return PCM_F64
     raise ValueError("honk_b200: PCM must be int16, float32 or float64, got %s" % t.dtype)
+
+
+def profile_enable(on=True):
+    lib().honk_profile_enable(1 if on else 0)
+
+
+def profile_reset():
+    lib().honk_profile_reset()
+
+
+def profile_get(span):
+    """(total milliseconds, span count) recorded for ``span`` since the last reset."""
+    ms, n = C.c_double(0), C.c_int64(0)
+    check(lib().honk_profile_get(span.encode(), C.byref(ms), C.byref(n)))
+    return ms.value, n.value

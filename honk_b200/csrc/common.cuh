@@ -73,4 +73,12 @@ struct Arena {
 
 int num_sms(int device);
 
+// Device-time spans (enabled by honk_profile_enable); no-ops otherwise.
+struct ProfSpan {
+  int slot = -1;
+  cudaStream_t stream;
+  ProfSpan(const char* name, cudaStream_t s);
+  ~ProfSpan();
+};
+
 }  // namespace honk

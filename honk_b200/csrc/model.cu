@@ -307,6 +307,7 @@ extern "C" int honk_model_forward(const honk_model* m, const float* d_mfcc, int6
              static_cast<long long>(honk_model_workspace_bytes(m, n_clips)));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (m->tc) return res_tc_forward(m, d_mfcc, n_clips, d_logits, d_workspace, workspace_bytes, s);
+  ProfSpan span("f32_model", s);
   const int64_t in_per = static_cast<int64_t>(m->H0) * m->W0;
   for (int64_t c0 = 0; c0 < n_clips; c0 += kChunkF32) {
     const int B = static_cast<int>(std::min(kChunkF32, n_clips - c0));

@@ -1,0 +1,111 @@
+"""Drop-in for ``service.TorchLabelService`` (service.py:28-51, 72-110 of the reference).
+
+``label(wav_bytes) -> (label, prob)`` keeps the reference semantics (int16 PCM / 32768 ->
+MFCC -> model -> softmax -> argmax) but the whole chain, including softmax/argmax, runs on
+the GPU through one fused C-ABI call; ``label_batch`` is the batched extension used for the
+sliding windows of the ``/listen`` endpoint (server.py:99-112).  Thread-safe: the model
+handle is immutable and every call allocates its own workspace on the caller's stream.
+"""
+from __future__ import annotations
+
+import os
+import wave
+
+import numpy as np
+import torch
+
+from . import model as mod
+from . import ops
+from .manage_audio import AudioPreprocessor
+
+
+def stride(array, stride_size, window_size):
+    """Sliding windows (service.py:106-110)."""
+    i = 0
+    while i + window_size <= len(array):
+        yield array[i:i + window_size]
+        i += stride_size
+
+
+class LabelService(object):
+    def evaluate(self, speech_dirs, indices=[]):
+        """Folder accuracy (service.py:29-48); one batched call per folder instead of per file."""
+        dir_labels = {}
+        if indices:
+            real_labels = [self.labels[i] for i in indices]
+        else:
+            real_labels = [os.path.basename(os.path.normpath(d)) for d in speech_dirs]
+        for i, label in enumerate(real_labels):
+            if label not in self.labels:
+                real_labels[i] = "_unknown_"
+            dir_labels[speech_dirs[i]] = real_labels[i]
+        accuracy = []
+        for folder in speech_dirs:
+            clips = []
+            for filename in sorted(os.listdir(folder)):
+                with wave.open(os.path.join(folder, filename)) as f:
+                    clips.append(f.readframes(16000))
+            for label, _ in self.label_batch(clips):
+                accuracy.append(int(label == dir_labels[folder]))
+        return sum(accuracy) / len(accuracy)
+
+    def label(self, wav_data):
+        raise NotImplementedError
+
+
+class TorchLabelService(LabelService):
+    def __init__(self, model_filename, no_cuda=False, labels=["_silence_", "_unknown_", "command", "random"],
+                 model_type=mod.ConfigType.CNN_TRAD_POOL2, n_samples=16000):
+        if no_cuda:
+            raise RuntimeError("honk_b200: no_cuda=True is not supported (there is no CPU fallback)")
+        self.labels = labels
+        self.model_filename = model_filename
+        self.no_cuda = no_cuda
+        self.model_type = model_type      # extension: the reference hard-codes cnn-trad-pool2 (service.py:81)
+        self.n_samples = n_samples
+        self.audio_processor = AudioPreprocessor()
+        self.reload()
+
+    def reload(self):
+        config = mod.find_config(self.model_type)
+        config["n_labels"] = len(self.labels)          # mutates the shared dict like service.py:82
+        self.model = mod.find_model(self.model_type)(config)
+        self.model.cuda()
+        if isinstance(self.model_filename, dict):
+            self.model.load_state_dict(self.model_filename)
+        else:
+            self.model.load(self.model_filename)
+        self.model.eval()
+
+    def _pcm_tensor(self, clips):
+        rows = np.zeros((len(clips), self.n_samples), dtype=np.int16)
+        for i, c in enumerate(clips):
+            a = np.frombuffer(c, dtype=np.int16) if isinstance(c, (bytes, bytearray, memoryview)) else np.asarray(c, dtype=np.int16)
+            n = min(len(a), self.n_samples)
+            rows[i, :n] = a[:n]                        # short clips are zero-padded (model.py:297)
+        return torch.from_numpy(rows).pin_memory().to(self.audio_processor.device, non_blocking=True)
+
+    def label_batch(self, clips):
+        """List of int16 PCM byte strings -> list of ``(label, prob)``."""
+        if len(clips) == 0:
+            return []
+        with torch.no_grad():
+            logits = self.model.forward_pcm(self._pcm_tensor(clips), self.audio_processor)
+            idx, prob = ops.label_from_logits(logits)
+            idx, prob = idx.cpu().numpy(), prob.cpu().numpy()
+        return [(self.labels[int(i)], float(p)) for i, p in zip(idx, prob)]
+
+    def label(self, wav_data):
+        """Labels audio data as one of the specified trained labels (service.py:89-104)."""
+        return self.label_batch([wav_data])[0]
+
+    def listen(self, wav_data, stride_ms=500, min_keyword_prob=0.85, keyword="command", method="all_label"):
+        """Batched form of ``ListenEndpoint.POST`` (server.py:99-112): all 1-s windows at once."""
+        step = int(2 * 16000 * stride_ms / 1000)
+        windows = list(stride(wav_data, step, 2 * 16000))
+        labels = {}
+        for label, prob in self.label_batch(windows):
+            labels[label] = labels.get(label, 0.0) + float(prob)
+            if label == keyword and prob >= min_keyword_prob and method == "command_tagging":
+                return dict(contains_command=True)
+        return dict(contains_command=False) if method == "command_tagging" else labels

@@ -161,6 +161,14 @@ HONK_API int honk_label_from_logits(const float* d_logits, int64_t n_clips, int3
 /* Number of kernels the library has launched in this process (for bench.py's gpu_launches). */
 HONK_API int64_t honk_launch_count(void);
 
+/* Optional per-span device timing (CUDA events on the launching stream) used by bench.py for
+ * the roofline line.  Spans: "frontend", "res_conv0", "res_conv", "res_tail", "f32_model".
+ * honk_profile_get synchronises the recorded events and returns the summed milliseconds and
+ * the number of spans since the last reset. */
+HONK_API int honk_profile_enable(int on);
+HONK_API int honk_profile_reset(void);
+HONK_API int honk_profile_get(const char* span, double* ms_total, int64_t* n_spans);
+
 /* Name of the code path honk_model_forward takes: "tcgen05-f16" or "cuda-core-f32". */
 HONK_API const char* honk_model_path(const honk_model* m);
 

@@ -1,0 +1,106 @@
+"""GPU parity of the front end (through the C ABI) against the CPU oracle and golden vectors.
+
+Tolerance: the kernel computes in FP64 like the reference, so the bound is set by the final
+float32 cast and the float32 power: |d MFCC| <= 2e-4 absolute (MFCC magnitudes reach ~150)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from honk_b200 import synth
+
+pytestmark = pytest.mark.gpu
+ATOL = 2e-4
+
+
+@pytest.fixture(scope="module")
+def pre():
+    from honk_b200 import AudioPreprocessor
+    return AudioPreprocessor()
+
+
+@pytest.fixture(scope="module")
+def orc():
+    from oracle import honk_oracle
+    return honk_oracle
+
+
+def test_tables_match_oracle(pre, orc):
+    np.testing.assert_allclose(pre.dct_filters, orc.dct_filters(40, 40), rtol=0, atol=1e-15)
+    np.testing.assert_allclose(pre.mel_basis(), orc.mel_filterbank(), rtol=0, atol=1e-15)
+    assert (pre.n_mels, pre.sr, pre.f_max, pre.f_min, pre.n_fft, pre.hop_length) == (40, 16000, 4000, 20, 480, 160)
+
+
+def test_golden_special_clips(pre, golden_dir):
+    g = np.load(os.path.join(golden_dir, "mfcc_golden.npz"))
+    for name, pcm in synth.special_clips().items():
+        out = pre.compute_mfccs(pcm / 32768.0)                  # float64 like service.py:98
+        assert out.shape == (101, 40, 1) and out.dtype == np.float32 and out.flags["F_CONTIGUOUS"]
+        err = np.abs(out[:, :, 0] - g["special/" + name]).max()
+        assert err <= ATOL, (name, err)
+    assert np.all(pre.compute_mfccs(np.zeros(16000)) == 0)      # the data > 0 guard (manage_audio.py:39)
+
+
+def test_golden_random_int16_batch(pre, golden_dir):
+    g = np.load(os.path.join(golden_dir, "mfcc_golden.npz"))
+    pcm = torch.from_numpy(synth.make_clips(8, start=0, seed=1234)).cuda()
+    out = pre.compute_mfccs_batch(pcm)
+    assert out.shape == (8, 101, 40) and out.is_cuda
+    assert np.abs(out.cpu().numpy() - g["random_pcm_start0_seed1234"]).max() <= ATOL
+    f32 = (pcm[:2].to(torch.float32) / 32768.0)
+    assert np.abs(pre.compute_mfccs_batch(f32).cpu().numpy() - g["random_f32in"]).max() <= ATOL
+
+
+def test_against_oracle_fresh_clips(pre, orc):
+    clips = synth.make_clips(48, start=5000, seed=77)
+    ref = orc.AudioPreprocessorOracle().compute_mfccs_batch([orc.pcm16_to_float(c) for c in clips])
+    got = pre.compute_mfccs_batch(torch.from_numpy(clips).cuda()).cpu().numpy()
+    err = np.abs(got - ref)
+    assert err.max() <= ATOL, err.max()
+    assert not np.isnan(got).any()
+
+
+def test_dtypes_agree_and_strided_rows(pre):
+    pcm = torch.from_numpy(synth.make_clips(5, start=900)).cuda()
+    a = pre.compute_mfccs_batch(pcm)
+    b = pre.compute_mfccs_batch(pcm.to(torch.float64) / 32768.0)
+    assert torch.equal(a, b)                                    # int16/32768 is exact in FP64
+    wide = torch.zeros((5, 20000), dtype=torch.int16, device="cuda")
+    wide[:, :16000] = pcm
+    assert torch.equal(pre.compute_mfccs_batch(wide[:, :16000]), a)   # row stride != n_samples
+
+
+def test_large_batch_properties(pre):
+    # size-independent properties at a BASELINE-size batch: batch invariance and scale law
+    base = torch.from_numpy(synth.make_clips(64, start=300)).cuda()
+    big = base.repeat(64, 1)                                    # 4096 clips
+    out = pre.compute_mfccs_batch(big)
+    assert torch.equal(out[:64], out[-64:]) and torch.equal(out[:64], pre.compute_mfccs_batch(base))
+    # doubling the amplitude adds 2*ln(2)*sqrt(40) to c0 only (log-mel shifts by a constant)
+    x = (base[:8].to(torch.float64) / 32768.0) * 0.25
+    m1, m2 = pre.compute_mfccs_batch(x), pre.compute_mfccs_batch(2 * x)
+    d = (m2 - m1).cpu().numpy()
+    live = (base[:8].abs().amax(1) > 0).cpu().numpy()
+    assert np.abs(d[live][:, :, 0] - 2 * np.log(2) * np.sqrt(40)).max() < 1e-3
+    assert np.abs(d[live][:, :, 1:]).max() < 1e-3
+
+
+def test_other_parameters(pre, orc):
+    from honk_b200 import AudioPreprocessor
+    p2 = AudioPreprocessor(n_mels=32, n_dct_filters=20, f_max=7600, f_min=60)
+    ref = orc.AudioPreprocessorOracle(n_mels=32, n_dct_filters=20, f_max=7600, f_min=60)
+    clip = synth.make_clip(11) / 32768.0
+    got = p2.compute_mfccs(clip)
+    assert got.shape == (101, 20, 1)
+    assert np.abs(got - ref.compute_mfccs(clip)).max() <= ATOL
+
+
+def test_errors(pre):
+    with pytest.raises(ValueError):
+        pre.compute_mfccs(np.zeros((2, 16000)))
+    with pytest.raises(ValueError):
+        pre.compute_mfccs_batch(torch.zeros(1, 100, device="cuda"))      # shorter than the reflect pad
+    assert pre.compute_mfccs_batch(torch.zeros(0, 16000, device="cuda")).shape == (0, 101, 40)
+    with pytest.raises(NotImplementedError):
+        pre.compute_pcen(np.zeros(16000))

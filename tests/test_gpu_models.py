@@ -1,0 +1,123 @@
+"""GPU parity of every architecture (through the C ABI) against the committed golden logits
+(produced by the reference's own classes) and the CPU oracle.
+
+Tolerances, relative to max|logit| of the batch:
+  cuda-core-f32 path : 2e-4   (float32 everywhere, different summation order)
+  tcgen05-f16 path   : 3e-2   (f16 operands, f32 accumulate, 7-25 stacked layers)"""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from honk_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+ARCHS = ["cnn-trad-pool2", "cnn-one-stride1", "cnn-one-fpool3", "cnn-one-fstride4", "cnn-one-fstride8",
+         "cnn-tpool2", "cnn-tpool3", "cnn-tstride2", "cnn-tstride4", "cnn-tstride8",
+         "res15", "res26", "res8", "res15-narrow", "res8-narrow", "res26-narrow"]
+TOL = {"cuda-core-f32": 2e-4, "tcgen05-f16": 3e-2}
+
+
+def load_golden(golden_dir, name):
+    g = np.load(os.path.join(golden_dir, "cnn_golden.npz"))
+    cfg = json.loads(bytes(g[name + "/config"]).decode())
+    sd = synth.make_state_dict(name, cfg, seed=1)
+    for k in g.files:
+        if k.startswith(name + "/sd/"):
+            sd[k[len(name) + 4:]] = g[k]
+    return g, cfg, sd
+
+
+def build(name, cfg, sd, precision=0):
+    import honk_b200 as hb
+    m = hb.find_model(name)(cfg)
+    m.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()}, strict=True)
+    m.precision = precision
+    return m.cuda().eval()
+
+
+@pytest.mark.parametrize("precision", [1, 0])
+@pytest.mark.parametrize("name", ARCHS)
+def test_golden_logits(golden_dir, name, precision):
+    g, cfg, sd = load_golden(golden_dir, name)
+    m = build(name, cfg, sd, precision)
+    x = torch.from_numpy(g["x"]).cuda()
+    y = m(x).cpu().numpy()
+    ref = g[name + "/logits_f64"]
+    assert y.shape == ref.shape and y.dtype == np.float32
+    path = m.native_path
+    if precision == 1:
+        assert path == "cuda-core-f32"
+    err = np.abs(y - ref).max() / np.abs(ref).max()
+    assert err <= TOL[path], (name, path, err)
+    if path == "cuda-core-f32":
+        assert (y.argmax(1) == ref.argmax(1)).all()
+
+
+@pytest.mark.parametrize("name", ["res8-narrow", "res8", "cnn-trad-pool2"])
+def test_against_oracle_batch64(name):
+    # BASELINE config 1 shape: batch 64 synthetic clips through front end + CNN
+    import honk_b200 as hb
+    from oracle import honk_oracle as orc
+    cfg = dict(hb.find_config(name))
+    cfg["n_labels"] = 12
+    clips = synth.make_clips(64, start=4000)
+    mf = orc.AudioPreprocessorOracle().compute_mfccs_batch([orc.pcm16_to_float(c) for c in clips])
+    sd = synth.make_state_dict(name, cfg, seed=3, calib_mfcc=mf[:16])
+    ref = orc.model_forward(name, sd, cfg, mf, torch.float64).numpy()
+    pre = hb.AudioPreprocessor()
+    for precision in (1, 0):
+        m = build(name, cfg, sd, precision)
+        y = m.forward_pcm(torch.from_numpy(clips).cuda(), pre).cpu().numpy()
+        err = np.abs(y - ref).max() / np.abs(ref).max()
+        assert err <= TOL[m.native_path] * 1.5, (name, m.native_path, err)
+        y2 = m(pre.compute_mfccs_batch(torch.from_numpy(clips).cuda())).cpu().numpy()
+        assert np.array_equal(y, y2)              # fused PCM entry == two-step entry
+
+
+def test_strict_state_dict_and_reload(golden_dir):
+    import honk_b200 as hb
+    g, cfg, sd = load_golden(golden_dir, "res8-narrow")
+    m = build("res8-narrow", cfg, sd, 1)
+    x = torch.from_numpy(g["x"]).cuda()
+    y0 = m(x)
+    bad = {k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()}
+    bad.pop("conv3.weight")
+    with pytest.raises(RuntimeError):
+        hb.SpeechResModel(cfg).load_state_dict(bad)
+    # weights changed in place -> the native handle is rebuilt
+    with torch.no_grad():
+        m.output.bias.add_(1.0)
+    assert torch.allclose(m(x), y0 + 1.0, atol=1e-5)
+    # non-contiguous / Fortran-ordered input (manage_audio.py:41)
+    xt = x.transpose(1, 2).contiguous().transpose(1, 2)
+    assert torch.equal(m(xt), m(x))
+    assert m(x[:0]).shape == (0, 12)
+    m.train()
+    with pytest.raises(RuntimeError):
+        m(x)
+
+
+def test_save_load_roundtrip(tmp_path, golden_dir):
+    import honk_b200 as hb
+    g, cfg, sd = load_golden(golden_dir, "cnn-trad-pool2")
+    m = build("cnn-trad-pool2", cfg, sd, 1)
+    f = str(tmp_path / "m.pt")
+    m.save(f)
+    m2 = hb.SpeechModel(cfg)
+    m2.load(f)
+    m2.cuda().eval()
+    x = torch.from_numpy(g["x"]).cuda()
+    assert torch.equal(m(x), m2(x))
+
+
+def test_label_kernel_matches_softmax():
+    from honk_b200 import ops
+    z = torch.randn(1000, 12, device="cuda") * 3
+    idx, p = ops.label_from_logits(z)
+    sm = torch.softmax(z.double(), 1)
+    assert torch.equal(idx.long(), sm.argmax(1))
+    assert torch.allclose(p.double(), sm.max(1).values, atol=1e-6)

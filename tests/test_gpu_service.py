@@ -1,0 +1,50 @@
+"""TorchLabelService-shaped calls (service.py:72-104, server.py:99-112) through the drop-in."""
+import numpy as np
+import pytest
+import torch
+
+from honk_b200 import synth
+
+pytestmark = pytest.mark.gpu
+LABELS = ["_silence_", "_unknown_"] + ["w%d" % i for i in range(10)]
+
+
+def test_label_matches_oracle():
+    import honk_b200 as hb
+    from honk_b200.service import TorchLabelService
+    from oracle import honk_oracle as orc
+    cfg = dict(hb.find_config("cnn-trad-pool2"))
+    cfg["n_labels"] = 12
+    sd = synth.make_state_dict("cnn-trad-pool2", cfg, seed=5)
+    tsd = {k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()}
+    svc = TorchLabelService(tsd, labels=LABELS)
+    assert hb.find_config("cnn-trad-pool2")["n_labels"] == 12        # shared dict mutated like service.py:82
+    pre = orc.AudioPreprocessorOracle()
+    clips = synth.make_clips(6, start=700)
+    for c in clips:
+        label, prob = svc.label(c.tobytes())
+        mf = pre.compute_mfccs(orc.pcm16_to_float(c)).squeeze(2)[None]
+        z = orc.cnn_forward(sd, cfg, mf, torch.float64).numpy()[0]
+        idx, p = orc.softmax_label(z)
+        assert label == LABELS[idx] and abs(prob - p) < 1e-3
+    hb.find_config("cnn-trad-pool2")["n_labels"] = 4
+
+
+def test_listen_windows_and_model_type():
+    import honk_b200 as hb
+    from honk_b200.service import TorchLabelService, stride
+    cfg = dict(hb.find_config("res8-narrow"))
+    sd = synth.make_state_dict("res8-narrow", cfg, seed=6)
+    tsd = {k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()}
+    svc = TorchLabelService(tsd, labels=LABELS, model_type=hb.ConfigType.RES8_NARROW)
+    long = np.concatenate([synth.make_clip(i, seed=5) for i in range(3)]).tobytes()     # 3 s
+    wins = list(stride(long, 16000, 32000))
+    assert len(wins) == 5
+    agg = svc.listen(long)
+    per = [svc.label(w) for w in wins]
+    ref = {}
+    for lab, p in per:
+        ref[lab] = ref.get(lab, 0.0) + p
+    assert set(agg) == set(ref) and all(abs(agg[k] - ref[k]) < 1e-5 for k in ref)
+    with pytest.raises(RuntimeError):
+        TorchLabelService(tsd, no_cuda=True, labels=LABELS, model_type=hb.ConfigType.RES8_NARROW)

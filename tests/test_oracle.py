@@ -1,0 +1,102 @@
+"""CPU tests of the oracle itself: it must reproduce the committed golden vectors (the CNN
+vectors were produced by the reference's own classes, tests/golden/make_golden.py) and agree
+with independent witnesses for the front end (whose parity the reference leaves unpinned)."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from honk_b200 import synth
+from oracle import honk_oracle as orc
+
+ARCHS = ["cnn-trad-pool2", "cnn-one-stride1", "cnn-one-fpool3", "cnn-one-fstride4", "cnn-one-fstride8",
+         "cnn-tpool2", "cnn-tpool3", "cnn-tstride2", "cnn-tstride4", "cnn-tstride8",
+         "res15", "res26", "res8", "res15-narrow", "res8-narrow", "res26-narrow"]
+
+
+def golden_model(golden_dir, name):
+    g = np.load(os.path.join(golden_dir, "cnn_golden.npz"))
+    cfg = json.loads(bytes(g[name + "/config"]).decode())
+    sd = synth.make_state_dict(name, cfg, seed=1)
+    for k in g.files:
+        if k.startswith(name + "/sd/"):
+            sd[k[len(name) + 4:]] = g[k]
+    return g, cfg, sd
+
+
+@pytest.mark.parametrize("name", ARCHS)
+def test_cnn_oracle_matches_reference_golden(golden_dir, name):
+    g, cfg, sd = golden_model(golden_dir, name)
+    y64 = orc.model_forward(name, sd, cfg, g["x"], torch.float64).numpy()
+    ref64 = g[name + "/logits_f64"]
+    scale = max(1.0, np.abs(ref64).max())
+    assert np.abs(y64 - ref64).max() <= 1e-9 * scale
+    y32 = orc.model_forward(name, sd, cfg, g["x"], torch.float32).numpy()
+    assert np.abs(y32 - ref64).max() <= 2e-4 * scale
+
+
+def test_mfcc_golden_frozen(golden_dir):
+    g = np.load(os.path.join(golden_dir, "mfcc_golden.npz"))
+    pre = orc.AudioPreprocessorOracle()
+    for k, pcm in synth.special_clips().items():
+        got = pre.compute_mfccs(orc.pcm16_to_float(pcm))
+        assert got.shape == (101, 40, 1) and got.dtype == np.float32 and got.flags["F_CONTIGUOUS"]
+        np.testing.assert_allclose(got[:, :, 0], g["special/" + k], rtol=0, atol=2e-5)
+    rnd = synth.make_clips(8, start=0, seed=1234)
+    got = pre.compute_mfccs_batch([orc.pcm16_to_float(c) for c in rnd])
+    np.testing.assert_allclose(got, g["random_pcm_start0_seed1234"], rtol=0, atol=2e-5)
+
+
+def test_zero_clip_stays_zero():
+    # data[data > 0] = log(...) leaves exact zeros alone (manage_audio.py:39)
+    out = orc.AudioPreprocessorOracle().compute_mfccs(np.zeros(16000))
+    assert np.all(out == 0)
+
+
+def test_mel_basis_against_torchaudio():
+    ta = pytest.importorskip("torchaudio")
+    fb = ta.functional.melscale_fbanks(241, 20.0, 4000.0, 40, 16000, norm="slaney", mel_scale="slaney").T.numpy()
+    W = orc.mel_filterbank()
+    assert np.abs(fb - W).max() <= 1e-5 * W.max()
+    nz = np.nonzero(W.sum(0))[0]
+    assert nz.min() == 1 and nz.max() == 119 and (W >= 0).all()
+
+
+def test_dct_orthonormal():
+    D = orc.dct_filters(40, 40)
+    assert np.abs(D @ D.T - np.eye(40)).max() < 1e-13
+
+
+def test_stft_against_direct_dft():
+    rng = np.random.default_rng(3)
+    y = rng.standard_normal(16000) * 0.1
+    P = orc.stft_power(y)
+    assert P.shape == (241, 101) and P.dtype == np.float32
+    ypad = np.pad(y, 240, mode="reflect")
+    n = np.arange(480)
+    win = 0.5 - 0.5 * np.cos(2 * np.pi * n / 480)
+    for t in (0, 50, 100):
+        fr = ypad[160 * t:160 * t + 480] * win
+        k = np.arange(241)[:, None]
+        X = (fr[None, :] * np.exp(-2j * np.pi * k * n[None, :] / 480)).sum(1)
+        np.testing.assert_allclose(P[:, t], np.abs(X) ** 2, rtol=2e-6, atol=1e-12)
+
+
+def test_sine_known_answer():
+    # a bin-centred sinusoid of amplitude A gives |X_b| = A*N/4 under a periodic Hann window
+    A, b = 0.5, 30
+    t = np.arange(16000) / 16000.0
+    y = A * np.sin(2 * np.pi * b * 16000 / 480.0 * t)
+    P = orc.stft_power(y)
+    np.testing.assert_allclose(P[b, 50], (A * 480 / 4) ** 2, rtol=1e-5)
+
+
+def test_flops_table():
+    from honk_b200 import model as mod
+    exp = {"res15": 1917.63e6, "res26": 878.07e6, "res8": 74.35e6, "res8-narrow": 14.05e6,
+           "res15-narrow": 342.66e6, "res26-narrow": 157.33e6, "cnn-trad-pool2": 191.95e6}
+    for name, fl in exp.items():
+        got = orc.conv_flops_per_clip(name, mod.find_config(name))
+        assert abs(got - fl) / fl < 2e-3, (name, got)

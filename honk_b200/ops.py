@@ -15,9 +15,14 @@ def _prep_pcm(pcm):
     N.require_cuda(pcm, "pcm")
     if pcm.dim() != 2:
         raise ValueError("honk_b200: pcm must be [n_clips, n_samples]")
-    if pcm.stride(1) != 1:
+    if pcm.stride(1) != 1 or (pcm.shape[0] > 1 and pcm.stride(0) < pcm.shape[1]):
         pcm = pcm.contiguous()
     return pcm
+
+
+def _row_stride(pcm):
+    # a size-1 batch dimension may carry any stride (numpy's a[None, :] gives 0)
+    return pcm.stride(0) if pcm.shape[0] > 1 else pcm.shape[1]
 
 
 @torch.library.custom_op("honk_b200::frontend_mfcc", mutates_args=(), device_types="cuda")
@@ -26,7 +31,7 @@ def frontend_mfcc(pcm: torch.Tensor, frontend: int, n_frames: int, n_dct: int) -
     out = torch.empty((pcm.shape[0], n_frames, n_dct), dtype=torch.float32, device=pcm.device)
     with torch.cuda.device(pcm.device):
         N.check(N.lib().honk_frontend_mfcc(frontend, pcm.data_ptr(), N.pcm_dtype_code(pcm), pcm.shape[0],
-                                           pcm.shape[1], pcm.stride(0), out.data_ptr(),
+                                           pcm.shape[1], _row_stride(pcm), out.data_ptr(),
                                            N.stream_ptr(pcm.device)))
     return out
 
@@ -66,7 +71,7 @@ def model_forward_pcm(pcm: torch.Tensor, model: int, frontend: int, n_labels: in
     ws = torch.empty((max(ws_bytes, 1),), dtype=torch.uint8, device=pcm.device)
     with torch.cuda.device(pcm.device):
         N.check(L.honk_model_forward_pcm(model, frontend, pcm.data_ptr(), N.pcm_dtype_code(pcm), B, pcm.shape[1],
-                                         pcm.stride(0), out.data_ptr(), ws.data_ptr(), ws_bytes,
+                                         _row_stride(pcm), out.data_ptr(), ws.data_ptr(), ws_bytes,
                                          N.stream_ptr(pcm.device)))
     return out
 

@@ -81,16 +81,19 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t mbar, uint32_t bytes) {
   asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(mbar), "r"(bytes)
                : "memory");
 }
+__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t mbar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+               : "=r"(ok)
+               : "r"(mbar), "r"(parity)
+               : "memory");
+  return ok;
+}
+// Bounded wait: a protocol bug (e.g. a TMA byte count that never arrives) traps instead of
+// hanging the GPU.  try_wait suspends in hardware, so the poll count stays small in normal runs.
 __device__ __forceinline__ void mbar_wait(uint32_t mbar, uint32_t parity) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "WAIT_LOOP:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra WAIT_DONE;\n\t"
-      "bra WAIT_LOOP;\n\t"
-      "WAIT_DONE:\n\t}" ::"r"(mbar),
-      "r"(parity)
-      : "memory");
+  for (uint32_t i = 0; !mbar_try_wait(mbar, parity); ++i)
+    if (i > (1u << 24)) __trap();
 }
 
 // generic-proxy writes (st.shared) -> visible to the async proxy (UMMA / TMA reads)

@@ -1,0 +1,402 @@
+#!/usr/bin/env python
+"""bench.py - headline benchmark of the honk_b200 hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--model res15] [--clips-per-gpu B]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+    python bench.py --impl reference ...       # the reference's CPU path on the host cores
+
+One "step" = one pass of the hot path (PCM -> MFCC front end -> CNN -> logits) over one batch
+of synthetic 1-s 16 kHz clips.  Workload: BASELINE.json configs[3], res15 with 65536 clips
+sharded over 8 GPUs = 8192 clips per GPU, kept fixed per GPU as N grows (weak scaling).
+Rank 0 prints ONE JSON line.  See DESIGN.md "Measurement" for the accounting.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "clips_per_s_mfcc_cnn"
+UNIT = "clips/s"
+N_UNIQUE = 1024          # distinct synthetic clips generated per rank, tiled to the batch
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="honk_b200", choices=["honk_b200", "reference"])
+    ap.add_argument("--model", default="res15")
+    ap.add_argument("--clips-per-gpu", type=int, default=8192)
+    ap.add_argument("--precision", type=int, default=0, help="0 = tcgen05 f16 operands, 1 = all-FP32 CUDA cores")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
+    return ap.parse_args()
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return dict(hbm_gbs=float(d["hbm_gbs"]), tf_burst=float(d["bf16_tflops"]),
+                    tf_sustained=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), source="measured")
+    return dict(hbm_gbs=6650.0, tf_burst=1590.0, tf_sustained=1400.0, source="fallback")
+
+
+# ----------------------------------------------------------------------------------------------
+# clocks sampler (NVML), runs during the timed region
+# ----------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+               0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop_evt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.ok = True
+        except Exception:
+            self.ok = False
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(int(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                try:
+                    r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                except Exception:
+                    r = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                for bit, name in self.REASONS.items():
+                    if r & bit and name != "gpu_idle":
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop_evt.wait(0.05)
+
+    def finish(self):
+        self._stop_evt.set()
+        if self.is_alive():
+            self.join(2.0)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["nvml_unavailable"]}
+        return {"sm_mhz": statistics.median(self.samples), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ----------------------------------------------------------------------------------------------
+# synthetic data / weights
+# ----------------------------------------------------------------------------------------------
+def make_pcm(n, start):
+    import numpy as np
+    from honk_b200 import synth
+    uniq = synth.make_clips(min(n, N_UNIQUE), start=start)
+    reps = (n + len(uniq) - 1) // len(uniq)
+    return np.ascontiguousarray(np.tile(uniq, (reps, 1))[:n])
+
+
+def make_weights(name, cfg, calib_mfcc):
+    from honk_b200 import synth
+    return synth.make_state_dict(name, cfg, seed=0, calib_mfcc=calib_mfcc)
+
+
+# ----------------------------------------------------------------------------------------------
+# CPU path of the reference (oracle port): per-clip MFCC like collate_fn + torch CPU forward
+# ----------------------------------------------------------------------------------------------
+class CpuPath:
+    """The reference's CPU implementation of the path, restated in oracle/ (kind "port": the
+    reference's librosa 0.6 dependency is not installable and /root/reference does not exist on
+    the GPU box).  MFCC one clip at a time like SpeechDataset.collate_fn (model.py:253-265) -
+    spread over a thread pool - then the model forward in float32, batch 64, all torch threads."""
+
+    def __init__(self, name, cfg, sd):
+        import torch
+        from concurrent.futures import ThreadPoolExecutor
+        from oracle import honk_oracle as orc
+        self.orc, self.torch = orc, torch
+        self.name, self.cfg, self.sd = name, cfg, sd
+        self.cores = os.cpu_count() or 1
+        try:
+            self.cores = len(os.sched_getaffinity(0))
+        except Exception:
+            pass
+        torch.set_num_threads(self.cores)
+        self.pre = orc.AudioPreprocessorOracle()
+        self.pool = ThreadPoolExecutor(max_workers=self.cores)
+
+    def _mfcc(self, clip):
+        return self.pre.compute_mfccs(self.orc.pcm16_to_float(clip)).reshape(-1, 40)
+
+    def run(self, pcm):
+        import numpy as np
+        torch = self.torch
+        mf = np.stack(list(self.pool.map(self._mfcc, pcm)))
+        outs = []
+        with torch.no_grad():
+            for i in range(0, len(mf), 64):
+                outs.append(self.orc.model_forward(self.name, self.sd, self.cfg, mf[i:i + 64], torch.float32))
+        return torch.cat(outs, 0).numpy()
+
+    def timed(self, pcm):
+        t0 = time.perf_counter()
+        out = self.run(pcm)
+        return time.perf_counter() - t0, out
+
+
+def cpu_sample_size(cpu, pcm, target_s, lo=64, hi=4096):
+    """Picks a sample size whose CPU time is about target_s, from a 64-clip calibration run."""
+    t, _ = cpu.timed(pcm[:lo])
+    n = int(max(lo, min(hi, target_s / max(t, 1e-6) * lo)))
+    return (n // 64) * 64, t
+
+
+# ----------------------------------------------------------------------------------------------
+def run_reference(args):
+    """--impl reference: the reference's own CPU path (oracle port) on the host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import honk_b200.model as hm        # config table only (no CUDA call)
+    name = args.model
+    cfg = dict(hm.find_config(name))
+    cfg["n_labels"] = 12
+    pcm = make_pcm(N_UNIQUE, 0)
+    from oracle import honk_oracle as orc
+    mf = orc.AudioPreprocessorOracle().compute_mfccs_batch([orc.pcm16_to_float(c) for c in pcm[:32]])
+    sd = make_weights(name, cfg, mf)
+    cpu = CpuPath(name, cfg, sd)
+    total = max(1, args.steps + args.warmup)
+    per_step_s = min(20.0, 150.0 / total)
+    n, _ = cpu_sample_size(cpu, pcm, per_step_s, hi=N_UNIQUE)
+    sample = pcm[:n]
+    for _ in range(args.warmup):
+        cpu.run(sample)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu.run(sample)
+    dt = (time.perf_counter() - t0) / max(1, args.steps)
+    value = n / dt
+    sample_desc = "%d clips per step (bounded sample of the %d-clip/GPU workload), MFCC per clip + %s fp32 forward batch 64" % (
+        n, args.clips_per_gpu, name)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64 front end / f32 CNN", "data": "synthetic",
+        "config": workload_config(args, args.gpus),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cpu.cores, "kind": "port", "sample": sample_desc},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def workload_config(args, world):
+    return {
+        "workload": "%s MFCC+CNN inference, %d synthetic 1-s 16 kHz int16 clips per GPU "
+                    "(BASELINE configs[3]: res15 batch 65536 over 8 GPUs = 8192/GPU)" % (args.model, args.clips_per_gpu),
+        "clips_per_gpu": args.clips_per_gpu, "global_clips": args.clips_per_gpu * world,
+        "n_samples": 16000, "n_labels": 12, "parallelism": "clip shards, %d independent rank(s), one all_gather of logits" % world,
+        "l2": "inputs %.0f MB per GPU per step > 126 MB L2 (no flush needed)" % (args.clips_per_gpu * 32000 / 1e6),
+        "unique_clips_per_rank": min(N_UNIQUE, args.clips_per_gpu),
+    }
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import honk_b200 as hb
+    from honk_b200 import _native as N
+    from honk_b200 import parallel
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; honk_b200 has no CPU fallback (use --impl reference for the CPU path)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    N.lib()                                            # fails loudly if the extension is missing
+
+    name = args.model
+    cfg = dict(hb.find_config(name))
+    cfg["n_labels"] = 12
+    B = args.clips_per_gpu
+    pcm_host = torch.from_numpy(make_pcm(B, rank * B)).pin_memory()
+    pcm = pcm_host.to(dev)
+    pre = hb.AudioPreprocessor()
+    calib = pre.compute_mfccs_batch(pcm[:32]).cpu().numpy()
+    sd = make_weights(name, cfg, calib)
+    model = hb.find_model(name)(cfg)
+    model.load_state_dict({k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()})
+    model.precision = args.precision
+    model.cuda().eval()
+
+    def step_device():
+        logits = model.forward_pcm(pcm, pre)
+        return parallel.gather_logits(logits, B * world) if world > 1 else logits
+
+    def step_e2e():
+        x = pcm_host.to(dev, non_blocking=True)
+        logits = model.forward_pcm(x, pre)
+        if world > 1:
+            logits = parallel.gather_logits(logits, B * world)
+        return logits.to("cpu", non_blocking=False)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.no_grad():
+        for _ in range(max(args.warmup, 0)):
+            out = step_device()
+        barrier()
+        # ---------------- timed region (device-resident inputs) ----------------
+        N.profile_reset()
+        N.profile_enable(True)
+        sampler = ClockSampler(local)
+        sampler.start()
+        launches0 = N.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            out = step_device()
+        e1.record()
+        barrier()
+        launches = N.launch_count() - launches0
+        clocks = sampler.finish()
+        N.profile_enable(False)
+        ms = e0.elapsed_time(e1) / max(1, args.steps)
+        spans = {}
+        for sp in ("frontend", "res_conv0", "res_conv", "res_tail", "f32_model"):
+            t, n = N.profile_get(sp)
+            if n:
+                spans[sp] = (t, n)
+        N.profile_reset()
+        # ---------------- end-to-end (pinned host PCM -> logits on host) ----------------
+        for _ in range(2):
+            step_e2e()
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        f0.record()
+        for _ in range(args.steps):
+            host_logits = step_e2e()
+        f1.record()
+        barrier()
+        e2e_wall = (time.perf_counter() - t0) / max(1, args.steps) * 1e3
+        e2e_ms = max(f0.elapsed_time(f1) / max(1, args.steps), e2e_wall)
+
+    if world > 1:
+        t = torch.tensor([ms, e2e_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_ms = float(t[0]), float(t[1])
+        lt = torch.tensor([launches], device=dev, dtype=torch.int64)
+        dist.all_reduce(lt)
+        launches = int(lt[0])
+
+    if rank == 0:
+        from oracle import honk_oracle as orc          # checker / CPU baseline only
+        peaks = measured_peaks()
+        total_clips = B * world
+        value = total_clips / (ms * 1e-3)
+        # ---- roofline of the dominant kernel (rank 0's spans) ----
+        n_layers = cfg.get("n_layers", 0)
+        roof = None
+        if "res_conv" in spans and name.startswith("res"):
+            C = cfg["n_feature_maps"]
+            H, W = 101, 40
+            if "res_pool" in cfg:
+                H, W = H // cfg["res_pool"][0], W // cfg["res_pool"][1]
+            flops_layer_clip = 2 * 9 * C * C * H * W                     # unpadded 2*MAC of one C->C 3x3 layer
+            t_ms, n_spans = spans["res_conv"]
+            clips_done = B * args.steps
+            n_launch = n_spans * n_layers
+            avg_launch_ms = t_ms / n_launch
+            achieved = flops_layer_clip * n_layers * clips_done / (t_ms * 1e-3) / 1e12
+            roof = {"bound": "tensor", "kernel": "tc_conv_kernel (dilated 3x3 C->C implicit GEMM, tcgen05)",
+                    "achieved": achieved, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
+                    "frac": achieved / peaks["tf_sustained"], "peak_source": peaks["source"] + " bf16 sustained",
+                    "traffic": None, "avg_launch_ms": avg_launch_ms,
+                    "flops_per_launch": flops_layer_clip * clips_done / n_spans,
+                    "share_of_step": t_ms / (ms * args.steps)}
+        elif "f32_model" in spans:
+            t_ms, n_spans = spans["f32_model"]
+            fl = orc.conv_flops_per_clip(name, cfg)
+            achieved = fl * B * args.steps / (t_ms * 1e-3) / 1e12
+            roof = {"bound": "tensor", "kernel": "conv_gemm_f32_kernel (CUDA-core FP32 path)", "achieved": achieved,
+                    "peak": peaks["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / peaks["tf_sustained"],
+                    "peak_source": peaks["source"] + " bf16 sustained", "traffic": None,
+                    "share_of_step": t_ms / (ms * args.steps)}
+        fe = None
+        if "frontend" in spans:
+            t_ms, n_spans = spans["frontend"]
+            bytes_clip = 32000 + 101 * 40 * 4
+            gbs = bytes_clip * B * args.steps / (t_ms * 1e-3) / 1e9
+            fe = {"kernel": "fe_mfcc_kernel", "bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                  "frac": gbs / peaks["hbm_gbs"], "clips_per_s": B * args.steps / (t_ms * 1e-3),
+                  "share_of_step": t_ms / (ms * args.steps)}
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64 front end; f16 operands / f32 accumulate CNN" if args.precision == 0 else "f64 front end; f32 CNN",
+            "data": "synthetic", "config": workload_config(args, world),
+            "path": model.native_path, "gpu_launches": launches, "clocks": clocks,
+            "e2e": {"value": total_clips / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
+                    "h2d_bytes_per_step": int(pcm_host.numel() * 2), "d2h_bytes_per_step": int(host_logits.numel() * 4)},
+            "roofline": roof, "frontend_roofline": fe,
+            "spans_ms_per_step": {k: v[0] / args.steps for k, v in spans.items()},
+            "algorithmic_flops_per_clip": orc.conv_flops_per_clip(name, cfg),
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            pcm_np = pcm_host.numpy()[:N_UNIQUE]
+            cpu = CpuPath(name, cfg, sd)
+            n, _ = cpu_sample_size(cpu, pcm_np, args.cpu_seconds, hi=N_UNIQUE)
+            dt, ref = cpu.timed(pcm_np[:n])
+            got = host_logits[:n].numpy()
+            agree = float((got.argmax(1) == ref.argmax(1)).mean())
+            line["cpu_baseline"] = {"value": n / dt, "unit": UNIT, "cores": cpu.cores, "kind": "port",
+                                    "sample": "%d clips of the same batch: per-clip float64 MFCC (thread pool) + %s fp32 forward, batch 64, torch %d threads"
+                                              % (n, name, cpu.cores),
+                                    "top1_agreement_vs_gpu": agree,
+                                    "max_logit_err_rel": float(np.abs(got - ref).max() / np.abs(ref).max())}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -3,6 +3,7 @@
 #include "model.cuh"
 
 #include <cmath>
+#include <cstdlib>
 
 using namespace honk;
 
@@ -273,8 +274,10 @@ extern "C" int honk_model_create(const honk_model_config* cfg, const honk_tensor
       m->bn_scale.push_back(d);
     }
     if (cfg->precision == 0) {
-      HONK_TRY(res_tc_plan_create(m.get()));
-      if (m->tc) m->path = "tcgen05-f16";
+      const char* no2 = getenv("HONK_DISABLE_TC2");
+      if (!(no2 && atoi(no2)) && cfg->n_feature_maps <= 48) HONK_TRY(res_tc2_plan_create(m.get(), &m->tc2));
+      if (!m->tc2) HONK_TRY(res_tc_plan_create(m.get()));
+      if (m->tc || m->tc2) m->path = "tcgen05-f16";
     }
   }
   *out = m.release();
@@ -284,6 +287,7 @@ extern "C" int honk_model_create(const honk_model_config* cfg, const honk_tensor
 extern "C" int honk_model_destroy(honk_model* m) {
   if (!m) return HONK_OK;
   if (m->tc) res_tc_plan_free(m->tc);
+  if (m->tc2) res_tc2_plan_free(m->tc2);
   for (void* p : m->owned) cudaFree(p);
   delete m;
   return HONK_OK;
@@ -293,6 +297,7 @@ extern "C" const char* honk_model_path(const honk_model* m) { return m ? m->path
 
 extern "C" int64_t honk_model_workspace_bytes(const honk_model* m, int64_t n_clips) {
   if (!m || n_clips <= 0) return 0;
+  if (m->tc2) return res_tc2_workspace_bytes(m->tc2, n_clips);
   return m->tc ? res_tc_workspace_bytes(m, n_clips) : f32_workspace(m, n_clips);
 }
 
@@ -306,6 +311,7 @@ extern "C" int honk_model_forward(const honk_model* m, const float* d_mfcc, int6
              "workspace too small: %lld < %lld bytes", static_cast<long long>(workspace_bytes),
              static_cast<long long>(honk_model_workspace_bytes(m, n_clips)));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (m->tc2) return res_tc2_forward(m->tc2, d_mfcc, n_clips, d_logits, d_workspace, workspace_bytes, s);
   if (m->tc) return res_tc_forward(m, d_mfcc, n_clips, d_logits, d_workspace, workspace_bytes, s);
   ProfSpan span("f32_model", s);
   const int64_t in_per = static_cast<int64_t>(m->H0) * m->W0;

@@ -22,6 +22,8 @@ struct HostTensor {
 
 struct ResTcPlan;   // res_tc.cu
 void res_tc_plan_free(ResTcPlan*);
+struct ResTc2Plan;  // res_tc2.cu
+void res_tc2_plan_free(ResTc2Plan*);
 
 }  // namespace honk
 
@@ -33,7 +35,8 @@ struct honk_model {
   std::map<std::string, float*> dev;                 // same tensors on the device (FP32 path)
   std::vector<float*> bn_scale;                      // [n_layers] 1/sqrt(var + 1e-5), device
   std::vector<void*> owned;                          // every cudaMalloc of this handle
-  honk::ResTcPlan* tc = nullptr;                     // non-null => tcgen05 path is used
+  honk::ResTcPlan* tc = nullptr;                     // non-null => per-layer tcgen05 path (pooled res8/res26)
+  honk::ResTc2Plan* tc2 = nullptr;                   // non-null => persistent multi-layer tcgen05 path (res15)
   std::string path = "cuda-core-f32";
   // geometry derived from cfg
   int H0 = 101, W0 = 40;                             // input
@@ -47,6 +50,11 @@ namespace honk {
 int fe_n_dct(const honk_frontend* fe);   // frontend.cu
 int res_tc_plan_create(honk_model* m);
 int64_t res_tc_workspace_bytes(const honk_model* m, int64_t n_clips);
+// res_tc2.cu: persistent multi-layer kernel for the un-pooled res* models; *out == nullptr when it does not apply.
+int res_tc2_plan_create(honk_model* m, ResTc2Plan** out);
+int64_t res_tc2_workspace_bytes(const ResTc2Plan* p, int64_t n_clips);
+int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, float* d_logits, void* ws, int64_t ws_bytes,
+                    cudaStream_t s);
 int res_tc_forward(const honk_model* m, const float* d_mfcc, int64_t n_clips, float* d_logits, void* ws,
                    int64_t ws_bytes, cudaStream_t s);
 

@@ -30,6 +30,8 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <vector>
 
 #include "model.cuh"
@@ -43,6 +45,7 @@ constexpr int T2_NSTAGE = 8;      // A-operand stages (one input column each)
 constexpr int T2_THREADS = 320;
 constexpr int T2_PAD = 16;        // zero rows above every channel plane (>= max dilation)
 constexpr int T2_MAXSEG = 8;
+constexpr int T2_MAXL = 24;       // layers (res26)
 constexpr int T2_EPI_THREADS = 256;
 
 struct T2Seg {                    // a run of output columns of one chain, owned by one CTA
@@ -62,7 +65,6 @@ struct T2Layer {
 };
 
 struct T2Params {
-  const T2Layer* layers;
   const unsigned char* wpack;
   const float* cst;
   const float* mfcc;              // [n_clips][H][W] float32
@@ -77,6 +79,11 @@ struct T2Params {
   int plane_rows;                 // H + T2_PAD
   int col_bytes;                  // NCG * plane_rows * 16
   int stage_stride, wbytes;
+  int mode;                       // debug: 1 = MMA issue only (no loads, no waits, no epilogue; results are garbage)
+  long long* dbg;                 // optional [gridDim][8] cycle counters (HONK_TC2_DEBUG)
+  // Per-layer tables live in the kernel parameter (constant) bank so that the MMA warp's descriptor
+  // arithmetic stays on the uniform datapath (no R2UR per tcgen05.mma operand).
+  T2Layer layers[T2_MAXL];
 };
 
 namespace {
@@ -115,15 +122,15 @@ __device__ __forceinline__ void stcg16(void* p, const uint4& v) {
   asm volatile("st.global.cg.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
-  a = fminf(fmaxf(a, -65504.f), 65504.f);
-  b = fminf(fmaxf(b, -65504.f), 65504.f);
-  __half2 h = __floats2half2_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&h);
+  uint32_t r;    // one instruction; out-of-range values saturate to +-65504 instead of becoming inf
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+  return r;
 }
+#define T2_TIMED(acc, stmt) do { if (p.mode == 1) break; if (p.dbg) { const long long t__ = clock64(); stmt; acc += clock64() - t__; } else { stmt; } } while (0)
 __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 template <int NCG>
-__global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const T2Params p) {
+__global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_constant__ T2Params p) {
   constexpr int NB = NCG * 8;            // padded channels = N block
   constexpr int NKC = NCG / 2;           // K chunks of 16 channels
   constexpr int NSLOT = 512 / NB;        // TMEM ring of output-column accumulators
@@ -137,7 +144,11 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const T2Params p
   __shared__ __align__(8) uint64_t bar_wfull[2], bar_wfree[2];
   __shared__ uint32_t tmem_base_s;
 
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);      // provably warp-uniform: keeps role code on the uniform datapath
+  const uint32_t a_full = smem_u32(&bar_full[0]), a_empty = smem_u32(&bar_empty[0]);
+  const uint32_t a_acc_full = smem_u32(&bar_acc_full[0]), a_acc_empty = smem_u32(&bar_acc_empty[0]);
+  const uint32_t a_wfull = smem_u32(&bar_wfull[0]), a_wfree = smem_u32(&bar_wfree[0]);
   const int team = blockIdx.x / T2_G, rank = blockIdx.x % T2_G, n_teams = gridDim.x / T2_G;
   unsigned char* stages = smem;
   unsigned char* wbuf = smem + T2_NSTAGE * p.stage_stride;
@@ -148,16 +159,16 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const T2Params p
   if (warp == 1) tmem_alloc(smem_u32(&tmem_base_s), 512);
   if (tid == 0) {
     for (int s = 0; s < T2_NSTAGE; ++s) {
-      mbar_init(smem_u32(&bar_full[s]), 1);
-      mbar_init(smem_u32(&bar_empty[s]), 1);
+      mbar_init((a_full + 8 * (s)), 1);
+      mbar_init((a_empty + 8 * (s)), 1);
     }
     for (int k = 0; k < NSLOT; ++k) {
-      mbar_init(smem_u32(&bar_acc_full[k]), 1);
-      mbar_init(smem_u32(&bar_acc_empty[k]), 8);
+      mbar_init((a_acc_full + 8 * (k)), 1);
+      mbar_init((a_acc_empty + 8 * (k)), 4);
     }
     for (int k = 0; k < 2; ++k) {
-      mbar_init(smem_u32(&bar_wfull[k]), 1);
-      mbar_init(smem_u32(&bar_wfree[k]), 1);
+      mbar_init((a_wfull + 8 * (k)), 1);
+      mbar_init((a_wfree + 8 * (k)), 1);
     }
     fence_mbar_init();
   }
@@ -171,34 +182,36 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const T2Params p
 
   if (warp == 0) {
     // ======================================= producer =======================================
-    if (lane == 0) {
+    if (lane == 0 && p.mode != 1) {
       uint32_t it = 0, q = 0;
       int piter = 0;
+      long long t_flag = 0, t_empty = 0;
+      const long long t_start = clock64();
       for (int pair = team; pair < n_pairs; pair += n_teams, ++piter) {
         const int nab = min(2, p.n_clips - 2 * pair);
         for (int L = 1; L <= p.n_layers; ++L, ++q) {
-          const T2Layer* ly = p.layers + (L - 1);
+          const T2Layer& ly = p.layers[L - 1];
           if (q == 0) {
-            mbar_expect_tx(smem_u32(&bar_wfull[0]), p.wbytes);
-            bulk_load(smem_u32(wbuf), p.wpack + __ldg(&ly->w_off), p.wbytes, smem_u32(&bar_wfull[0]));
+            mbar_expect_tx((a_wfull + 8 * (0)), p.wbytes);
+            bulk_load(smem_u32(wbuf), p.wpack + ly.w_off, p.wbytes, (a_wfull + 8 * (0)));
           }
-          const int d = __ldg(&ly->d);
+          const int d = ly.d;
           const uint32_t bytes = (NCG - 1) * plane_bytes + (p.H + 2 * d) * 16;
-          const int nseg = __ldg(&ly->n_seg[rank]);
+          const int nseg = ly.n_seg[rank];
           for (int ab = 0; ab < nab; ++ab) {
             const int clip = 2 * pair + ab, slot = 2 * team + ab;
             const unsigned char* in = (L & 1) ? p.Q + (static_cast<long long>(piter & 1) * p.n_slots + slot) * p.slot_stride
                                               : p.P + static_cast<long long>(slot) * p.slot_stride;
             in += (T2_PAD - d) * 16;
-            wait_flag(p.flags + clip, T2_G * L);          // every CTA of the team finished layer L-1 (conv0 = layer 0)
+            T2_TIMED(t_flag, wait_flag(p.flags + clip, T2_G * L));          // every CTA of the team finished layer L-1 (conv0 = layer 0)
             fence_proxy_async_global();
             for (int s = 0; s < nseg; ++s) {
-              const T2Seg* sg = &ly->seg[rank][s];
-              const int r = __ldg(&sg->r), jin0 = __ldg(&sg->jin0), n_in = __ldg(&sg->n_in);
+              const T2Seg& sg = ly.seg[rank][s];
+              const int r = sg.r, jin0 = sg.jin0, n_in = sg.n_in;
               for (int t = 0; t < n_in; ++t, ++it) {
                 const int st = it % T2_NSTAGE;
-                mbar_wait(smem_u32(&bar_empty[st]), ((it / T2_NSTAGE) & 1) ^ 1);
-                const uint32_t full = smem_u32(&bar_full[st]);
+                T2_TIMED(t_empty, mbar_wait((a_empty + 8 * (st)), ((it / T2_NSTAGE) & 1) ^ 1));
+                const uint32_t full = (a_full + 8 * (st));
                 mbar_expect_tx(full, bytes);
                 bulk_load(smem_u32(stages + st * p.stage_stride), in + static_cast<long long>(r + (jin0 + t) * d) * p.col_bytes,
                           bytes, full);
@@ -209,13 +222,14 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const T2Params p
           const bool more = (L < p.n_layers) || (pair + n_teams < n_pairs);
           if (more) {
             const uint32_t qn = q + 1;
-            const T2Layer* nl = p.layers + (L < p.n_layers ? L : 0);
-            if (qn >= 2) mbar_wait(smem_u32(&bar_wfree[qn & 1]), ((qn - 2) >> 1) & 1);
-            mbar_expect_tx(smem_u32(&bar_wfull[qn & 1]), p.wbytes);
-            bulk_load(smem_u32(wbuf + (qn & 1) * p.wbytes), p.wpack + __ldg(&nl->w_off), p.wbytes, smem_u32(&bar_wfull[qn & 1]));
+            const T2Layer& nl = p.layers[L < p.n_layers ? L : 0];
+            if (qn >= 2) mbar_wait((a_wfree + 8 * (qn & 1)), ((qn - 2) >> 1) & 1);
+            mbar_expect_tx((a_wfull + 8 * (qn & 1)), p.wbytes);
+            bulk_load(smem_u32(wbuf + (qn & 1) * p.wbytes), p.wpack + nl.w_off, p.wbytes, (a_wfull + 8 * (qn & 1)));
           }
         }
       }
+      if (p.dbg) { long long* o = p.dbg + blockIdx.x * 8; o[0] = clock64() - t_start; o[1] = t_flag; o[2] = t_empty; }
     }
   } else if (warp == 1) {
     // ======================================= MMA issuer =====================================
@@ -223,66 +237,113 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const T2Params p
     const uint32_t a_lbo = (static_cast<uint32_t>(p.plane_rows) & 0x3FFF) << 16;
     const uint64_t b_hi = make_desc(0, 3 * NB * 16, 128) & 0xFFFFFFFF00000000ull;
     const uint32_t b_lbo = (static_cast<uint32_t>(3 * NB) & 0x3FFF) << 16;
-    uint32_t it = 0, q = 0, g = 0;
+    const uint32_t stages16 = smem_u32(stages) >> 4, stage16 = static_cast<uint32_t>(p.stage_stride) >> 4;
+    const uint32_t pr2 = 2 * p.plane_rows;
+    constexpr uint32_t IDESC0 = make_idesc(128, 0, 0), IDESC_BLK = static_cast<uint32_t>(NB >> 3) << 17;
+    uint32_t st = 0, stpar = 0, q = 0;
+    int gseg = 2 * NSLOT;                       // ring index of the segment's first output (offset keeps halo indices >= 0)
+    long long t_acc = 0, t_full = 0, t_w = 0;
+    const long long t_start = clock64();
     for (int pair = team; pair < n_pairs; pair += n_teams) {
       const int nab = min(2, p.n_clips - 2 * pair);
       for (int L = 1; L <= p.n_layers; ++L, ++q) {
-        const T2Layer* ly = p.layers + (L - 1);
-        const int d = __ldg(&ly->d);
-        const int nseg = __ldg(&ly->n_seg[rank]);
-        mbar_wait(smem_u32(&bar_wfull[q & 1]), (q >> 1) & 1);
+        const T2Layer& ly = p.layers[L - 1];
+        const uint32_t d = ly.d;
+        const int nseg = ly.n_seg[rank];
+        T2_TIMED(t_w, mbar_wait((a_wfull + 8 * (q & 1)), (q >> 1) & 1));
         const uint32_t b_lo0 = b_lbo | (smem_u32(wbuf + (q & 1) * p.wbytes) >> 4);
         for (int ab = 0; ab < nab; ++ab) {
           for (int s = 0; s < nseg; ++s) {
-            const T2Seg* sg = &ly->seg[rank][s];
-            const int j0 = __ldg(&sg->j0), n_out = __ldg(&sg->n_out), jin0 = __ldg(&sg->jin0), n_in = __ldg(&sg->n_in);
+            const T2Seg& sg = ly.seg[rank][s];
+            const int j0 = sg.j0, n_out = sg.n_out, jin0 = sg.jin0, n_in = sg.n_in;
             const int jend = j0 + n_out - 1;
-            for (int t = 0; t < n_in; ++t, ++it) {
+            int gc = gseg + (jin0 - j0);          // ring index of the output column aligned with the input column
+            for (int t = 0; t < n_in; ++t, ++gc) {
               const int jc = jin0 + t;
-              const int st = it % T2_NSTAGE;
-              const int o_lo = max(jc - 1, j0), o_hi = min(jc + 1, jend);
-              const int ft_lo = (t == 0) ? o_lo : jc + 1;                  // first-touched outputs: ft_lo..o_hi
-              for (int o = ft_lo; o <= o_hi; ++o) {
-                const uint32_t gi = g + (o - j0);
-                mbar_wait(smem_u32(&bar_acc_empty[gi % NSLOT]), ((gi / NSLOT) & 1) ^ 1);
+              const bool lo_in = jc > j0, c_in = (jc >= j0) && (jc <= jend), hi_in = jc < jend;
+              const int first_blk = lo_in ? 0 : (c_in ? 1 : 2), last_blk = hi_in ? 2 : (c_in ? 1 : 0);
+              const int n = last_blk - first_blk + 1;
+              const uint32_t gf = static_cast<uint32_t>(gc - 1 + first_blk);
+              const uint32_t sf = gf % NSLOT;
+              const bool wrap = sf + n > NSLOT;
+              const int n1 = wrap ? static_cast<int>(NSLOT - sf) : n;
+              // first-touched outputs need their ring slot drained by the epilogue: block 2, and at t == 0 block 1 too
+              if (p.mode != 1) {
+                const long long tw0 = p.dbg ? clock64() : 0;
+                if (t == 0 && c_in) {
+                  const uint32_t g1 = static_cast<uint32_t>(gc);
+                  mbar_wait((a_acc_empty + 8 * (g1 % NSLOT)), ((g1 / NSLOT) & 1) ^ 1);
+                }
+                if (hi_in) {
+                  const uint32_t g2 = static_cast<uint32_t>(gc + 1);
+                  mbar_wait((a_acc_empty + 8 * (g2 % NSLOT)), ((g2 / NSLOT) & 1) ^ 1);
+                }
+                const long long tw1 = p.dbg ? clock64() : 0;
+                mbar_wait((a_full + 8 * (st)), stpar);
+                if (p.dbg) { t_acc += tw1 - tw0; t_full += clock64() - tw1; }
               }
-              mbar_wait(smem_u32(&bar_full[st]), (it / T2_NSTAGE) & 1);
               fence_after();
               if (elect_one()) {
-                const uint32_t a_lo0 = a_lbo | (smem_u32(stages + st * p.stage_stride) >> 4);
-                // issues D[outs lo..hi] (+)= A(kh,kc) * B(kh,kc)[blocks], split where the ring wraps
-                auto issue = [&](int lo, int hi, int i, uint32_t acc) {
-                  const int n = hi - lo + 1;
-                  if (n <= 0) return;
-                  const int kh = i / NKC, kc = i - kh * NKC;
-                  const uint64_t ad = a_hi | static_cast<uint64_t>(a_lo0 + static_cast<uint32_t>(2 * kc * p.plane_rows + kh * d));
-                  const uint32_t gi = g + (lo - j0);
-                  const int s_lo = gi % NSLOT;
-                  const int first = min(n, NSLOT - s_lo);
-                  const int blk = lo - (jc - 1);
-                  const uint64_t bd = b_hi | static_cast<uint64_t>(b_lo0 + static_cast<uint32_t>(i * BT16 + blk * NB));
-                  mma_f16_ss(tmem + s_lo * NB, ad, bd, make_idesc(128, first * NB, 0), acc);
-                  if (n > first)
-                    mma_f16_ss(tmem, ad, bd + static_cast<uint64_t>(first * NB), make_idesc(128, (n - first) * NB, 0), acc);
-                };
-                issue(o_lo, min(ft_lo - 1, o_hi), 0, 1);
-                issue(max(ft_lo, o_lo), o_hi, 0, 0);
+                const uint32_t a_lo = a_lbo | (stages16 + st * stage16);
+                const uint32_t b_f = b_lo0 + first_blk * NB;
+                const uint32_t d1 = tmem + sf * NB;
+                const uint32_t id1 = IDESC0 + n1 * IDESC_BLK, id2 = IDESC0 + (n - n1) * IDESC_BLK;
+                {   // i = 0 (kh = 0, kc = 0): first-touched blocks overwrite, the others accumulate
+                  const uint64_t ad = a_hi | a_lo, bd = b_hi | b_f;
+                  if (t == 0 || !hi_in) {
+                    const uint32_t acc0 = (t != 0);
+                    mma_f16_ss(d1, ad, bd, id1, acc0);
+                    if (wrap) mma_f16_ss(tmem, ad, bd + static_cast<uint64_t>(n1 * NB), id2, acc0);
+                  } else {
+                    const int na = 2 - first_blk;                        // accumulating blocks (1 or 2), then block 2 overwrites
+                    if (!wrap || n1 == na) {
+                      mma_f16_ss(d1, ad, bd, IDESC0 + na * IDESC_BLK, 1);
+                      mma_f16_ss(wrap ? tmem : d1 + na * NB, ad, bd + static_cast<uint64_t>(na * NB), IDESC0 + IDESC_BLK, 0);
+                    } else {                                             // ring wraps inside the accumulating part (na == 2, n1 == 1)
+                      mma_f16_ss(d1, ad, bd, IDESC0 + IDESC_BLK, 1);
+                      mma_f16_ss(tmem, ad, bd + static_cast<uint64_t>(NB), IDESC0 + IDESC_BLK, 1);
+                      mma_f16_ss(tmem + NB, ad, bd + static_cast<uint64_t>(2 * NB), IDESC0 + IDESC_BLK, 0);
+                    }
+                  }
+                }
+                if (!wrap) {
 #pragma unroll
-                for (int i = 1; i < NMMA; ++i) issue(o_lo, o_hi, i, 1);
-                commit(smem_u32(&bar_empty[st]));
-                if (jc - 1 >= j0 && jc - 1 <= jend) commit(smem_u32(&bar_acc_full[(g + (jc - 1 - j0)) % NSLOT]));
-                if (t == n_in - 1 && jc <= jend) commit(smem_u32(&bar_acc_full[(g + (jc - j0)) % NSLOT]));
+                  for (int i = 1; i < NMMA; ++i) {
+                    const int kh = i / NKC, kc = i - kh * NKC;
+                    mma_f16_ss(d1, a_hi | static_cast<uint64_t>(a_lo + kc * pr2 + kh * d),
+                               b_hi | static_cast<uint64_t>(b_f + i * BT16), id1, 1);
+                  }
+                } else {
+#pragma unroll
+                  for (int i = 1; i < NMMA; ++i) {
+                    const int kh = i / NKC, kc = i - kh * NKC;
+                    const uint64_t ad = a_hi | static_cast<uint64_t>(a_lo + kc * pr2 + kh * d);
+                    const uint64_t bd = b_hi | static_cast<uint64_t>(b_f + i * BT16);
+                    mma_f16_ss(d1, ad, bd, id1, 1);
+                    mma_f16_ss(tmem, ad, bd + static_cast<uint64_t>(n1 * NB), id2, 1);
+                  }
+                }
+                commit((a_empty + 8 * (st)));
+                if (lo_in) commit((a_acc_full + 8 * (static_cast<uint32_t>(gc - 1) % NSLOT)));
+                if (t == n_in - 1 && c_in) commit((a_acc_full + 8 * (static_cast<uint32_t>(gc) % NSLOT)));
               }
               __syncwarp();
+              if (++st == T2_NSTAGE) { st = 0; stpar ^= 1; }
             }
-            g += n_out;
+            gseg += n_out;
           }
         }
-        if (elect_one()) commit(smem_u32(&bar_wfree[q & 1]));
+        if (elect_one()) commit((a_wfree + 8 * (q & 1)));
         __syncwarp();
       }
     }
-  } else {
+    if (p.mode == 1) {
+      if (elect_one()) commit((a_full + 8 * (0)));
+      __syncwarp();
+      mbar_wait((a_full + 8 * (0)), 0);
+    }
+    if (p.dbg && lane == 0) { long long* o = p.dbg + blockIdx.x * 8; o[3] = clock64() - t_start; o[4] = t_acc; o[5] = t_full; o[6] = t_w; }
+  } else if (p.mode != 1) {
     // ======================================= epilogue =======================================
     const int ew = warp - 2, quad = warp & 3, half = ew >> 2;
     const int h = quad * 32 + lane;
@@ -290,6 +351,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const T2Params p
     const int etid = ew * 32 + lane;
     uint32_t g = 0;
     int piter = 0;
+    long long t_wait = 0;
     for (int pair = team; pair < n_pairs; pair += n_teams, ++piter) {
       const int nab = min(2, p.n_clips - 2 * pair);
       const long long qoff = static_cast<long long>(piter & 1) * p.n_slots;
@@ -327,104 +389,105 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const T2Params p
             }
           }
         }
-        __threadfence();
-        fence_proxy_async_global();
         epi_bar();
-        if (etid == 0) red_release_gpu_add(p.flags + clip, 1);
-      }
-      // ---- layers 1..n ----
-      for (int L = 1; L <= p.n_layers; ++L) {
-        const T2Layer* ly = p.layers + (L - 1);
-        const int d = __ldg(&ly->d), flags = __ldg(&ly->flags);
-        const bool add_res = flags & 1, last = flags & 2;
-        const int nseg = __ldg(&ly->n_seg[rank]);
-        float cst[HALF];
-        {
-          const float4* c4 = reinterpret_cast<const float4*>(p.cst + __ldg(&ly->cst_off) + half * HALF);
-#pragma unroll
-          for (int k = 0; k < HALF / 4; ++k) {
-            const float4 v = __ldg(c4 + k);
-            cst[4 * k] = v.x; cst[4 * k + 1] = v.y; cst[4 * k + 2] = v.z; cst[4 * k + 3] = v.w;
-          }
+        if (etid == 0) {
+          __threadfence();
+          fence_proxy_async_global();
+          red_release_gpu_add(p.flags + clip, 1);
         }
+      }
+      // ---- layers 1..n: the two groups of 4 warps take alternate output columns (all NB channels each) ----
+      for (int L = 1; L <= p.n_layers; ++L) {
+        const T2Layer& ly = p.layers[L - 1];
+        const int d = ly.d, flags = ly.flags;
+        const bool add_res = flags & 1, last = flags & 2;
+        const int nseg = ly.n_seg[rank];
+        const float4* c4 = reinterpret_cast<const float4*>(p.cst + ly.cst_off);
         for (int ab = 0; ab < nab; ++ab) {
           const int clip = 2 * pair + ab, slot = 2 * team + ab;
-          unsigned char* Qs = p.Q + (qoff + slot) * p.slot_stride;
-          unsigned char* Ps = p.P + static_cast<long long>(slot) * p.slot_stride;
+          unsigned char* Qs = p.Q + (qoff + slot) * p.slot_stride + (T2_PAD + h) * 16;
+          unsigned char* Ps = p.P + static_cast<long long>(slot) * p.slot_stride + (T2_PAD + h) * 16;
           unsigned char* outb = (L & 1) ? Ps : Qs;            // odd: Q -> P ; even: P (+Q residual) -> Q in place
-          float psum[HALF];
+          float psum[NB];
+          if (last) {
 #pragma unroll
-          for (int k = 0; k < HALF; ++k) psum[k] = 0.f;
+            for (int k = 0; k < NB; ++k) psum[k] = 0.f;
+          }
           for (int s = 0; s < nseg; ++s) {
-            const T2Seg* sg = &ly->seg[rank][s];
-            const int r = __ldg(&sg->r), j0 = __ldg(&sg->j0), n_out = __ldg(&sg->n_out);
+            const T2Seg& sg = ly.seg[rank][s];
+            const int r = sg.r, j0 = sg.j0, n_out = sg.n_out;
             for (int o = j0; o < j0 + n_out; ++o, ++g) {
-              const int w = r + o * d;
+              if ((g & 1) != static_cast<uint32_t>(half)) continue;
               const int sl = g % NSLOT;
-              const long long off = static_cast<long long>(w) * p.col_bytes + (half * (HALF / 8)) * plane_bytes + (T2_PAD + h) * 16;
-              uint4 rv[HALF / 8];
+              const long long off = static_cast<long long>(r + o * d) * p.col_bytes;
+              // rc = residual + epilogue constant, prepared while the MMAs of this column are still running
+              float rc[NB];
+#pragma unroll
+              for (int k = 0; k < NB / 4; ++k) {
+                const float4 v = __ldg(c4 + k);
+                rc[4 * k] = v.x; rc[4 * k + 1] = v.y; rc[4 * k + 2] = v.z; rc[4 * k + 3] = v.w;
+              }
               if (add_res && valid) {
 #pragma unroll
-                for (int c = 0; c < HALF / 8; ++c) rv[c] = ldcg16(Qs + off + c * plane_bytes);
-              }
-              mbar_wait(smem_u32(&bar_acc_full[sl]), (g / NSLOT) & 1);
-              fence_after();
-              uint32_t v[HALF];
-              const uint32_t taddr = tmem + (static_cast<uint32_t>(quad * 32) << 16) + sl * NB + half * HALF;
-              if constexpr (HALF == 24) {
-                tmem_ld16(taddr, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));
-                tmem_ld8(taddr + 16, *reinterpret_cast<uint32_t(*)[8]>(&v[16]));
-              } else {
-                tmem_ld16(taddr, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));
-              }
-              tmem_ld_wait();
-              fence_before();
-              __syncwarp();
-              if (lane == 0) mbar_arrive(smem_u32(&bar_acc_empty[sl]));
-#pragma unroll
-              for (int c = 0; c < HALF / 8; ++c) {
-                float x[8];
-#pragma unroll
-                for (int k = 0; k < 8; ++k) x[k] = fmaxf(__uint_as_float(v[c * 8 + k]), 0.f) + cst[c * 8 + k];
-                if (add_res && valid) {
-                  const __half2* rh = reinterpret_cast<const __half2*>(&rv[c]);
+                for (int c = 0; c < NCG; ++c) {
+                  const uint4 rv = ldcg16(Qs + off + c * plane_bytes);
+                  const __half2* rh = reinterpret_cast<const __half2*>(&rv);
 #pragma unroll
                   for (int k = 0; k < 4; ++k) {
                     const float2 f = __half22float2(rh[k]);
-                    x[2 * k] += f.x;
-                    x[2 * k + 1] += f.y;
+                    rc[c * 8 + 2 * k] += f.x;
+                    rc[c * 8 + 2 * k + 1] += f.y;
                   }
                 }
-                if (!last) {
-                  if (valid) {
+              }
+              T2_TIMED(t_wait, mbar_wait((a_acc_full + 8 * (sl)), (g / NSLOT) & 1));
+              fence_after();
+              uint32_t v[NB];
+              const uint32_t taddr = tmem + (static_cast<uint32_t>(quad * 32) << 16) + sl * NB;
+#pragma unroll
+              for (int c = 0; c < NB / 16; ++c) tmem_ld16(taddr + c * 16, *reinterpret_cast<uint32_t(*)[16]>(&v[c * 16]));
+              tmem_ld_wait();
+              fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive((a_acc_empty + 8 * (sl)));
+              if (!last) {
+                if (valid) {
+#pragma unroll
+                  for (int c = 0; c < NCG; ++c) {
                     uint4 ov;
-                    ov.x = pack_h2(x[0], x[1]); ov.y = pack_h2(x[2], x[3]); ov.z = pack_h2(x[4], x[5]); ov.w = pack_h2(x[6], x[7]);
+                    ov.x = pack_h2(fmaxf(__uint_as_float(v[c * 8 + 0]), 0.f) + rc[c * 8 + 0], fmaxf(__uint_as_float(v[c * 8 + 1]), 0.f) + rc[c * 8 + 1]);
+                    ov.y = pack_h2(fmaxf(__uint_as_float(v[c * 8 + 2]), 0.f) + rc[c * 8 + 2], fmaxf(__uint_as_float(v[c * 8 + 3]), 0.f) + rc[c * 8 + 3]);
+                    ov.z = pack_h2(fmaxf(__uint_as_float(v[c * 8 + 4]), 0.f) + rc[c * 8 + 4], fmaxf(__uint_as_float(v[c * 8 + 5]), 0.f) + rc[c * 8 + 5]);
+                    ov.w = pack_h2(fmaxf(__uint_as_float(v[c * 8 + 6]), 0.f) + rc[c * 8 + 6], fmaxf(__uint_as_float(v[c * 8 + 7]), 0.f) + rc[c * 8 + 7]);
                     stcg16(outb + off + c * plane_bytes, ov);
                   }
-                } else if (valid) {
-#pragma unroll
-                  for (int k = 0; k < 8; ++k) psum[c * 8 + k] += x[k];
                 }
+              } else if (valid) {
+#pragma unroll
+                for (int k = 0; k < NB; ++k) psum[k] += fmaxf(__uint_as_float(v[k]), 0.f) + rc[k];
               }
             }
           }
           if (last) {
 #pragma unroll
-            for (int k = 0; k < HALF; ++k) {
+            for (int k = 0; k < NB; ++k) {
               float sum = psum[k];
 #pragma unroll
               for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-              if (lane == 0) atomicAdd(p.pool + static_cast<long long>(clip) * NB + half * HALF + k, sum);
+              if (lane == 0) atomicAdd(p.pool + static_cast<long long>(clip) * NB + k, sum);
             }
           } else {
-            __threadfence();
-            fence_proxy_async_global();
-            epi_bar();
-            if (etid == 0) red_release_gpu_add(p.flags + clip, 1);
+            epi_bar();                                        // all stores of this CTA for (clip, L) are issued
+            if (etid == 0) {
+              __threadfence();
+              fence_proxy_async_global();
+              red_release_gpu_add(p.flags + clip, 1);
+            }
           }
         }
       }
     }
+    if (p.dbg && etid == 0) p.dbg[blockIdx.x * 8 + 7] = t_wait;
   }
 
   fence_before();
@@ -454,7 +517,7 @@ struct ResTc2Plan {
   int plane_rows = 117, col_bytes = 0, stage_stride = 0, wbytes = 0, smem_bytes = 0;
   long long slot_stride = 0;
   int max_teams = 37;
-  T2Layer* d_layers = nullptr;
+  std::vector<T2Layer> layers;
   unsigned char* d_wpack = nullptr;
   float* d_cst = nullptr;
   float* d_w0 = nullptr;
@@ -530,7 +593,7 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
   const honk_model_config& c = m->cfg;
   const int C = c.n_feature_maps;
   if (c.family != HONK_FAMILY_RES || C > 48 || c.res_pool[0] > 0) return HONK_OK;
-  if (m->H0 > 112 || m->H0 < 8 || m->W0 < T2_G || m->W0 > 1024 || c.n_layers < 1) return HONK_OK;
+  if (m->H0 > 112 || m->H0 < 8 || m->W0 < T2_G || m->W0 > 1024 || c.n_layers < 1 || c.n_layers > T2_MAXL) return HONK_OK;
   for (int i = 1; i <= c.n_layers; ++i)
     if ((c.use_dilation ? (1 << ((i - 1) / 3)) : 1) > T2_PAD) return HONK_OK;
   std::unique_ptr<ResTc2Plan, void (*)(ResTc2Plan*)> p(new ResTc2Plan(), res_tc2_plan_free);
@@ -600,7 +663,7 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
                 hw[idx] = __float2half(v);
               }
   }
-  HONK_TRY(up(p.get(), layers, &p->d_layers));
+  p->layers = layers;
   HONK_TRY(up(p.get(), wpack, &p->d_wpack));
   HONK_TRY(up(p.get(), cst, &p->d_cst));
   {
@@ -657,7 +720,7 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
   // zero rows between planes must be zero; pool sums and layer counters start at zero
   HONK_CUDA(cudaMemsetAsync(act, 0, static_cast<size_t>(ar.off), s));
   T2Params a{};
-  a.layers = p->d_layers;
+  for (size_t i = 0; i < p->layers.size(); ++i) a.layers[i] = p->layers[i];
   a.wpack = p->d_wpack;
   a.cst = p->d_cst;
   a.mfcc = d_mfcc;
@@ -676,11 +739,32 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
   a.col_bytes = p->col_bytes;
   a.stage_stride = p->stage_stride;
   a.wbytes = p->wbytes;
+  a.dbg = nullptr;
+  if (const char* e = getenv("HONK_TC2_MODE")) a.mode = atoi(e);
+  static long long* s_dbg = nullptr;
+  const char* dbg_env = getenv("HONK_TC2_DEBUG");
+  if (dbg_env && atoi(dbg_env)) {
+    if (!s_dbg) HONK_CUDA(cudaMalloc(&s_dbg, 160 * 8 * sizeof(long long)));
+    HONK_CUDA(cudaMemsetAsync(s_dbg, 0, 160 * 8 * sizeof(long long), s));
+    a.dbg = s_dbg;
+  }
   {
     ProfSpan span("res_conv", s);
     if (p->ncg == 6) tc2_res_kernel<6><<<teams * T2_G, T2_THREADS, p->smem_bytes, s>>>(a);
     else tc2_res_kernel<4><<<teams * T2_G, T2_THREADS, p->smem_bytes, s>>>(a);
     HONK_LAUNCH_CHECK();
+  }
+  if (a.dbg) {
+    std::vector<long long> h(160 * 8);
+    HONK_CUDA(cudaStreamSynchronize(s));
+    HONK_CUDA(cudaMemcpy(h.data(), a.dbg, h.size() * sizeof(long long), cudaMemcpyDeviceToHost));
+    double m[8] = {0};
+    const int nb = teams * T2_G;
+    for (int b = 0; b < nb; ++b)
+      for (int k = 0; k < 8; ++k) m[k] += static_cast<double>(h[b * 8 + k]) / nb;
+    fprintf(stderr, "tc2 dbg (mean cycles/CTA, %d CTAs, %lld clips): producer total %.0f flag-wait %.0f stage-empty-wait %.0f | "
+            "mma total %.0f acc-empty-wait %.0f stage-full-wait %.0f weight-wait %.0f | epilogue acc-full-wait %.0f\n",
+            nb, static_cast<long long>(n_clips), m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[7]);
   }
   {
     ProfSpan span("res_tail", s);

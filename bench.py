@@ -342,14 +342,17 @@ def main():
             flops_layer_clip = 2 * 9 * C * C * H * W                     # unpadded 2*MAC of one C->C 3x3 layer
             t_ms, n_spans = spans["res_conv"]
             clips_done = B * args.steps
-            n_launch = n_spans * n_layers
+            persistent = "res_conv0" not in spans          # one launch runs conv0 + all C->C layers (res_tc2.cu)
+            n_launch = n_spans if persistent else n_spans * n_layers
             avg_launch_ms = t_ms / n_launch
             achieved = flops_layer_clip * n_layers * clips_done / (t_ms * 1e-3) / 1e12
-            roof = {"bound": "tensor", "kernel": "tc_conv_kernel (dilated 3x3 C->C implicit GEMM, tcgen05)",
+            roof = {"bound": "tensor",
+                    "kernel": ("tc2_res_kernel (persistent: conv0 + %d dilated 3x3 C->C layers, tcgen05 ring-accumulate)" % n_layers)
+                              if persistent else "tc_conv_kernel (dilated 3x3 C->C implicit GEMM, tcgen05)",
                     "achieved": achieved, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
                     "frac": achieved / peaks["tf_sustained"], "peak_source": peaks["source"] + " bf16 sustained",
-                    "traffic": None, "avg_launch_ms": avg_launch_ms,
-                    "flops_per_launch": flops_layer_clip * clips_done / n_spans,
+                    "traffic": None, "avg_launch_ms": avg_launch_ms, "launches_per_step": n_launch / args.steps,
+                    "flops_per_launch": flops_layer_clip * n_layers * clips_done / n_launch,
                     "share_of_step": t_ms / (ms * args.steps)}
         elif "f32_model" in spans:
             t_ms, n_spans = spans["f32_model"]

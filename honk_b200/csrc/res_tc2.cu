@@ -13,18 +13,21 @@
 // are start-address offsets of the A operand (rows of the staged column), time dilation = kh*d
 // rows, zero padding = physically zero rows between the channel planes in HBM.
 //
-// BatchNorm (affine=False, after the residual add, model.py:112-118) is folded exactly: the
-// stored activation is z_i = x_i - mean_i, so zero padding of z equals the reference's zero
-// padding of bn_i(x_i); the scale 1/sqrt(var_i+eps) is folded into the NEXT layer's weights, and
-// the raw residual is recovered as x_{i-2} = z_{i-2} + mean_{i-2} from the buffer the previous
-// layer read.  Even layers therefore update their residual buffer in place and two rotating
-// buffers (P, Q) per clip suffice.
+// BatchNorm (affine=False, after the residual add, model.py:112-118) is folded exactly.  The stored
+// activation is the raw x_i = relu(conv_i) [+ x_{i-2}] (so the residual stream needs no extra
+// copy: even layers update their residual buffer in place and two rotating buffers P, Q per clip
+// suffice).  bn_i's scale 1/sqrt(var_i+eps) is folded into conv_{i+1}'s weights, and its mean shift
+// into two spare input channels (NB-2, NB-1) that hold 1.0 at real positions and 0 in the padding:
+// their per-tap weights are the hi/lo f16 halves of -sum_ci W*scale*mean, so exactly the in-range
+// taps subtract the mean - the same result as zero padding applied after bn_i.
 //
-// Scheduling.  A team of 4 CTAs (consecutive blockIdx) owns two clips at a time and runs them
-// through all layers, alternating clips per layer so that the team-wide "layer done" flag of one
-// clip is hidden behind the other clip's work.  Each CTA owns whole chains (or chain segments
-// with one halo input column per cut).  Roles: warp 0 = bulk-copy (TMA) producer, warp 1 = MMA
-// issuer, warps 2-9 = epilogue (TMEM -> ReLU + residual + mean shift -> f16 -> L2) and conv0.
+// Scheduling.  A team of 4 CTAs (consecutive blockIdx) owns K = 3 clips at a time and runs them
+// through all layers in lockstep (A.L, B.L, C.L, A.L+1, ...), so the team-wide "layer L of clip A
+// done" flag (a release counter in global memory) is hidden behind the other clips' work.  Each
+// CTA owns whole chains (or chain segments with one halo input column per cut).  Roles: warp 0 =
+// bulk-copy (TMA) producer, warp 1 = MMA issuer, warps 2-9 = epilogue (TMEM -> ReLU + residual ->
+// f16 -> L2; two groups of 4 warps take alternate columns) and conv0, warp 10 = flag signaller.
+// Working set: 37 teams x 3 clips x 2 buffers x 449 KB = 100 MB, L2-resident.
 #include "res_tc.cuh"
 #include "umma.cuh"
 
@@ -42,7 +45,7 @@ using namespace umma;
 
 constexpr int T2_G = 4;           // CTAs per team
 constexpr int T2_NSTAGE = 8;      // A-operand stages (one input column each)
-constexpr int T2_THREADS = 320;
+constexpr int T2_THREADS = 352;    // warp 0 producer, 1 MMA, 2-9 epilogue, 10 flag signaller
 constexpr int T2_PAD = 16;        // zero rows above every channel plane (>= max dilation)
 constexpr int T2_MAXSEG = 8;
 constexpr int T2_MAXL = 24;       // layers (res26)
@@ -59,14 +62,13 @@ struct T2Layer {
   int d;                          // dilation
   int flags;                      // bit0: add residual, bit1: last layer (pool, no store)
   int w_off;                      // byte offset of this layer's packed weights
-  int cst_off;                    // float offset of the epilogue constants [NB]
+  int reserved;
   int n_seg[T2_G];
   T2Seg seg[T2_G][T2_MAXSEG];
 };
 
 struct T2Params {
   const unsigned char* wpack;
-  const float* cst;
   const float* mfcc;              // [n_clips][H][W] float32
   const float* w0;                // conv0 weights [9][NB]
   unsigned char* P;               // [n_slots] activation buffers
@@ -75,6 +77,7 @@ struct T2Params {
   unsigned int* flags;            // [n_clips] team-wide layer counters
   long long slot_stride;          // bytes per clip buffer
   int n_layers, n_clips, n_slots;
+  int K;                          // clips per team in flight
   int H, W;
   int plane_rows;                 // H + T2_PAD
   int col_bytes;                  // NCG * plane_rows * 16
@@ -107,11 +110,17 @@ __device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
 __device__ __forceinline__ void red_release_gpu_add(unsigned int* p, unsigned int v) {
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ unsigned int ld_relaxed_gpu(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// Polls with relaxed loads (an acquire load invalidates the SM's L1 on every poll) and acquires once.
 __device__ __forceinline__ void wait_flag(const unsigned int* p, unsigned int target) {
-  for (uint32_t i = 0; ld_acquire_gpu(p) < target; ++i) {
-    __nanosleep(40);
+  for (uint32_t i = 0; ld_relaxed_gpu(p) < target; ++i) {
     if (i > (1u << 25)) __trap();
   }
+  asm volatile("fence.acq_rel.gpu;" ::: "memory");
 }
 __device__ __forceinline__ uint4 ldcg16(const void* p) {
   uint4 v;
@@ -127,6 +136,12 @@ __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
   return r;
 }
 #define T2_TIMED(acc, stmt) do { if (p.mode == 1) break; if (p.dbg) { const long long t__ = clock64(); stmt; acc += clock64() - t__; } else { stmt; } } while (0)
+// relu(y) + r on packed halves (r = 0 when the layer has no residual)
+__device__ __forceinline__ uint32_t relu_add_h2(uint32_t y, uint32_t r) {
+  uint32_t o;
+  asm("{\n\t.reg .b32 t;\n\tmax.f16x2 t, %1, %3;\n\tadd.rn.f16x2 %0, t, %2;\n\t}" : "=r"(o) : "r"(y), "r"(r), "r"(0u));
+  return o;
+}
 __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 template <int NCG>
@@ -142,6 +157,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
   __shared__ __align__(8) uint64_t bar_full[T2_NSTAGE], bar_empty[T2_NSTAGE];
   __shared__ __align__(8) uint64_t bar_acc_full[NSLOT], bar_acc_empty[NSLOT];
   __shared__ __align__(8) uint64_t bar_wfull[2], bar_wfree[2];
+  __shared__ __align__(8) uint64_t bar_done[4];        // epilogue -> signaller: this CTA's stores of one (clip, layer) are issued
   __shared__ uint32_t tmem_base_s;
 
   const int tid = threadIdx.x, lane = tid & 31;
@@ -149,12 +165,13 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
   const uint32_t a_full = smem_u32(&bar_full[0]), a_empty = smem_u32(&bar_empty[0]);
   const uint32_t a_acc_full = smem_u32(&bar_acc_full[0]), a_acc_empty = smem_u32(&bar_acc_empty[0]);
   const uint32_t a_wfull = smem_u32(&bar_wfull[0]), a_wfree = smem_u32(&bar_wfree[0]);
+  const uint32_t a_done = smem_u32(&bar_done[0]);
   const int team = blockIdx.x / T2_G, rank = blockIdx.x % T2_G, n_teams = gridDim.x / T2_G;
   unsigned char* stages = smem;
   unsigned char* wbuf = smem + T2_NSTAGE * p.stage_stride;
   float* xs = reinterpret_cast<float*>(wbuf + 2 * p.wbytes);          // conv0 input tile [(H+2)][XS]
   const int XS = p.W + 3;
-  float* w0s = xs + (p.H + 2) * XS;                                   // [9][NB]
+  float* w0s = xs + (((p.H + 2) * XS + 3) & ~3);                      // [9][NB], 16-byte aligned
 
   if (warp == 1) tmem_alloc(smem_u32(&tmem_base_s), 512);
   if (tid == 0) {
@@ -170,6 +187,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
       mbar_init((a_wfull + 8 * (k)), 1);
       mbar_init((a_wfree + 8 * (k)), 1);
     }
+    for (int k = 0; k < 4; ++k) mbar_init(a_done + 8 * k, 8);
     fence_mbar_init();
   }
   for (int i = tid; i < 9 * NB; i += T2_THREADS) w0s[i] = __ldg(p.w0 + i);
@@ -177,7 +195,8 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
   __syncthreads();
   fence_after();
   const uint32_t tmem = tmem_base_s;
-  const int n_pairs = (p.n_clips + 1) / 2;
+  const int K = p.K;                                  // clips a team runs in lockstep (layer-interleaved)
+  const int n_pairs = (p.n_clips + K - 1) / K;        // clip groups
   const int plane_bytes = p.plane_rows * 16;
 
   if (warp == 0) {
@@ -188,7 +207,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
       long long t_flag = 0, t_empty = 0;
       const long long t_start = clock64();
       for (int pair = team; pair < n_pairs; pair += n_teams, ++piter) {
-        const int nab = min(2, p.n_clips - 2 * pair);
+        const int nab = min(K, p.n_clips - K * pair);
         for (int L = 1; L <= p.n_layers; ++L, ++q) {
           const T2Layer& ly = p.layers[L - 1];
           if (q == 0) {
@@ -199,8 +218,8 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
           const uint32_t bytes = (NCG - 1) * plane_bytes + (p.H + 2 * d) * 16;
           const int nseg = ly.n_seg[rank];
           for (int ab = 0; ab < nab; ++ab) {
-            const int clip = 2 * pair + ab, slot = 2 * team + ab;
-            const unsigned char* in = (L & 1) ? p.Q + (static_cast<long long>(piter & 1) * p.n_slots + slot) * p.slot_stride
+            const int clip = K * pair + ab, slot = K * team + ab;
+            const unsigned char* in = (L & 1) ? p.Q + static_cast<long long>(slot) * p.slot_stride
                                               : p.P + static_cast<long long>(slot) * p.slot_stride;
             in += (T2_PAD - d) * 16;
             T2_TIMED(t_flag, wait_flag(p.flags + clip, T2_G * L));          // every CTA of the team finished layer L-1 (conv0 = layer 0)
@@ -245,7 +264,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
     long long t_acc = 0, t_full = 0, t_w = 0;
     const long long t_start = clock64();
     for (int pair = team; pair < n_pairs; pair += n_teams) {
-      const int nab = min(2, p.n_clips - 2 * pair);
+      const int nab = min(K, p.n_clips - K * pair);
       for (int L = 1; L <= p.n_layers; ++L, ++q) {
         const T2Layer& ly = p.layers[L - 1];
         const uint32_t d = ly.d;
@@ -343,21 +362,23 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
       mbar_wait((a_full + 8 * (0)), 0);
     }
     if (p.dbg && lane == 0) { long long* o = p.dbg + blockIdx.x * 8; o[3] = clock64() - t_start; o[4] = t_acc; o[5] = t_full; o[6] = t_w; }
-  } else if (p.mode != 1) {
+  } else if (warp < 10 && p.mode != 1) {
     // ======================================= epilogue =======================================
     const int ew = warp - 2, quad = warp & 3, half = ew >> 2;
     const int h = quad * 32 + lane;
     const bool valid = h < p.H;
     const int etid = ew * 32 + lane;
-    uint32_t g = 0;
+    uint32_t g = 0, ev = 0;
     int piter = 0;
     long long t_wait = 0;
     for (int pair = team; pair < n_pairs; pair += n_teams, ++piter) {
-      const int nab = min(2, p.n_clips - 2 * pair);
-      const long long qoff = static_cast<long long>(piter & 1) * p.n_slots;
+      const int nab = min(K, p.n_clips - K * pair);
+      const long long qoff = 0;
       // ---- layer 0: conv0 1->C 3x3 pad 1 + ReLU in FP32 (model.py:107-111); z0 = x0 -> Q ----
       for (int ab = 0; ab < nab; ++ab) {
-        const int clip = 2 * pair + ab, slot = 2 * team + ab;
+        const int clip = K * pair + ab, slot = K * team + ab;
+        // the slot's Q buffer is still read by the team's last-layer MMAs of the previous group's clip
+        if (etid == 0 && piter > 0) wait_flag(p.flags + (clip - K * n_teams), T2_G * (p.n_layers + 1));
         epi_bar();
         const float* src = p.mfcc + static_cast<long long>(clip) * p.H * p.W;
         for (int i = etid; i < (p.H + 2) * XS; i += T2_EPI_THREADS) {
@@ -385,29 +406,30 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
               o.y = pack_h2(fmaxf(a[c * 8 + 2], 0.f), fmaxf(a[c * 8 + 3], 0.f));
               o.z = pack_h2(fmaxf(a[c * 8 + 4], 0.f), fmaxf(a[c * 8 + 5], 0.f));
               o.w = pack_h2(fmaxf(a[c * 8 + 6], 0.f), fmaxf(a[c * 8 + 7], 0.f));
+              if (half == 1 && c == HALF / 8 - 1) o.w = 0x3C003C00u;   // constant-one channels NB-2, NB-1
               stcg16(dst + static_cast<long long>(w) * p.col_bytes + (half * (HALF / 8) + c) * plane_bytes + (T2_PAD + h) * 16, o);
             }
           }
         }
-        epi_bar();
-        if (etid == 0) {
-          __threadfence();
-          fence_proxy_async_global();
-          red_release_gpu_add(p.flags + clip, 1);
-        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(a_done + 8 * (ev & 3));       // the signaller warp publishes the team flag
+        ++ev;
       }
-      // ---- layers 1..n: the two groups of 4 warps take alternate output columns (all NB channels each) ----
+      // ---- layers 1..n: the two groups of 4 warps take alternate output columns (all NB channels each).
+      // Stored activations are the raw x_L = relu(conv) [+ x_{L-2}]; BatchNorm lives in the next layer's weights
+      // (scale) and in its two constant-one input channels (mean shift, exact at the zero-padded borders).
       for (int L = 1; L <= p.n_layers; ++L) {
         const T2Layer& ly = p.layers[L - 1];
         const int d = ly.d, flags = ly.flags;
         const bool add_res = flags & 1, last = flags & 2;
         const int nseg = ly.n_seg[rank];
-        const float4* c4 = reinterpret_cast<const float4*>(p.cst + ly.cst_off);
+        const long long cstep = 2ll * d * p.col_bytes;        // this group's next column of a segment
         for (int ab = 0; ab < nab; ++ab) {
-          const int clip = 2 * pair + ab, slot = 2 * team + ab;
+          const int clip = K * pair + ab, slot = K * team + ab;
           unsigned char* Qs = p.Q + (qoff + slot) * p.slot_stride + (T2_PAD + h) * 16;
           unsigned char* Ps = p.P + static_cast<long long>(slot) * p.slot_stride + (T2_PAD + h) * 16;
           unsigned char* outb = (L & 1) ? Ps : Qs;            // odd: Q -> P ; even: P (+Q residual) -> Q in place
+          const bool ld_res = add_res && valid;
           float psum[NB];
           if (last) {
 #pragma unroll
@@ -415,32 +437,28 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
           }
           for (int s = 0; s < nseg; ++s) {
             const T2Seg& sg = ly.seg[rank][s];
-            const int r = sg.r, j0 = sg.j0, n_out = sg.n_out;
-            for (int o = j0; o < j0 + n_out; ++o, ++g) {
-              if ((g & 1) != static_cast<uint32_t>(half)) continue;
-              const int sl = g % NSLOT;
-              const long long off = static_cast<long long>(r + o * d) * p.col_bytes;
-              // rc = residual + epilogue constant, prepared while the MMAs of this column are still running
-              float rc[NB];
+            const int j0 = sg.j0, jlim = sg.j0 + sg.n_out;
+            const int o0 = j0 + ((g ^ static_cast<uint32_t>(half)) & 1);   // first column of this group
+            uint32_t gi = g + (o0 - j0);
+            g += sg.n_out;
+            long long off = static_cast<long long>(sg.r + o0 * d) * p.col_bytes;
+            uint4 rv[NCG];                                     // residual, prefetched one column ahead
 #pragma unroll
-              for (int k = 0; k < NB / 4; ++k) {
-                const float4 v = __ldg(c4 + k);
-                rc[4 * k] = v.x; rc[4 * k + 1] = v.y; rc[4 * k + 2] = v.z; rc[4 * k + 3] = v.w;
+            for (int c = 0; c < NCG; ++c) rv[c] = make_uint4(0, 0, 0, 0);
+            if (ld_res && o0 < jlim) {
+#pragma unroll
+              for (int c = 0; c < NCG; ++c) rv[c] = ldcg16(Qs + off + c * plane_bytes);
+            }
+            for (int o = o0; o < jlim; o += 2, gi += 2, off += cstep) {
+              const uint32_t sl = gi % NSLOT;
+              uint4 rc[NCG];
+#pragma unroll
+              for (int c = 0; c < NCG; ++c) rc[c] = rv[c];
+              if (ld_res && o + 2 < jlim) {
+#pragma unroll
+                for (int c = 0; c < NCG; ++c) rv[c] = ldcg16(Qs + off + cstep + c * plane_bytes);
               }
-              if (add_res && valid) {
-#pragma unroll
-                for (int c = 0; c < NCG; ++c) {
-                  const uint4 rv = ldcg16(Qs + off + c * plane_bytes);
-                  const __half2* rh = reinterpret_cast<const __half2*>(&rv);
-#pragma unroll
-                  for (int k = 0; k < 4; ++k) {
-                    const float2 f = __half22float2(rh[k]);
-                    rc[c * 8 + 2 * k] += f.x;
-                    rc[c * 8 + 2 * k + 1] += f.y;
-                  }
-                }
-              }
-              T2_TIMED(t_wait, mbar_wait((a_acc_full + 8 * (sl)), (g / NSLOT) & 1));
+              T2_TIMED(t_wait, mbar_wait(a_acc_full + 8 * sl, (gi / NSLOT) & 1));
               fence_after();
               uint32_t v[NB];
               const uint32_t taddr = tmem + (static_cast<uint32_t>(quad * 32) << 16) + sl * NB;
@@ -449,22 +467,29 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
               tmem_ld_wait();
               fence_before();
               __syncwarp();
-              if (lane == 0) mbar_arrive((a_acc_empty + 8 * (sl)));
+              if (lane == 0) mbar_arrive(a_acc_empty + 8 * sl);
               if (!last) {
-                if (valid) {
 #pragma unroll
-                  for (int c = 0; c < NCG; ++c) {
-                    uint4 ov;
-                    ov.x = pack_h2(fmaxf(__uint_as_float(v[c * 8 + 0]), 0.f) + rc[c * 8 + 0], fmaxf(__uint_as_float(v[c * 8 + 1]), 0.f) + rc[c * 8 + 1]);
-                    ov.y = pack_h2(fmaxf(__uint_as_float(v[c * 8 + 2]), 0.f) + rc[c * 8 + 2], fmaxf(__uint_as_float(v[c * 8 + 3]), 0.f) + rc[c * 8 + 3]);
-                    ov.z = pack_h2(fmaxf(__uint_as_float(v[c * 8 + 4]), 0.f) + rc[c * 8 + 4], fmaxf(__uint_as_float(v[c * 8 + 5]), 0.f) + rc[c * 8 + 5]);
-                    ov.w = pack_h2(fmaxf(__uint_as_float(v[c * 8 + 6]), 0.f) + rc[c * 8 + 6], fmaxf(__uint_as_float(v[c * 8 + 7]), 0.f) + rc[c * 8 + 7]);
-                    stcg16(outb + off + c * plane_bytes, ov);
-                  }
+                for (int c = 0; c < NCG; ++c) {
+                  uint32_t w4[4];
+                  const uint32_t* rr = reinterpret_cast<const uint32_t*>(&rc[c]);
+#pragma unroll
+                  for (int k = 0; k < 4; ++k)
+                    w4[k] = relu_add_h2(pack_h2(__uint_as_float(v[c * 8 + 2 * k]), __uint_as_float(v[c * 8 + 2 * k + 1])), rr[k]);
+                  if (c == NCG - 1) w4[3] = 0x3C003C00u;       // the two constant-one channels
+                  if (valid) stcg16(outb + off + c * plane_bytes, make_uint4(w4[0], w4[1], w4[2], w4[3]));
                 }
               } else if (valid) {
 #pragma unroll
-                for (int k = 0; k < NB; ++k) psum[k] += fmaxf(__uint_as_float(v[k]), 0.f) + rc[k];
+                for (int c = 0; c < NCG; ++c) {
+                  const __half2* rh = reinterpret_cast<const __half2*>(&rc[c]);
+#pragma unroll
+                  for (int k = 0; k < 4; ++k) {
+                    const float2 f = __half22float2(rh[k]);
+                    psum[c * 8 + 2 * k] += fmaxf(__uint_as_float(v[c * 8 + 2 * k]), 0.f) + f.x;
+                    psum[c * 8 + 2 * k + 1] += fmaxf(__uint_as_float(v[c * 8 + 2 * k + 1]), 0.f) + f.y;
+                  }
+                }
               }
             }
           }
@@ -476,18 +501,32 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
               for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
               if (lane == 0) atomicAdd(p.pool + static_cast<long long>(clip) * NB + k, sum);
             }
-          } else {
-            epi_bar();                                        // all stores of this CTA for (clip, L) are issued
-            if (etid == 0) {
-              __threadfence();
-              fence_proxy_async_global();
-              red_release_gpu_add(p.flags + clip, 1);
-            }
           }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(a_done + 8 * (ev & 3));     // this warp's stores for (clip, L) are issued
+          ++ev;
         }
       }
     }
     if (p.dbg && etid == 0) p.dbg[blockIdx.x * 8 + 7] = t_wait;
+  } else if (warp == 10 && p.mode != 1) {
+    // ======================================= flag signaller =================================
+    // Publishes "all stores of this CTA for (clip, layer) are visible" to the team: waits until the eight
+    // epilogue warps have arrived, then a gpu-scope fence (cumulative over the stores observed through the
+    // mbarrier) + release increment of the clip's layer counter.  Keeps fences off the epilogue warps.
+    if (lane == 0) {
+      uint32_t ev = 0;
+      for (int pair = team; pair < n_pairs; pair += n_teams) {
+        const int nab = min(K, p.n_clips - K * pair);
+        for (int L = 0; L <= p.n_layers; ++L) {             // L = 0 is conv0
+          for (int ab = 0; ab < nab; ++ab, ++ev) {
+            mbar_wait(a_done + 8 * (ev & 3), (ev >> 2) & 1);
+            fence_proxy_async_global();
+            red_release_gpu_add(p.flags + K * pair + ab, 1);
+          }
+        }
+      }
+    }
   }
 
   fence_before();
@@ -517,9 +556,9 @@ struct ResTc2Plan {
   int plane_rows = 117, col_bytes = 0, stage_stride = 0, wbytes = 0, smem_bytes = 0;
   long long slot_stride = 0;
   int max_teams = 37;
+  int K = 3;                      // clips per team in flight: 37 teams x 3 x 2 buffers x 449 KB = 100 MB of L2
   std::vector<T2Layer> layers;
   unsigned char* d_wpack = nullptr;
-  float* d_cst = nullptr;
   float* d_w0 = nullptr;
   float* d_wout = nullptr;
   float* d_bout = nullptr;
@@ -592,13 +631,13 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
   *out = nullptr;
   const honk_model_config& c = m->cfg;
   const int C = c.n_feature_maps;
-  if (c.family != HONK_FAMILY_RES || C > 48 || c.res_pool[0] > 0) return HONK_OK;
+  if (c.family != HONK_FAMILY_RES || C > 46 || c.res_pool[0] > 0) return HONK_OK;   // two spare channels carry the mean shift
   if (m->H0 > 112 || m->H0 < 8 || m->W0 < T2_G || m->W0 > 1024 || c.n_layers < 1 || c.n_layers > T2_MAXL) return HONK_OK;
   for (int i = 1; i <= c.n_layers; ++i)
     if ((c.use_dilation ? (1 << ((i - 1) / 3)) : 1) > T2_PAD) return HONK_OK;
   std::unique_ptr<ResTc2Plan, void (*)(ResTc2Plan*)> p(new ResTc2Plan(), res_tc2_plan_free);
   p->C = C;
-  p->ncg = C <= 32 ? 4 : 6;
+  p->ncg = C <= 30 ? 4 : 6;
   p->NB = p->ncg * 8;
   p->H = m->H0;
   p->W = m->W0;
@@ -610,11 +649,12 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
   // a stage holds planes 0..ncg-1 of one column; the kh taps over-read up to 127 + 2*16 rows of the last plane
   p->stage_stride = static_cast<int>(align_up((p->ncg - 1) * p->plane_rows * 16 + (128 + 2 * T2_PAD) * 16, 128));
   p->wbytes = 3 * (p->ncg / 2) * 6 * p->NB * 16;
-  p->smem_bytes = T2_NSTAGE * p->stage_stride + 2 * p->wbytes + ((p->H + 2) * (p->W + 3) + 9 * p->NB) * 4;
+  p->smem_bytes = T2_NSTAGE * p->stage_stride + 2 * p->wbytes + (((p->H + 2) * (p->W + 3) + 3) / 4 * 4 + 9 * p->NB) * 4;
   int max_smem = 0;
   HONK_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, m->device));
   if (p->smem_bytes + 2048 > max_smem) return HONK_OK;
   p->max_teams = std::max(1, m->n_sms / T2_G);
+  if (const char* e = getenv("HONK_TC2_K")) p->K = std::max(1, std::min(8, atoi(e)));
   const int N = p->NB, ncg = p->ncg, NKC = ncg / 2;
 
   // per-layer BatchNorm statistics (mean_0 = 0, scale_0 = 1: conv1 reads the raw conv0 output)
@@ -629,7 +669,6 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
   }
   std::vector<T2Layer> layers(c.n_layers);
   std::vector<unsigned char> wpack(static_cast<size_t>(c.n_layers) * p->wbytes, 0);
-  std::vector<float> cst(static_cast<size_t>(c.n_layers) * N, 0.f);
   for (int L = 1; L <= c.n_layers; ++L) {
     T2Layer& ly = layers[L - 1];
     memset(&ly, 0, sizeof(ly));
@@ -637,35 +676,38 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
     const bool even = (L % 2 == 0), last = (L == c.n_layers);
     ly.flags = (even ? 1 : 0) | (last ? 2 : 0);
     ly.w_off = (L - 1) * p->wbytes;
-    ly.cst_off = (L - 1) * N;
     if (!plan_segments(ly, p->W, ly.d)) return HONK_OK;
-    // epilogue constant: z_L = relu(acc) [+ z_{L-2}] + cst ; last layer pools x_L itself
-    for (int k = 0; k < C; ++k) {
-      float v = even ? mean[L - 2][k] : 0.f;
-      if (!last) v -= mean[L][k];
-      cst[static_cast<size_t>(L - 1) * N + k] = v;
-    }
-    // B operand: [i = kh*NKC + kc][K half][n = blk*NB + co][ci % 8], blk <-> kw = 2 - blk,
-    // value = W[co][ci][kh][kw] * scale_{L-1}[ci]
+    // B operand: [i = kh*NKC + kc][K half][n = blk*NB + co][ci % 8], blk <-> kw = 2 - blk.
+    //   ci <  C       : W[co][ci][kh][kw] * scale_{L-1}[ci]                 (BatchNorm scale of the producer)
+    //   ci = NB-1/NB-2: hi / lo halves of  -sum_ci W*scale*mean_{L-1}[ci]   per TAP; these input channels hold
+    //                   1.0 at real positions and 0 in the padding, so only in-range taps subtract the mean,
+    //                   exactly like zero padding applied after bn_{L-1} (model.py:112-118)
     const HostTensor& w = m->host.at("conv" + std::to_string(L) + ".weight");
     __half* hw = reinterpret_cast<__half*>(wpack.data() + static_cast<size_t>(L - 1) * p->wbytes);
+    auto slot = [&](int kh, int blk, int co, int ci) -> __half& {
+      const int kc = ci / 16, khalf = (ci % 16) / 8, e = ci % 8;
+      return hw[((static_cast<size_t>(kh * NKC + kc) * 2 + khalf) * (3 * N) + blk * N + co) * 8 + e];
+    };
     for (int kh = 0; kh < 3; ++kh)
-      for (int kc = 0; kc < NKC; ++kc)
-        for (int khalf = 0; khalf < 2; ++khalf)
-          for (int blk = 0; blk < 3; ++blk)
-            for (int co = 0; co < C; ++co)
-              for (int e = 0; e < 8; ++e) {
-                const int ci = kc * 16 + khalf * 8 + e;
-                if (ci >= C) continue;
-                const int kw = 2 - blk;
-                const float v = w.data[((static_cast<size_t>(co) * C + ci) * 3 + kh) * 3 + kw] * scale[L - 1][ci];
-                const size_t idx = ((static_cast<size_t>(kh * NKC + kc) * 2 + khalf) * (3 * N) + blk * N + co) * 8 + e;
-                hw[idx] = __float2half(v);
-              }
+      for (int blk = 0; blk < 3; ++blk) {
+        const int kw = 2 - blk;
+        for (int co = 0; co < C; ++co) {
+          double bias = 0.0;
+          for (int ci = 0; ci < C; ++ci) {
+            const float v = w.data[((static_cast<size_t>(co) * C + ci) * 3 + kh) * 3 + kw] * scale[L - 1][ci];
+            const __half hv = __float2half(v);
+            slot(kh, blk, co, ci) = hv;
+            bias -= static_cast<double>(__half2float(hv)) * mean[L - 1][ci];   // mean of what the MMA really multiplies
+          }
+          const __half hi = __float2half(static_cast<float>(bias));
+          const __half lo = __float2half(static_cast<float>(bias - static_cast<double>(__half2float(hi))));
+          slot(kh, blk, co, N - 1) = hi;
+          slot(kh, blk, co, N - 2) = lo;
+        }
+      }
   }
   p->layers = layers;
   HONK_TRY(up(p.get(), wpack, &p->d_wpack));
-  HONK_TRY(up(p.get(), cst, &p->d_cst));
   {
     const HostTensor& w = m->host.at("conv0.weight");
     std::vector<float> h(9 * N, 0.f);
@@ -697,13 +739,13 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
 }
 
 static int tc2_teams(const ResTc2Plan* p, int64_t n_clips) {
-  return static_cast<int>(std::min<int64_t>(p->max_teams, (n_clips + 1) / 2));
+  return static_cast<int>(std::min<int64_t>(p->max_teams, (n_clips + p->K - 1) / p->K));
 }
 
 int64_t res_tc2_workspace_bytes(const ResTc2Plan* p, int64_t n_clips) {
-  const int n_slots = 2 * tc2_teams(p, n_clips);
+  const int n_slots = p->K * tc2_teams(p, n_clips);
   Arena a(nullptr, 0);
-  a.take<unsigned char>(3ll * n_slots * p->slot_stride);
+  a.take<unsigned char>(2ll * n_slots * p->slot_stride);
   a.take<float>(n_clips * p->NB);
   a.take<unsigned int>(n_clips);
   return align_up(a.off, 256);
@@ -711,9 +753,9 @@ int64_t res_tc2_workspace_bytes(const ResTc2Plan* p, int64_t n_clips) {
 
 int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, float* d_logits, void* ws, int64_t ws_bytes,
                     cudaStream_t s) {
-  const int teams = tc2_teams(p, n_clips), n_slots = 2 * teams;
+  const int teams = tc2_teams(p, n_clips), n_slots = p->K * teams;
   Arena ar(ws, ws_bytes);
-  unsigned char* act = ar.take<unsigned char>(3ll * n_slots * p->slot_stride);
+  unsigned char* act = ar.take<unsigned char>(2ll * n_slots * p->slot_stride);
   float* pool = ar.take<float>(n_clips * p->NB);
   unsigned int* flags = ar.take<unsigned int>(n_clips);
   HONK_CHECK(ar.ok(), HONK_ERR_WORKSPACE, "internal: tcgen05 workspace overrun");
@@ -722,7 +764,6 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
   T2Params a{};
   for (size_t i = 0; i < p->layers.size(); ++i) a.layers[i] = p->layers[i];
   a.wpack = p->d_wpack;
-  a.cst = p->d_cst;
   a.mfcc = d_mfcc;
   a.w0 = p->d_w0;
   a.P = act;
@@ -733,6 +774,7 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
   a.n_layers = p->n_layers;
   a.n_clips = static_cast<int>(n_clips);
   a.n_slots = n_slots;
+  a.K = p->K;
   a.H = p->H;
   a.W = p->W;
   a.plane_rows = p->plane_rows;

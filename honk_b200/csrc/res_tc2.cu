@@ -152,6 +152,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
   constexpr int HALF = NB / 2;           // columns per epilogue warp
   constexpr int BT16 = 6 * NB;           // one (kh,kc) B tile in 16-byte units: 2 K-halves x 3NB rows
   constexpr int NMMA = 3 * NKC;          // MMAs per input column
+  constexpr int NSPLIT = NMMA / 2 + 1;   // MMAs issued before the look-ahead probe of the next task
 
   extern __shared__ __align__(1024) unsigned char smem[];
   __shared__ __align__(8) uint64_t bar_full[T2_NSTAGE], bar_empty[T2_NSTAGE];
@@ -248,7 +249,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
           }
         }
       }
-      if (p.dbg) { long long* o = p.dbg + blockIdx.x * 8; o[0] = clock64() - t_start; o[1] = t_flag; o[2] = t_empty; }
+      if (p.dbg) { long long* o = p.dbg + blockIdx.x * 16; o[0] = clock64() - t_start; o[1] = t_flag; o[2] = t_empty; }
     }
   } else if (warp == 1) {
     // ======================================= MMA issuer =====================================
@@ -261,7 +262,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
     constexpr uint32_t IDESC0 = make_idesc(128, 0, 0), IDESC_BLK = static_cast<uint32_t>(NB >> 3) << 17;
     uint32_t st = 0, stpar = 0, q = 0;
     int gseg = 2 * NSLOT;                       // ring index of the segment's first output (offset keeps halo indices >= 0)
-    long long t_acc = 0, t_full = 0, t_w = 0;
+    long long t_acc = 0, t_full = 0, t_w = 0, n_task = 0, n_hit = 0;
     const long long t_start = clock64();
     for (int pair = team; pair < n_pairs; pair += n_teams) {
       const int nab = min(K, p.n_clips - K * pair);
@@ -277,6 +278,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
             const int j0 = sg.j0, n_out = sg.n_out, jin0 = sg.jin0, n_in = sg.n_in;
             const int jend = j0 + n_out - 1;
             int gc = gseg + (jin0 - j0);          // ring index of the output column aligned with the input column
+            bool pre = false;                     // this task's barriers were already seen complete by the look-ahead
             for (int t = 0; t < n_in; ++t, ++gc) {
               const int jc = jin0 + t;
               const bool lo_in = jc > j0, c_in = (jc >= j0) && (jc <= jend), hi_in = jc < jend;
@@ -287,7 +289,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
               const bool wrap = sf + n > NSLOT;
               const int n1 = wrap ? static_cast<int>(NSLOT - sf) : n;
               // first-touched outputs need their ring slot drained by the epilogue: block 2, and at t == 0 block 1 too
-              if (p.mode != 1) {
+              if (p.mode != 1 && !pre) {
                 const long long tw0 = p.dbg ? clock64() : 0;
                 if (t == 0 && c_in) {
                   const uint32_t g1 = static_cast<uint32_t>(gc);
@@ -327,14 +329,52 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
                 }
                 if (!wrap) {
 #pragma unroll
-                  for (int i = 1; i < NMMA; ++i) {
+                  for (int i = 1; i < NSPLIT; ++i) {
                     const int kh = i / NKC, kc = i - kh * NKC;
                     mma_f16_ss(d1, a_hi | static_cast<uint64_t>(a_lo + kc * pr2 + kh * d),
                                b_hi | static_cast<uint64_t>(b_f + i * BT16), id1, 1);
                   }
                 } else {
 #pragma unroll
-                  for (int i = 1; i < NMMA; ++i) {
+                  for (int i = 1; i < NSPLIT; ++i) {
+                    const int kh = i / NKC, kc = i - kh * NKC;
+                    const uint64_t ad = a_hi | static_cast<uint64_t>(a_lo + kc * pr2 + kh * d);
+                    const uint64_t bd = b_hi | static_cast<uint64_t>(b_f + i * BT16);
+                    mma_f16_ss(d1, ad, bd, id1, 1);
+                    mma_f16_ss(tmem, ad, bd + static_cast<uint64_t>(n1 * NB), id2, 1);
+                  }
+                }
+              }
+              __syncwarp();
+              // Look one task ahead while the queued MMAs drain: probe (never block on) the barriers the next
+              // task of this segment needs, so that its issue can start without a serialized poll.
+              pre = false;
+              if (p.mode != 1 && t + 1 < n_in) {
+                const uint32_t st1 = (st + 1 == T2_NSTAGE) ? 0 : st + 1;
+                const uint32_t par1 = (st + 1 == T2_NSTAGE) ? stpar ^ 1 : stpar;
+                bool ok = mbar_test_wait(a_full + 8 * st1, par1);
+                if (jc + 1 < jend) {                                    // next task first-touches block gc + 2
+                  const uint32_t g2 = static_cast<uint32_t>(gc + 2);
+                  ok = mbar_test_wait(a_acc_empty + 8 * (g2 % NSLOT), ((g2 / NSLOT) & 1) ^ 1) && ok;
+                }
+                pre = ok;
+                if (p.dbg) { n_task += 1; n_hit += ok; }
+              }
+              if (elect_one()) {
+                const uint32_t a_lo = a_lbo | (stages16 + st * stage16);
+                const uint32_t b_f = b_lo0 + first_blk * NB;
+                const uint32_t d1 = tmem + sf * NB;
+                const uint32_t id1 = IDESC0 + n1 * IDESC_BLK, id2 = IDESC0 + (n - n1) * IDESC_BLK;
+                if (!wrap) {
+#pragma unroll
+                  for (int i = NSPLIT; i < NMMA; ++i) {
+                    const int kh = i / NKC, kc = i - kh * NKC;
+                    mma_f16_ss(d1, a_hi | static_cast<uint64_t>(a_lo + kc * pr2 + kh * d),
+                               b_hi | static_cast<uint64_t>(b_f + i * BT16), id1, 1);
+                  }
+                } else {
+#pragma unroll
+                  for (int i = NSPLIT; i < NMMA; ++i) {
                     const int kh = i / NKC, kc = i - kh * NKC;
                     const uint64_t ad = a_hi | static_cast<uint64_t>(a_lo + kc * pr2 + kh * d);
                     const uint64_t bd = b_hi | static_cast<uint64_t>(b_f + i * BT16);
@@ -361,7 +401,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
       __syncwarp();
       mbar_wait((a_full + 8 * (0)), 0);
     }
-    if (p.dbg && lane == 0) { long long* o = p.dbg + blockIdx.x * 8; o[3] = clock64() - t_start; o[4] = t_acc; o[5] = t_full; o[6] = t_w; }
+    if (p.dbg && lane == 0) { long long* o = p.dbg + blockIdx.x * 16; o[3] = clock64() - t_start; o[4] = t_acc; o[5] = t_full; o[6] = t_w; o[11] = n_hit; o[12] = n_task; }
   } else if (warp < 10 && p.mode != 1) {
     // ======================================= epilogue =======================================
     const int ew = warp - 2, quad = warp & 3, half = ew >> 2;
@@ -370,15 +410,17 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
     const int etid = ew * 32 + lane;
     uint32_t g = 0, ev = 0;
     int piter = 0;
-    long long t_wait = 0;
+    long long t_wait = 0, t_c0 = 0, t_qflag = 0;
+    const long long t_start_e = clock64();
     for (int pair = team; pair < n_pairs; pair += n_teams, ++piter) {
+      const long long tc0 = p.dbg ? clock64() : 0;
       const int nab = min(K, p.n_clips - K * pair);
       const long long qoff = 0;
       // ---- layer 0: conv0 1->C 3x3 pad 1 + ReLU in FP32 (model.py:107-111); z0 = x0 -> Q ----
       for (int ab = 0; ab < nab; ++ab) {
         const int clip = K * pair + ab, slot = K * team + ab;
         // the slot's Q buffer is still read by the team's last-layer MMAs of the previous group's clip
-        if (etid == 0 && piter > 0) wait_flag(p.flags + (clip - K * n_teams), T2_G * (p.n_layers + 1));
+        if (etid == 0 && piter > 0) T2_TIMED(t_qflag, wait_flag(p.flags + (clip - K * n_teams), T2_G * (p.n_layers + 1)));
         epi_bar();
         const float* src = p.mfcc + static_cast<long long>(clip) * p.H * p.W;
         for (int i = etid; i < (p.H + 2) * XS; i += T2_EPI_THREADS) {
@@ -415,6 +457,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
         if (lane == 0) mbar_arrive(a_done + 8 * (ev & 3));       // the signaller warp publishes the team flag
         ++ev;
       }
+      if (p.dbg) t_c0 += clock64() - tc0;
       // ---- layers 1..n: the two groups of 4 warps take alternate output columns (all NB channels each).
       // Stored activations are the raw x_L = relu(conv) [+ x_{L-2}]; BatchNorm lives in the next layer's weights
       // (scale) and in its two constant-one input channels (mean shift, exact at the zero-padded borders).
@@ -508,7 +551,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
         }
       }
     }
-    if (p.dbg && etid == 0) p.dbg[blockIdx.x * 8 + 7] = t_wait;
+    if (p.dbg && etid == 0) { long long* o = p.dbg + blockIdx.x * 16; o[7] = t_wait; o[8] = clock64() - t_start_e; o[9] = t_c0; o[10] = t_qflag; }
   } else if (warp == 10 && p.mode != 1) {
     // ======================================= flag signaller =================================
     // Publishes "all stores of this CTA for (clip, layer) are visible" to the team: waits until the eight
@@ -786,8 +829,8 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
   static long long* s_dbg = nullptr;
   const char* dbg_env = getenv("HONK_TC2_DEBUG");
   if (dbg_env && atoi(dbg_env)) {
-    if (!s_dbg) HONK_CUDA(cudaMalloc(&s_dbg, 160 * 8 * sizeof(long long)));
-    HONK_CUDA(cudaMemsetAsync(s_dbg, 0, 160 * 8 * sizeof(long long), s));
+    if (!s_dbg) HONK_CUDA(cudaMalloc(&s_dbg, 160 * 16 * sizeof(long long)));
+    HONK_CUDA(cudaMemsetAsync(s_dbg, 0, 160 * 16 * sizeof(long long), s));
     a.dbg = s_dbg;
   }
   {
@@ -797,16 +840,16 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
     HONK_LAUNCH_CHECK();
   }
   if (a.dbg) {
-    std::vector<long long> h(160 * 8);
+    std::vector<long long> h(160 * 16);
     HONK_CUDA(cudaStreamSynchronize(s));
     HONK_CUDA(cudaMemcpy(h.data(), a.dbg, h.size() * sizeof(long long), cudaMemcpyDeviceToHost));
-    double m[8] = {0};
+    double m[16] = {0};
     const int nb = teams * T2_G;
     for (int b = 0; b < nb; ++b)
-      for (int k = 0; k < 8; ++k) m[k] += static_cast<double>(h[b * 8 + k]) / nb;
+      for (int k = 0; k < 16; ++k) m[k] += static_cast<double>(h[b * 16 + k]) / nb;
     fprintf(stderr, "tc2 dbg (mean cycles/CTA, %d CTAs, %lld clips): producer total %.0f flag-wait %.0f stage-empty-wait %.0f | "
-            "mma total %.0f acc-empty-wait %.0f stage-full-wait %.0f weight-wait %.0f | epilogue acc-full-wait %.0f\n",
-            nb, static_cast<long long>(n_clips), m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[7]);
+            "mma total %.0f acc-empty-wait %.0f stage-full-wait %.0f weight-wait %.0f | epilogue total %.0f acc-full-wait %.0f conv0 %.0f (q-flag wait %.0f) | lookahead hits %.0f of %.0f tasks\n",
+            nb, static_cast<long long>(n_clips), m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[8], m[7], m[9], m[10], m[11], m[12]);
   }
   {
     ProfSpan span("res_tail", s);

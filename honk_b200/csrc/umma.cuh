@@ -89,6 +89,16 @@ __device__ __forceinline__ uint32_t mbar_try_wait(uint32_t mbar, uint32_t parity
                : "memory");
   return ok;
 }
+// Non-blocking probe of a phase (mbarrier.test_wait never suspends): used to look one task ahead.
+__device__ __forceinline__ bool mbar_test_wait(uint32_t mbar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n.reg .pred p;\nmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+      : "=r"(ok)
+      : "r"(mbar), "r"(parity)
+      : "memory");
+  return ok;
+}
 // Bounded wait: a protocol bug (e.g. a TMA byte count that never arrives) traps instead of
 // hanging the GPU.  try_wait suspends in hardware, so the poll count stays small in normal runs.
 __device__ __forceinline__ void mbar_wait(uint32_t mbar, uint32_t parity) {

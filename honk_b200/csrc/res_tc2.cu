@@ -1,5 +1,5 @@
 // Persistent multi-layer tcgen05 kernel for the un-pooled res* models (res15, res15-narrow):
-// every dilated 3x3 C->C layer of SpeechResModel.forward (utils/model.py:104-121) plus conv0 in
+// conv0 and every dilated 3x3 C->C layer of SpeechResModel.forward (utils/model.py:104-121) in
 // ONE launch, with the activations of the clips in flight kept L2-resident.
 //
 // GEMM formulation ("ring accumulate").  One task = one INPUT column (MFCC-coefficient index w)
@@ -9,9 +9,17 @@
 // Input column c contributes its kw block to OUTPUT column c - (kw-1)*d.  Columns of one residue
 // class mod d form a chain; along a chain the three N blocks of input j land on outputs j-1, j,
 // j+1, which sit in ADJACENT 48-column blocks of a TMEM ring, so the 3-way shifted add happens
-// inside the tensor core accumulator (no cross-lane traffic, no extra TMEM reads).  Time taps kh
-// are start-address offsets of the A operand (rows of the staged column), time dilation = kh*d
-// rows, zero padding = physically zero rows between the channel planes in HBM.
+// inside the tensor core accumulator (no cross-lane traffic, no extra TMEM reads).  Every MMA
+// accumulates: the epilogue hands a ring slot back zeroed (tcgen05.st), so no task needs a
+// separate overwrite MMA for its first-touched block.  Time taps kh are start-address offsets of
+// the A operand (rows of the staged column), time dilation = kh*d rows, zero padding = physically
+// zero rows between the channel planes in memory.
+//
+// conv0 (1 -> C channels, model.py:107-111) runs on the tensor cores too, as layer 0 with K = 16:
+// the MFCC value x is split into f16 hi + lo and fed as input channels (hi, lo, hi) against weight
+// rows (w_hi, w_hi, w_lo), i.e. x*w to ~2^-21 relative with FP32 accumulation.  A small pre-pass
+// writes that 16-byte-per-position image (tc2_pack_x0_kernel); the second 8-channel K half of the
+// MMA reads whatever finite f16 data sits one plane further in the stage and meets zero weights.
 //
 // BatchNorm (affine=False, after the residual add, model.py:112-118) is folded exactly.  The stored
 // activation is the raw x_i = relu(conv_i) [+ x_{i-2}] (so the residual stream needs no extra
@@ -26,8 +34,8 @@
 // done" flag (a release counter in global memory) is hidden behind the other clips' work.  Each
 // CTA owns whole chains (or chain segments with one halo input column per cut).  Roles: warp 0 =
 // bulk-copy (TMA) producer, warp 1 = MMA issuer, warps 2-9 = epilogue (TMEM -> ReLU + residual ->
-// f16 -> L2; two groups of 4 warps take alternate columns) and conv0, warp 10 = flag signaller.
-// Working set: 37 teams x 3 clips x 2 buffers x 449 KB = 100 MB, L2-resident.
+// f16 -> L2; two groups of 4 warps take alternate columns), warp 10 = flag signaller.
+// Working set: 37 teams x 3 clips x 2 buffers x 449 KB = 100 MB.
 #include "res_tc.cuh"
 #include "umma.cuh"
 
@@ -45,11 +53,11 @@ using namespace umma;
 
 constexpr int T2_G = 4;           // CTAs per team
 constexpr int T2_NSTAGE = 8;      // A-operand stages (one input column each)
-constexpr int T2_THREADS = 352;    // warp 0 producer, 1 MMA, 2-9 epilogue, 10 flag signaller
+constexpr int T2_THREADS = 352;   // warp 0 producer, 1 MMA, 2-9 epilogue, 10 flag signaller
 constexpr int T2_PAD = 16;        // zero rows above every channel plane (>= max dilation)
 constexpr int T2_MAXSEG = 8;
-constexpr int T2_MAXL = 24;       // layers (res26)
-constexpr int T2_EPI_THREADS = 256;
+constexpr int T2_MAXL = 24;       // C->C layers (res26)
+constexpr int T2_NDBG = 16;       // debug counters per CTA
 
 struct T2Seg {                    // a run of output columns of one chain, owned by one CTA
   short r;                        // residue class (first column of the chain)
@@ -60,33 +68,32 @@ struct T2Seg {                    // a run of output columns of one chain, owned
 
 struct T2Layer {
   int d;                          // dilation
-  int flags;                      // bit0: add residual, bit1: last layer (pool, no store)
+  int flags;                      // bit0: add residual, bit1: last layer (pool, no store), bit2: conv0 (input = x0 image)
   int w_off;                      // byte offset of this layer's packed weights
-  int reserved;
+  int w_bytes;                    // 3 * nkc B tiles
   int n_seg[T2_G];
   T2Seg seg[T2_G][T2_MAXSEG];
 };
 
 struct T2Params {
   const unsigned char* wpack;
-  const float* mfcc;              // [n_clips][H][W] float32
-  const float* w0;                // conv0 weights [9][NB]
+  const unsigned char* x0;        // [n_clips][W][H+2][8] f16: (hi, lo, hi, 0...) of the MFCCs, zero first/last row
   unsigned char* P;               // [n_slots] activation buffers
-  unsigned char* Q;               // [2][n_slots]
+  unsigned char* Q;               // [n_slots]
   float* pool;                    // [n_clips][NB]
   unsigned int* flags;            // [n_clips] team-wide layer counters
   long long slot_stride;          // bytes per clip buffer
-  int n_layers, n_clips, n_slots;
+  long long x0_clip_stride;
+  int n_layers, n_clips, n_slots; // n_layers counts the C->C layers; layers[0] is conv0
   int K;                          // clips per team in flight
   int H, W;
   int plane_rows;                 // H + T2_PAD
   int col_bytes;                  // NCG * plane_rows * 16
-  int stage_stride, wbytes;
-  int mode;                       // debug: 1 = MMA issue only (no loads, no waits, no epilogue; results are garbage)
-  long long* dbg;                 // optional [gridDim][8] cycle counters (HONK_TC2_DEBUG)
+  int stage_stride, wbytes;       // wbytes = size of one weight buffer (largest layer)
+  long long* dbg;                 // optional [gridDim][T2_NDBG] cycle counters (HONK_TC2_DEBUG)
   // Per-layer tables live in the kernel parameter (constant) bank so that the MMA warp's descriptor
   // arithmetic stays on the uniform datapath (no R2UR per tcgen05.mma operand).
-  T2Layer layers[T2_MAXL];
+  T2Layer layers[T2_MAXL + 1];
 };
 
 namespace {
@@ -96,17 +103,18 @@ __device__ __forceinline__ uint32_t elect_one() {
   asm volatile("{\n\t.reg .pred px;\n\telect.sync _|px, 0xFFFFFFFF;\n\t@px mov.s32 %0, 1;\n\t}" : "+r"(pred));
   return pred;
 }
+// Hides how a value was computed: the compiler keeps it in a register instead of rematerialising
+// the shared-window address arithmetic (S2UR CgaCtaId + shifts) at every barrier operation.
+__device__ __forceinline__ uint32_t keep(uint32_t x) {
+  asm volatile("mov.b32 %0, %0;" : "+r"(x));
+  return x;
+}
 __device__ __forceinline__ void bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t mbar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
                "l"(src), "r"(bytes), "r"(mbar)
                : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
-__device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
-  unsigned int v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
 __device__ __forceinline__ void red_release_gpu_add(unsigned int* p, unsigned int v) {
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -135,22 +143,42 @@ __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
   asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
   return r;
 }
-#define T2_TIMED(acc, stmt) do { if (p.mode == 1) break; if (p.dbg) { const long long t__ = clock64(); stmt; acc += clock64() - t__; } else { stmt; } } while (0)
 // relu(y) + r on packed halves (r = 0 when the layer has no residual)
 __device__ __forceinline__ uint32_t relu_add_h2(uint32_t y, uint32_t r) {
   uint32_t o;
   asm("{\n\t.reg .b32 t;\n\tmax.f16x2 t, %1, %3;\n\tadd.rn.f16x2 %0, t, %2;\n\t}" : "=r"(o) : "r"(y), "r"(r), "r"(0u));
   return o;
 }
-__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+// 32 lanes x 16 columns of zeros (hands an accumulator slot back cleared)
+__device__ __forceinline__ void tmem_zero16(uint32_t taddr) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1};" ::"r"(taddr), "r"(0u)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
-template <int NCG>
+#define T2_TIMED(acc, stmt) do { if (DBG) { const long long t__ = clock64(); stmt; acc += clock64() - t__; } else { stmt; } } while (0)
+
+// MMAs [I0, I1) of one task: index i = kh * NK + kc reads the A rows shifted by kh*d and the 16-channel chunk kc, against B
+// tile i.  WRAP: the task's N blocks straddle the end of the TMEM ring and every MMA is issued in two parts.
+template <int I0, int I1, int NK, int NB, bool WRAP>
+__device__ __forceinline__ void issue_mmas(uint64_t a_hi, uint32_t a_lo, uint32_t pr2, uint32_t d, uint64_t b_hi, uint32_t b_f,
+                                           uint32_t d1, uint32_t id1, uint32_t d2, uint32_t id2, uint32_t b2) {
+#pragma unroll
+  for (int i = I0; i < I1; ++i) {
+    const int kh = i / NK, kc = i - kh * NK;
+    const uint64_t ad = a_hi | static_cast<uint64_t>(a_lo + kc * pr2 + kh * d);
+    const uint64_t bd = b_hi | static_cast<uint64_t>(b_f + i * 6 * NB);
+    mma_f16_ss(d1, ad, bd, id1, 1);
+    if (WRAP) mma_f16_ss(d2, ad, bd + static_cast<uint64_t>(b2), id2, 1);
+  }
+}
+
+template <int NCG, bool DBG>
 __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_constant__ T2Params p) {
   constexpr int NB = NCG * 8;            // padded channels = N block
   constexpr int NKC = NCG / 2;           // K chunks of 16 channels
   constexpr int NSLOT = 512 / NB;        // TMEM ring of output-column accumulators
-  constexpr int HALF = NB / 2;           // columns per epilogue warp
-  constexpr int BT16 = 6 * NB;           // one (kh,kc) B tile in 16-byte units: 2 K-halves x 3NB rows
   constexpr int NMMA = 3 * NKC;          // MMAs per input column
   constexpr int NSPLIT = NMMA / 2 + 1;   // MMAs issued before the look-ahead probe of the next task
 
@@ -163,78 +191,91 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
 
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);      // provably warp-uniform: keeps role code on the uniform datapath
-  const uint32_t a_full = smem_u32(&bar_full[0]), a_empty = smem_u32(&bar_empty[0]);
-  const uint32_t a_acc_full = smem_u32(&bar_acc_full[0]), a_acc_empty = smem_u32(&bar_acc_empty[0]);
-  const uint32_t a_wfull = smem_u32(&bar_wfull[0]), a_wfree = smem_u32(&bar_wfree[0]);
-  const uint32_t a_done = smem_u32(&bar_done[0]);
+  const uint32_t a_full = keep(smem_u32(&bar_full[0])), a_empty = keep(smem_u32(&bar_empty[0]));
+  const uint32_t a_acc_full = keep(smem_u32(&bar_acc_full[0])), a_acc_empty = keep(smem_u32(&bar_acc_empty[0]));
+  const uint32_t a_wfull = keep(smem_u32(&bar_wfull[0])), a_wfree = keep(smem_u32(&bar_wfree[0]));
+  const uint32_t a_done = keep(smem_u32(&bar_done[0]));
   const int team = blockIdx.x / T2_G, rank = blockIdx.x % T2_G, n_teams = gridDim.x / T2_G;
   unsigned char* stages = smem;
   unsigned char* wbuf = smem + T2_NSTAGE * p.stage_stride;
-  float* xs = reinterpret_cast<float*>(wbuf + 2 * p.wbytes);          // conv0 input tile [(H+2)][XS]
-  const int XS = p.W + 3;
-  float* w0s = xs + (((p.H + 2) * XS + 3) & ~3);                      // [9][NB], 16-byte aligned
 
   if (warp == 1) tmem_alloc(smem_u32(&tmem_base_s), 512);
   if (tid == 0) {
     for (int s = 0; s < T2_NSTAGE; ++s) {
-      mbar_init((a_full + 8 * (s)), 1);
-      mbar_init((a_empty + 8 * (s)), 1);
+      mbar_init(a_full + 8 * s, 1);
+      mbar_init(a_empty + 8 * s, 1);
     }
     for (int k = 0; k < NSLOT; ++k) {
-      mbar_init((a_acc_full + 8 * (k)), 1);
-      mbar_init((a_acc_empty + 8 * (k)), 4);
+      mbar_init(a_acc_full + 8 * k, 1);
+      mbar_init(a_acc_empty + 8 * k, 4);
     }
     for (int k = 0; k < 2; ++k) {
-      mbar_init((a_wfull + 8 * (k)), 1);
-      mbar_init((a_wfree + 8 * (k)), 1);
+      mbar_init(a_wfull + 8 * k, 1);
+      mbar_init(a_wfree + 8 * k, 1);
     }
     for (int k = 0; k < 4; ++k) mbar_init(a_done + 8 * k, 8);
     fence_mbar_init();
   }
-  for (int i = tid; i < 9 * NB; i += T2_THREADS) w0s[i] = __ldg(p.w0 + i);
+  // conv0's second K half reads stage bytes no copy of that layer wrote: they must be finite f16 from the start
+  for (int i = tid * 16; i < T2_NSTAGE * p.stage_stride; i += T2_THREADS * 16) *reinterpret_cast<uint4*>(stages + i) = make_uint4(0, 0, 0, 0);
+  fence_async_smem();
   fence_before();
   __syncthreads();
   fence_after();
   const uint32_t tmem = tmem_base_s;
+  if (warp >= 2 && warp < 6) {                        // accumulators start from zero: every MMA accumulates
+    for (int c = 0; c < 512 / 16; ++c) tmem_zero16(tmem + (static_cast<uint32_t>((warp & 3) * 32) << 16) + c * 16);
+    tmem_st_wait();
+  }
+  fence_before();
+  __syncthreads();
+  fence_after();
   const int K = p.K;                                  // clips a team runs in lockstep (layer-interleaved)
   const int n_pairs = (p.n_clips + K - 1) / K;        // clip groups
   const int plane_bytes = p.plane_rows * 16;
+  const int x0_col_bytes = (p.H + 2) * 16;
 
   if (warp == 0) {
     // ======================================= producer =======================================
-    if (lane == 0 && p.mode != 1) {
+    if (lane == 0) {
       uint32_t it = 0, q = 0;
       int piter = 0;
       long long t_flag = 0, t_empty = 0;
       const long long t_start = clock64();
       for (int pair = team; pair < n_pairs; pair += n_teams, ++piter) {
         const int nab = min(K, p.n_clips - K * pair);
-        for (int L = 1; L <= p.n_layers; ++L, ++q) {
-          const T2Layer& ly = p.layers[L - 1];
+        for (int L = 0; L <= p.n_layers; ++L, ++q) {
+          const T2Layer& ly = p.layers[L];
           if (q == 0) {
-            mbar_expect_tx((a_wfull + 8 * (0)), p.wbytes);
-            bulk_load(smem_u32(wbuf), p.wpack + ly.w_off, p.wbytes, (a_wfull + 8 * (0)));
+            mbar_expect_tx(a_wfull, ly.w_bytes);
+            bulk_load(smem_u32(wbuf), p.wpack + ly.w_off, ly.w_bytes, a_wfull);
           }
           const int d = ly.d;
-          const uint32_t bytes = (NCG - 1) * plane_bytes + (p.H + 2 * d) * 16;
+          const bool from_x0 = ly.flags & 4;
+          const uint32_t bytes = from_x0 ? x0_col_bytes : (NCG - 1) * plane_bytes + (p.H + 2 * d) * 16;
+          const long long colb = from_x0 ? x0_col_bytes : p.col_bytes;
           const int nseg = ly.n_seg[rank];
           for (int ab = 0; ab < nab; ++ab) {
             const int clip = K * pair + ab, slot = K * team + ab;
-            const unsigned char* in = (L & 1) ? p.Q + static_cast<long long>(slot) * p.slot_stride
-                                              : p.P + static_cast<long long>(slot) * p.slot_stride;
-            in += (T2_PAD - d) * 16;
-            T2_TIMED(t_flag, wait_flag(p.flags + clip, T2_G * L));          // every CTA of the team finished layer L-1 (conv0 = layer 0)
-            fence_proxy_async_global();
+            const unsigned char* in;
+            if (from_x0) {
+              in = p.x0 + static_cast<long long>(clip) * p.x0_clip_stride;
+              // conv0 writes Q[slot]: the team's last-layer MMAs of the previous clip in this slot still read it
+              if (piter > 0) T2_TIMED(t_flag, wait_flag(p.flags + (clip - K * n_teams), T2_G * (p.n_layers + 1)));
+            } else {
+              in = ((L & 1) ? p.Q : p.P) + static_cast<long long>(slot) * p.slot_stride + (T2_PAD - d) * 16;
+              T2_TIMED(t_flag, wait_flag(p.flags + clip, T2_G * L));        // every CTA of the team finished layer L-1
+              fence_proxy_async_global();
+            }
             for (int s = 0; s < nseg; ++s) {
               const T2Seg& sg = ly.seg[rank][s];
               const int r = sg.r, jin0 = sg.jin0, n_in = sg.n_in;
               for (int t = 0; t < n_in; ++t, ++it) {
                 const int st = it % T2_NSTAGE;
-                T2_TIMED(t_empty, mbar_wait((a_empty + 8 * (st)), ((it / T2_NSTAGE) & 1) ^ 1));
-                const uint32_t full = (a_full + 8 * (st));
+                T2_TIMED(t_empty, mbar_wait(a_empty + 8 * st, ((it / T2_NSTAGE) & 1) ^ 1));
+                const uint32_t full = a_full + 8 * st;
                 mbar_expect_tx(full, bytes);
-                bulk_load(smem_u32(stages + st * p.stage_stride), in + static_cast<long long>(r + (jin0 + t) * d) * p.col_bytes,
-                          bytes, full);
+                bulk_load(smem_u32(stages + st * p.stage_stride), in + (r + (jin0 + t) * d) * colb, bytes, full);
               }
             }
           }
@@ -242,14 +283,14 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
           const bool more = (L < p.n_layers) || (pair + n_teams < n_pairs);
           if (more) {
             const uint32_t qn = q + 1;
-            const T2Layer& nl = p.layers[L < p.n_layers ? L : 0];
-            if (qn >= 2) mbar_wait((a_wfree + 8 * (qn & 1)), ((qn - 2) >> 1) & 1);
-            mbar_expect_tx((a_wfull + 8 * (qn & 1)), p.wbytes);
-            bulk_load(smem_u32(wbuf + (qn & 1) * p.wbytes), p.wpack + nl.w_off, p.wbytes, (a_wfull + 8 * (qn & 1)));
+            const T2Layer& nl = p.layers[L < p.n_layers ? L + 1 : 0];
+            if (qn >= 2) mbar_wait(a_wfree + 8 * (qn & 1), ((qn - 2) >> 1) & 1);
+            mbar_expect_tx(a_wfull + 8 * (qn & 1), nl.w_bytes);
+            bulk_load(smem_u32(wbuf + (qn & 1) * p.wbytes), p.wpack + nl.w_off, nl.w_bytes, a_wfull + 8 * (qn & 1));
           }
         }
       }
-      if (p.dbg) { long long* o = p.dbg + blockIdx.x * 16; o[0] = clock64() - t_start; o[1] = t_flag; o[2] = t_empty; }
+      if (DBG) { long long* o = p.dbg + blockIdx.x * T2_NDBG; o[0] = clock64() - t_start; o[1] = t_flag; o[2] = t_empty; }
     }
   } else if (warp == 1) {
     // ======================================= MMA issuer =====================================
@@ -257,20 +298,23 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
     const uint32_t a_lbo = (static_cast<uint32_t>(p.plane_rows) & 0x3FFF) << 16;
     const uint64_t b_hi = make_desc(0, 3 * NB * 16, 128) & 0xFFFFFFFF00000000ull;
     const uint32_t b_lbo = (static_cast<uint32_t>(3 * NB) & 0x3FFF) << 16;
-    const uint32_t stages16 = smem_u32(stages) >> 4, stage16 = static_cast<uint32_t>(p.stage_stride) >> 4;
+    const uint32_t stage16 = static_cast<uint32_t>(p.stage_stride) >> 4;
+    const uint32_t a_st0 = a_lbo | (smem_u32(stages) >> 4);
     const uint32_t pr2 = 2 * p.plane_rows;
     constexpr uint32_t IDESC0 = make_idesc(128, 0, 0), IDESC_BLK = static_cast<uint32_t>(NB >> 3) << 17;
     uint32_t st = 0, stpar = 0, q = 0;
+    uint32_t a_st = a_st0;                      // low descriptor word of stage st
     int gseg = 2 * NSLOT;                       // ring index of the segment's first output (offset keeps halo indices >= 0)
     long long t_acc = 0, t_full = 0, t_w = 0, n_task = 0, n_hit = 0;
     const long long t_start = clock64();
     for (int pair = team; pair < n_pairs; pair += n_teams) {
       const int nab = min(K, p.n_clips - K * pair);
-      for (int L = 1; L <= p.n_layers; ++L, ++q) {
-        const T2Layer& ly = p.layers[L - 1];
+      for (int L = 0; L <= p.n_layers; ++L, ++q) {
+        const T2Layer& ly = p.layers[L];
         const uint32_t d = ly.d;
+        const bool conv0 = ly.flags & 4;
         const int nseg = ly.n_seg[rank];
-        T2_TIMED(t_w, mbar_wait((a_wfull + 8 * (q & 1)), (q >> 1) & 1));
+        T2_TIMED(t_w, mbar_wait(a_wfull + 8 * (q & 1), (q >> 1) & 1));
         const uint32_t b_lo0 = b_lbo | (smem_u32(wbuf + (q & 1) * p.wbytes) >> 4);
         for (int ab = 0; ab < nab; ++ab) {
           for (int s = 0; s < nseg; ++s) {
@@ -284,72 +328,44 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
               const bool lo_in = jc > j0, c_in = (jc >= j0) && (jc <= jend), hi_in = jc < jend;
               const int first_blk = lo_in ? 0 : (c_in ? 1 : 2), last_blk = hi_in ? 2 : (c_in ? 1 : 0);
               const int n = last_blk - first_blk + 1;
-              const uint32_t gf = static_cast<uint32_t>(gc - 1 + first_blk);
-              const uint32_t sf = gf % NSLOT;
+              const uint32_t sf = static_cast<uint32_t>(gc - 1 + first_blk) % NSLOT;
               const bool wrap = sf + n > NSLOT;
               const int n1 = wrap ? static_cast<int>(NSLOT - sf) : n;
-              // first-touched outputs need their ring slot drained by the epilogue: block 2, and at t == 0 block 1 too
-              if (p.mode != 1 && !pre) {
-                const long long tw0 = p.dbg ? clock64() : 0;
+              // first-touched outputs need their ring slot handed back (read and zeroed) by the epilogue:
+              // block 2, and at t == 0 block 1 too
+              if (!pre) {
+                const long long tw0 = DBG ? clock64() : 0;
                 if (t == 0 && c_in) {
                   const uint32_t g1 = static_cast<uint32_t>(gc);
-                  mbar_wait((a_acc_empty + 8 * (g1 % NSLOT)), ((g1 / NSLOT) & 1) ^ 1);
+                  mbar_wait(a_acc_empty + 8 * (g1 % NSLOT), ((g1 / NSLOT) & 1) ^ 1);
                 }
                 if (hi_in) {
                   const uint32_t g2 = static_cast<uint32_t>(gc + 1);
-                  mbar_wait((a_acc_empty + 8 * (g2 % NSLOT)), ((g2 / NSLOT) & 1) ^ 1);
+                  mbar_wait(a_acc_empty + 8 * (g2 % NSLOT), ((g2 / NSLOT) & 1) ^ 1);
                 }
-                const long long tw1 = p.dbg ? clock64() : 0;
-                mbar_wait((a_full + 8 * (st)), stpar);
-                if (p.dbg) { t_acc += tw1 - tw0; t_full += clock64() - tw1; }
+                const long long tw1 = DBG ? clock64() : 0;
+                mbar_wait(a_full + 8 * st, stpar);
+                if (DBG) { t_acc += tw1 - tw0; t_full += clock64() - tw1; }
               }
               fence_after();
+              const uint32_t b_f = b_lo0 + first_blk * NB;
+              const uint32_t d1 = tmem + sf * NB;
+              const uint32_t id1 = IDESC0 + n1 * IDESC_BLK, id2 = IDESC0 + (n - n1) * IDESC_BLK;
+              const uint32_t b2 = n1 * NB;
               if (elect_one()) {
-                const uint32_t a_lo = a_lbo | (stages16 + st * stage16);
-                const uint32_t b_f = b_lo0 + first_blk * NB;
-                const uint32_t d1 = tmem + sf * NB;
-                const uint32_t id1 = IDESC0 + n1 * IDESC_BLK, id2 = IDESC0 + (n - n1) * IDESC_BLK;
-                {   // i = 0 (kh = 0, kc = 0): first-touched blocks overwrite, the others accumulate
-                  const uint64_t ad = a_hi | a_lo, bd = b_hi | b_f;
-                  if (t == 0 || !hi_in) {
-                    const uint32_t acc0 = (t != 0);
-                    mma_f16_ss(d1, ad, bd, id1, acc0);
-                    if (wrap) mma_f16_ss(tmem, ad, bd + static_cast<uint64_t>(n1 * NB), id2, acc0);
-                  } else {
-                    const int na = 2 - first_blk;                        // accumulating blocks (1 or 2), then block 2 overwrites
-                    if (!wrap || n1 == na) {
-                      mma_f16_ss(d1, ad, bd, IDESC0 + na * IDESC_BLK, 1);
-                      mma_f16_ss(wrap ? tmem : d1 + na * NB, ad, bd + static_cast<uint64_t>(na * NB), IDESC0 + IDESC_BLK, 0);
-                    } else {                                             // ring wraps inside the accumulating part (na == 2, n1 == 1)
-                      mma_f16_ss(d1, ad, bd, IDESC0 + IDESC_BLK, 1);
-                      mma_f16_ss(tmem, ad, bd + static_cast<uint64_t>(NB), IDESC0 + IDESC_BLK, 1);
-                      mma_f16_ss(tmem + NB, ad, bd + static_cast<uint64_t>(2 * NB), IDESC0 + IDESC_BLK, 0);
-                    }
-                  }
-                }
-                if (!wrap) {
-#pragma unroll
-                  for (int i = 1; i < NSPLIT; ++i) {
-                    const int kh = i / NKC, kc = i - kh * NKC;
-                    mma_f16_ss(d1, a_hi | static_cast<uint64_t>(a_lo + kc * pr2 + kh * d),
-                               b_hi | static_cast<uint64_t>(b_f + i * BT16), id1, 1);
-                  }
+                if (conv0) {
+                  if (!wrap) issue_mmas<0, 3, 1, NB, false>(a_hi, a_st, pr2, d, b_hi, b_f, d1, id1, tmem, id2, b2);
+                  else issue_mmas<0, 3, 1, NB, true>(a_hi, a_st, pr2, d, b_hi, b_f, d1, id1, tmem, id2, b2);
                 } else {
-#pragma unroll
-                  for (int i = 1; i < NSPLIT; ++i) {
-                    const int kh = i / NKC, kc = i - kh * NKC;
-                    const uint64_t ad = a_hi | static_cast<uint64_t>(a_lo + kc * pr2 + kh * d);
-                    const uint64_t bd = b_hi | static_cast<uint64_t>(b_f + i * BT16);
-                    mma_f16_ss(d1, ad, bd, id1, 1);
-                    mma_f16_ss(tmem, ad, bd + static_cast<uint64_t>(n1 * NB), id2, 1);
-                  }
+                  if (!wrap) issue_mmas<0, NSPLIT, NKC, NB, false>(a_hi, a_st, pr2, d, b_hi, b_f, d1, id1, tmem, id2, b2);
+                  else issue_mmas<0, NSPLIT, NKC, NB, true>(a_hi, a_st, pr2, d, b_hi, b_f, d1, id1, tmem, id2, b2);
                 }
               }
               __syncwarp();
               // Look one task ahead while the queued MMAs drain: probe (never block on) the barriers the next
               // task of this segment needs, so that its issue can start without a serialized poll.
               pre = false;
-              if (p.mode != 1 && t + 1 < n_in) {
+              if (t + 1 < n_in) {
                 const uint32_t st1 = (st + 1 == T2_NSTAGE) ? 0 : st + 1;
                 const uint32_t par1 = (st + 1 == T2_NSTAGE) ? stpar ^ 1 : stpar;
                 bool ok = mbar_test_wait(a_full + 8 * st1, par1);
@@ -358,120 +374,57 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
                   ok = mbar_test_wait(a_acc_empty + 8 * (g2 % NSLOT), ((g2 / NSLOT) & 1) ^ 1) && ok;
                 }
                 pre = ok;
-                if (p.dbg) { n_task += 1; n_hit += ok; }
+                if (DBG) { n_task += 1; n_hit += ok; }
               }
               if (elect_one()) {
-                const uint32_t a_lo = a_lbo | (stages16 + st * stage16);
-                const uint32_t b_f = b_lo0 + first_blk * NB;
-                const uint32_t d1 = tmem + sf * NB;
-                const uint32_t id1 = IDESC0 + n1 * IDESC_BLK, id2 = IDESC0 + (n - n1) * IDESC_BLK;
-                if (!wrap) {
-#pragma unroll
-                  for (int i = NSPLIT; i < NMMA; ++i) {
-                    const int kh = i / NKC, kc = i - kh * NKC;
-                    mma_f16_ss(d1, a_hi | static_cast<uint64_t>(a_lo + kc * pr2 + kh * d),
-                               b_hi | static_cast<uint64_t>(b_f + i * BT16), id1, 1);
-                  }
-                } else {
-#pragma unroll
-                  for (int i = NSPLIT; i < NMMA; ++i) {
-                    const int kh = i / NKC, kc = i - kh * NKC;
-                    const uint64_t ad = a_hi | static_cast<uint64_t>(a_lo + kc * pr2 + kh * d);
-                    const uint64_t bd = b_hi | static_cast<uint64_t>(b_f + i * BT16);
-                    mma_f16_ss(d1, ad, bd, id1, 1);
-                    mma_f16_ss(tmem, ad, bd + static_cast<uint64_t>(n1 * NB), id2, 1);
-                  }
+                if (!conv0) {
+                  if (!wrap) issue_mmas<NSPLIT, NMMA, NKC, NB, false>(a_hi, a_st, pr2, d, b_hi, b_f, d1, id1, tmem, id2, b2);
+                  else issue_mmas<NSPLIT, NMMA, NKC, NB, true>(a_hi, a_st, pr2, d, b_hi, b_f, d1, id1, tmem, id2, b2);
                 }
-                commit((a_empty + 8 * (st)));
-                if (lo_in) commit((a_acc_full + 8 * (static_cast<uint32_t>(gc - 1) % NSLOT)));
-                if (t == n_in - 1 && c_in) commit((a_acc_full + 8 * (static_cast<uint32_t>(gc) % NSLOT)));
+                commit(a_empty + 8 * st);
+                if (lo_in) commit(a_acc_full + 8 * (static_cast<uint32_t>(gc - 1) % NSLOT));
+                if (t == n_in - 1 && c_in) commit(a_acc_full + 8 * (static_cast<uint32_t>(gc) % NSLOT));
               }
               __syncwarp();
-              if (++st == T2_NSTAGE) { st = 0; stpar ^= 1; }
+              a_st += stage16;
+              if (++st == T2_NSTAGE) { st = 0; stpar ^= 1; a_st = a_st0; }
             }
             gseg += n_out;
           }
         }
-        if (elect_one()) commit((a_wfree + 8 * (q & 1)));
+        if (elect_one()) commit(a_wfree + 8 * (q & 1));
         __syncwarp();
       }
     }
-    if (p.mode == 1) {
-      if (elect_one()) commit((a_full + 8 * (0)));
-      __syncwarp();
-      mbar_wait((a_full + 8 * (0)), 0);
+    if (DBG && lane == 0) {
+      long long* o = p.dbg + blockIdx.x * T2_NDBG;
+      o[3] = clock64() - t_start; o[4] = t_acc; o[5] = t_full; o[6] = t_w; o[11] = n_hit; o[12] = n_task;
     }
-    if (p.dbg && lane == 0) { long long* o = p.dbg + blockIdx.x * 16; o[3] = clock64() - t_start; o[4] = t_acc; o[5] = t_full; o[6] = t_w; o[11] = n_hit; o[12] = n_task; }
-  } else if (warp < 10 && p.mode != 1) {
+  } else if (warp < 10) {
     // ======================================= epilogue =======================================
+    // The two groups of 4 warps take alternate output columns (all NB channels each).  Stored activations
+    // are the raw x_L = relu(conv) [+ x_{L-2}]; BatchNorm lives in the next layer's weights (scale) and in
+    // its two constant-one input channels (mean shift, exact at the zero-padded borders).
     const int ew = warp - 2, quad = warp & 3, half = ew >> 2;
     const int h = quad * 32 + lane;
     const bool valid = h < p.H;
     const int etid = ew * 32 + lane;
     uint32_t g = 0, ev = 0;
-    int piter = 0;
-    long long t_wait = 0, t_c0 = 0, t_qflag = 0;
+    long long t_wait = 0;
     const long long t_start_e = clock64();
-    for (int pair = team; pair < n_pairs; pair += n_teams, ++piter) {
-      const long long tc0 = p.dbg ? clock64() : 0;
+    for (int pair = team; pair < n_pairs; pair += n_teams) {
       const int nab = min(K, p.n_clips - K * pair);
-      const long long qoff = 0;
-      // ---- layer 0: conv0 1->C 3x3 pad 1 + ReLU in FP32 (model.py:107-111); z0 = x0 -> Q ----
-      for (int ab = 0; ab < nab; ++ab) {
-        const int clip = K * pair + ab, slot = K * team + ab;
-        // the slot's Q buffer is still read by the team's last-layer MMAs of the previous group's clip
-        if (etid == 0 && piter > 0) T2_TIMED(t_qflag, wait_flag(p.flags + (clip - K * n_teams), T2_G * (p.n_layers + 1)));
-        epi_bar();
-        const float* src = p.mfcc + static_cast<long long>(clip) * p.H * p.W;
-        for (int i = etid; i < (p.H + 2) * XS; i += T2_EPI_THREADS) {
-          const int y = i / XS - 1, x = i % XS - 1;
-          xs[i] = (y >= 0 && y < p.H && x >= 0 && x < p.W) ? __ldg(src + y * p.W + x) : 0.f;
-        }
-        epi_bar();
-        const int c0 = rank * p.W / T2_G, c1 = (rank + 1) * p.W / T2_G;
-        unsigned char* dst = p.Q + (qoff + slot) * p.slot_stride;
-        if (valid) {
-          for (int w = c0; w < c1; ++w) {
-            float a[HALF];
-#pragma unroll
-            for (int k = 0; k < HALF; ++k) a[k] = 0.f;
-#pragma unroll
-            for (int tap = 0; tap < 9; ++tap) {
-              const float v = xs[(h + tap / 3) * XS + w + tap % 3];
-#pragma unroll
-              for (int k = 0; k < HALF; ++k) a[k] = fmaf(v, w0s[tap * NB + half * HALF + k], a[k]);
-            }
-#pragma unroll
-            for (int c = 0; c < HALF / 8; ++c) {
-              uint4 o;
-              o.x = pack_h2(fmaxf(a[c * 8 + 0], 0.f), fmaxf(a[c * 8 + 1], 0.f));
-              o.y = pack_h2(fmaxf(a[c * 8 + 2], 0.f), fmaxf(a[c * 8 + 3], 0.f));
-              o.z = pack_h2(fmaxf(a[c * 8 + 4], 0.f), fmaxf(a[c * 8 + 5], 0.f));
-              o.w = pack_h2(fmaxf(a[c * 8 + 6], 0.f), fmaxf(a[c * 8 + 7], 0.f));
-              if (half == 1 && c == HALF / 8 - 1) o.w = 0x3C003C00u;   // constant-one channels NB-2, NB-1
-              stcg16(dst + static_cast<long long>(w) * p.col_bytes + (half * (HALF / 8) + c) * plane_bytes + (T2_PAD + h) * 16, o);
-            }
-          }
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(a_done + 8 * (ev & 3));       // the signaller warp publishes the team flag
-        ++ev;
-      }
-      if (p.dbg) t_c0 += clock64() - tc0;
-      // ---- layers 1..n: the two groups of 4 warps take alternate output columns (all NB channels each).
-      // Stored activations are the raw x_L = relu(conv) [+ x_{L-2}]; BatchNorm lives in the next layer's weights
-      // (scale) and in its two constant-one input channels (mean shift, exact at the zero-padded borders).
-      for (int L = 1; L <= p.n_layers; ++L) {
-        const T2Layer& ly = p.layers[L - 1];
+      for (int L = 0; L <= p.n_layers; ++L) {
+        const T2Layer& ly = p.layers[L];
         const int d = ly.d, flags = ly.flags;
         const bool add_res = flags & 1, last = flags & 2;
         const int nseg = ly.n_seg[rank];
         const long long cstep = 2ll * d * p.col_bytes;        // this group's next column of a segment
         for (int ab = 0; ab < nab; ++ab) {
           const int clip = K * pair + ab, slot = K * team + ab;
-          unsigned char* Qs = p.Q + (qoff + slot) * p.slot_stride + (T2_PAD + h) * 16;
+          unsigned char* Qs = p.Q + static_cast<long long>(slot) * p.slot_stride + (T2_PAD + h) * 16;
           unsigned char* Ps = p.P + static_cast<long long>(slot) * p.slot_stride + (T2_PAD + h) * 16;
-          unsigned char* outb = (L & 1) ? Ps : Qs;            // odd: Q -> P ; even: P (+Q residual) -> Q in place
+          unsigned char* outb = (L & 1) ? Ps : Qs;            // conv0 -> Q; odd: Q -> P; even: P (+Q residual) -> Q in place
           const bool ld_res = add_res && valid;
           float psum[NB];
           if (last) {
@@ -508,9 +461,8 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
 #pragma unroll
               for (int c = 0; c < NB / 16; ++c) tmem_ld16(taddr + c * 16, *reinterpret_cast<uint32_t(*)[16]>(&v[c * 16]));
               tmem_ld_wait();
-              fence_before();
-              __syncwarp();
-              if (lane == 0) mbar_arrive(a_acc_empty + 8 * sl);
+#pragma unroll
+              for (int c = 0; c < NB / 16; ++c) tmem_zero16(taddr + c * 16);   // the slot goes back cleared (completes below)
               if (!last) {
 #pragma unroll
                 for (int c = 0; c < NCG; ++c) {
@@ -534,6 +486,10 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
                   }
                 }
               }
+              tmem_st_wait();
+              fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(a_acc_empty + 8 * sl);
             }
           }
           if (last) {
@@ -551,8 +507,8 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
         }
       }
     }
-    if (p.dbg && etid == 0) { long long* o = p.dbg + blockIdx.x * 16; o[7] = t_wait; o[8] = clock64() - t_start_e; o[9] = t_c0; o[10] = t_qflag; }
-  } else if (warp == 10 && p.mode != 1) {
+    if (DBG && etid == 0) { long long* o = p.dbg + blockIdx.x * T2_NDBG; o[7] = t_wait; o[8] = clock64() - t_start_e; }
+  } else if (warp == 10) {
     // ======================================= flag signaller =================================
     // Publishes "all stores of this CTA for (clip, layer) are visible" to the team: waits until the eight
     // epilogue warps have arrived, then a gpu-scope fence (cumulative over the stores observed through the
@@ -577,6 +533,29 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
   if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
+// MFCC [n_clips][H][W] float32 -> conv0's A operand [n_clips][W][H+2][8] f16 = (hi, lo, hi, 0, 0, 0, 0, 0) with a
+// zero row above and below (the time padding of conv0).  hi + lo carries 22 significant bits of the MFCC.
+__global__ void __launch_bounds__(256) tc2_pack_x0_kernel(const float* __restrict__ mfcc, unsigned char* __restrict__ x0, int H, int W) {
+  extern __shared__ float tile[];                      // [H][W + 1]
+  const float* src = mfcc + static_cast<long long>(blockIdx.x) * H * W;
+  for (int i = threadIdx.x; i < H * W; i += blockDim.x) tile[(i / W) * (W + 1) + i % W] = __ldg(src + i);
+  __syncthreads();
+  uint4* dst = reinterpret_cast<uint4*>(x0) + static_cast<long long>(blockIdx.x) * W * (H + 2);
+  for (int i = threadIdx.x; i < W * (H + 2); i += blockDim.x) {
+    const int w = i / (H + 2), r = i - w * (H + 2);
+    uint4 o = make_uint4(0, 0, 0, 0);
+    if (r >= 1 && r <= H) {
+      const float x = fminf(fmaxf(tile[(r - 1) * (W + 1) + w], -60000.f), 60000.f);   // stays finite in f16
+      const __half hi = __float2half_rn(x);
+      const __half lo = __float2half_rn(x - __half2float(hi));
+      const uint32_t uh = __half_as_ushort(hi), ul = __half_as_ushort(lo);
+      o.x = uh | (ul << 16);
+      o.y = uh;
+    }
+    dst[i] = o;
+  }
+}
+
 // logits = W'(pool / HW) + b' with the last BatchNorm folded into W', b'
 __global__ void tc2_tail_kernel(const float* __restrict__ pool, const float* __restrict__ wout,
                                 const float* __restrict__ bout, float* __restrict__ logits, int n_clips, int N, int L,
@@ -597,12 +576,11 @@ __global__ void tc2_tail_kernel(const float* __restrict__ pool, const float* __r
 struct ResTc2Plan {
   int ncg = 6, NB = 48, C = 45, H = 101, W = 40, n_layers = 13, n_labels = 12;
   int plane_rows = 117, col_bytes = 0, stage_stride = 0, wbytes = 0, smem_bytes = 0;
-  long long slot_stride = 0;
+  long long slot_stride = 0, x0_clip_stride = 0;
   int max_teams = 37;
   int K = 3;                      // clips per team in flight: 37 teams x 3 x 2 buffers x 449 KB = 100 MB of L2
-  std::vector<T2Layer> layers;
+  std::vector<T2Layer> layers;    // [0] = conv0, [1..n_layers] = the C->C layers
   unsigned char* d_wpack = nullptr;
-  float* d_w0 = nullptr;
   float* d_wout = nullptr;
   float* d_bout = nullptr;
   std::vector<void*> owned;
@@ -668,6 +646,12 @@ bool plan_segments(T2Layer& ly, int W, int d) {
   return true;
 }
 
+template <typename Kern>
+int set_smem(Kern k, int bytes) {
+  HONK_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  return HONK_OK;
+}
+
 }  // namespace
 
 int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
@@ -689,10 +673,13 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
   p->plane_rows = p->H + T2_PAD;
   p->col_bytes = p->ncg * p->plane_rows * 16;
   p->slot_stride = align_up(static_cast<int64_t>(p->W) * p->col_bytes + T2_PAD * 16, 256);
+  p->x0_clip_stride = static_cast<long long>(p->W) * (p->H + 2) * 16;
   // a stage holds planes 0..ncg-1 of one column; the kh taps over-read up to 127 + 2*16 rows of the last plane
   p->stage_stride = static_cast<int>(align_up((p->ncg - 1) * p->plane_rows * 16 + (128 + 2 * T2_PAD) * 16, 128));
-  p->wbytes = 3 * (p->ncg / 2) * 6 * p->NB * 16;
-  p->smem_bytes = T2_NSTAGE * p->stage_stride + 2 * p->wbytes + (((p->H + 2) * (p->W + 3) + 3) / 4 * 4 + 9 * p->NB) * 4;
+  const int tile_bytes = 6 * p->NB * 16;                       // one (kh, kc) B tile: 2 K halves x 3NB rows x 8 halves
+  const int w0_bytes = 3 * tile_bytes;
+  p->wbytes = 3 * (p->ncg / 2) * tile_bytes;
+  p->smem_bytes = T2_NSTAGE * p->stage_stride + 2 * p->wbytes;
   int max_smem = 0;
   HONK_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, m->device));
   if (p->smem_bytes + 2048 > max_smem) return HONK_OK;
@@ -710,15 +697,42 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
       scale[i][k] = 1.0f / std::sqrt(var.data[k] + 1e-5f);       // BatchNorm2d(affine=False), eval
     }
   }
-  std::vector<T2Layer> layers(c.n_layers);
-  std::vector<unsigned char> wpack(static_cast<size_t>(c.n_layers) * p->wbytes, 0);
+  std::vector<T2Layer> layers(c.n_layers + 1);
+  std::vector<unsigned char> wpack(static_cast<size_t>(w0_bytes) + static_cast<size_t>(c.n_layers) * p->wbytes, 0);
+  {
+    // conv0 (bias-free, model.py:107): B tile kh = [K half][n = blk*NB + co][8]; input channels 0..2 = (x_hi, x_lo, x_hi)
+    // meet (w_hi, w_hi, w_lo); everything else (the whole second K half included) is zero.
+    T2Layer& ly = layers[0];
+    memset(&ly, 0, sizeof(ly));
+    ly.d = 1;
+    ly.flags = 4;
+    ly.w_off = 0;
+    ly.w_bytes = w0_bytes;
+    if (!plan_segments(ly, p->W, 1)) return HONK_OK;
+    const HostTensor& w = m->host.at("conv0.weight");
+    __half* hw = reinterpret_cast<__half*>(wpack.data());
+    for (int kh = 0; kh < 3; ++kh)
+      for (int blk = 0; blk < 3; ++blk) {
+        const int kw = 2 - blk;
+        for (int co = 0; co < C; ++co) {
+          const float v = w.data[co * 9 + kh * 3 + kw];
+          const __half hi = __float2half(v);
+          const __half lo = __float2half(v - __half2float(hi));
+          __half* row = hw + ((static_cast<size_t>(kh) * 2 + 0) * (3 * N) + blk * N + co) * 8;
+          row[0] = hi;
+          row[1] = hi;
+          row[2] = lo;
+        }
+      }
+  }
   for (int L = 1; L <= c.n_layers; ++L) {
-    T2Layer& ly = layers[L - 1];
+    T2Layer& ly = layers[L];
     memset(&ly, 0, sizeof(ly));
     ly.d = c.use_dilation ? (1 << ((L - 1) / 3)) : 1;
     const bool even = (L % 2 == 0), last = (L == c.n_layers);
     ly.flags = (even ? 1 : 0) | (last ? 2 : 0);
-    ly.w_off = (L - 1) * p->wbytes;
+    ly.w_off = w0_bytes + (L - 1) * p->wbytes;
+    ly.w_bytes = p->wbytes;
     if (!plan_segments(ly, p->W, ly.d)) return HONK_OK;
     // B operand: [i = kh*NKC + kc][K half][n = blk*NB + co][ci % 8], blk <-> kw = 2 - blk.
     //   ci <  C       : W[co][ci][kh][kw] * scale_{L-1}[ci]                 (BatchNorm scale of the producer)
@@ -726,7 +740,7 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
     //                   1.0 at real positions and 0 in the padding, so only in-range taps subtract the mean,
     //                   exactly like zero padding applied after bn_{L-1} (model.py:112-118)
     const HostTensor& w = m->host.at("conv" + std::to_string(L) + ".weight");
-    __half* hw = reinterpret_cast<__half*>(wpack.data() + static_cast<size_t>(L - 1) * p->wbytes);
+    __half* hw = reinterpret_cast<__half*>(wpack.data() + ly.w_off);
     auto slot = [&](int kh, int blk, int co, int ci) -> __half& {
       const int kc = ci / 16, khalf = (ci % 16) / 8, e = ci % 8;
       return hw[((static_cast<size_t>(kh * NKC + kc) * 2 + khalf) * (3 * N) + blk * N + co) * 8 + e];
@@ -752,13 +766,6 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
   p->layers = layers;
   HONK_TRY(up(p.get(), wpack, &p->d_wpack));
   {
-    const HostTensor& w = m->host.at("conv0.weight");
-    std::vector<float> h(9 * N, 0.f);
-    for (int co = 0; co < C; ++co)
-      for (int t = 0; t < 9; ++t) h[t * N + co] = w.data[co * 9 + t];
-    HONK_TRY(up(p.get(), h, &p->d_w0));
-  }
-  {
     // logits = W_o (s (.) (mean_hw(x_n) - mu_n)) + b_o  (last BN commutes with the mean)
     const HostTensor& w = m->host.at("output.weight");
     const HostTensor& b = m->host.at("output.bias");
@@ -775,8 +782,13 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
     HONK_TRY(up(p.get(), hwv, &p->d_wout));
     HONK_TRY(up(p.get(), hb, &p->d_bout));
   }
-  if (ncg == 6) HONK_CUDA(cudaFuncSetAttribute(tc2_res_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem_bytes));
-  else HONK_CUDA(cudaFuncSetAttribute(tc2_res_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem_bytes));
+  if (ncg == 6) {
+    HONK_TRY(set_smem(tc2_res_kernel<6, false>, p->smem_bytes));
+    HONK_TRY(set_smem(tc2_res_kernel<6, true>, p->smem_bytes));
+  } else {
+    HONK_TRY(set_smem(tc2_res_kernel<4, false>, p->smem_bytes));
+    HONK_TRY(set_smem(tc2_res_kernel<4, true>, p->smem_bytes));
+  }
   *out = p.release();
   return HONK_OK;
 }
@@ -791,6 +803,7 @@ int64_t res_tc2_workspace_bytes(const ResTc2Plan* p, int64_t n_clips) {
   a.take<unsigned char>(2ll * n_slots * p->slot_stride);
   a.take<float>(n_clips * p->NB);
   a.take<unsigned int>(n_clips);
+  a.take<unsigned char>(n_clips * p->x0_clip_stride);
   return align_up(a.off, 256);
 }
 
@@ -801,19 +814,26 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
   unsigned char* act = ar.take<unsigned char>(2ll * n_slots * p->slot_stride);
   float* pool = ar.take<float>(n_clips * p->NB);
   unsigned int* flags = ar.take<unsigned int>(n_clips);
+  const int64_t zero_bytes = ar.off;
+  unsigned char* x0 = ar.take<unsigned char>(n_clips * p->x0_clip_stride);
   HONK_CHECK(ar.ok(), HONK_ERR_WORKSPACE, "internal: tcgen05 workspace overrun");
   // zero rows between planes must be zero; pool sums and layer counters start at zero
-  HONK_CUDA(cudaMemsetAsync(act, 0, static_cast<size_t>(ar.off), s));
+  HONK_CUDA(cudaMemsetAsync(act, 0, static_cast<size_t>(zero_bytes), s));
+  {
+    ProfSpan span("res_pack_x0", s);
+    tc2_pack_x0_kernel<<<static_cast<unsigned>(n_clips), 256, p->H * (p->W + 1) * sizeof(float), s>>>(d_mfcc, x0, p->H, p->W);
+    HONK_LAUNCH_CHECK();
+  }
   T2Params a{};
   for (size_t i = 0; i < p->layers.size(); ++i) a.layers[i] = p->layers[i];
   a.wpack = p->d_wpack;
-  a.mfcc = d_mfcc;
-  a.w0 = p->d_w0;
+  a.x0 = x0;
   a.P = act;
   a.Q = act + static_cast<long long>(n_slots) * p->slot_stride;
   a.pool = pool;
   a.flags = flags;
   a.slot_stride = p->slot_stride;
+  a.x0_clip_stride = p->x0_clip_stride;
   a.n_layers = p->n_layers;
   a.n_clips = static_cast<int>(n_clips);
   a.n_slots = n_slots;
@@ -825,31 +845,38 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
   a.stage_stride = p->stage_stride;
   a.wbytes = p->wbytes;
   a.dbg = nullptr;
-  if (const char* e = getenv("HONK_TC2_MODE")) a.mode = atoi(e);
   static long long* s_dbg = nullptr;
   const char* dbg_env = getenv("HONK_TC2_DEBUG");
-  if (dbg_env && atoi(dbg_env)) {
-    if (!s_dbg) HONK_CUDA(cudaMalloc(&s_dbg, 160 * 16 * sizeof(long long)));
-    HONK_CUDA(cudaMemsetAsync(s_dbg, 0, 160 * 16 * sizeof(long long), s));
+  const bool dbg = dbg_env && atoi(dbg_env);
+  if (dbg) {
+    if (!s_dbg) HONK_CUDA(cudaMalloc(&s_dbg, 160 * T2_NDBG * sizeof(long long)));
+    HONK_CUDA(cudaMemsetAsync(s_dbg, 0, 160 * T2_NDBG * sizeof(long long), s));
     a.dbg = s_dbg;
   }
   {
     ProfSpan span("res_conv", s);
-    if (p->ncg == 6) tc2_res_kernel<6><<<teams * T2_G, T2_THREADS, p->smem_bytes, s>>>(a);
-    else tc2_res_kernel<4><<<teams * T2_G, T2_THREADS, p->smem_bytes, s>>>(a);
+    const dim3 grid(teams * T2_G);
+    if (p->ncg == 6) {
+      if (dbg) tc2_res_kernel<6, true><<<grid, T2_THREADS, p->smem_bytes, s>>>(a);
+      else tc2_res_kernel<6, false><<<grid, T2_THREADS, p->smem_bytes, s>>>(a);
+    } else {
+      if (dbg) tc2_res_kernel<4, true><<<grid, T2_THREADS, p->smem_bytes, s>>>(a);
+      else tc2_res_kernel<4, false><<<grid, T2_THREADS, p->smem_bytes, s>>>(a);
+    }
     HONK_LAUNCH_CHECK();
   }
-  if (a.dbg) {
-    std::vector<long long> h(160 * 16);
+  if (dbg) {
+    std::vector<long long> h(160 * T2_NDBG);
     HONK_CUDA(cudaStreamSynchronize(s));
     HONK_CUDA(cudaMemcpy(h.data(), a.dbg, h.size() * sizeof(long long), cudaMemcpyDeviceToHost));
-    double m[16] = {0};
+    double m[T2_NDBG] = {0};
     const int nb = teams * T2_G;
     for (int b = 0; b < nb; ++b)
-      for (int k = 0; k < 16; ++k) m[k] += static_cast<double>(h[b * 16 + k]) / nb;
+      for (int k = 0; k < T2_NDBG; ++k) m[k] += static_cast<double>(h[b * T2_NDBG + k]) / nb;
     fprintf(stderr, "tc2 dbg (mean cycles/CTA, %d CTAs, %lld clips): producer total %.0f flag-wait %.0f stage-empty-wait %.0f | "
-            "mma total %.0f acc-empty-wait %.0f stage-full-wait %.0f weight-wait %.0f | epilogue total %.0f acc-full-wait %.0f conv0 %.0f (q-flag wait %.0f) | lookahead hits %.0f of %.0f tasks\n",
-            nb, static_cast<long long>(n_clips), m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[8], m[7], m[9], m[10], m[11], m[12]);
+            "mma total %.0f acc-empty-wait %.0f stage-full-wait %.0f weight-wait %.0f | epilogue total %.0f acc-full-wait %.0f | "
+            "lookahead hits %.0f of %.0f tasks\n",
+            nb, static_cast<long long>(n_clips), m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[8], m[7], m[11], m[12]);
   }
   {
     ProfSpan span("res_tail", s);

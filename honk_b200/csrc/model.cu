@@ -352,3 +352,104 @@ extern "C" int honk_model_forward_pcm(const honk_model* m, const honk_frontend* 
   return honk_model_forward(m, mfcc, n_clips, d_logits, static_cast<char*>(d_workspace) + mf,
                             workspace_bytes - mf, stream);
 }
+
+// ------------------------------------------------------------------------------------------
+// host-buffer pipeline
+// ------------------------------------------------------------------------------------------
+namespace {
+
+struct HostPipe {                       // second stream + events of one call, released on every exit path
+  cudaStream_t copy = nullptr;
+  cudaEvent_t copied[2] = {nullptr, nullptr}, done[2] = {nullptr, nullptr}, start = nullptr;
+  int init() {
+    HONK_CUDA(cudaStreamCreateWithFlags(&copy, cudaStreamNonBlocking));
+    for (int k = 0; k < 2; ++k) {
+      HONK_CUDA(cudaEventCreateWithFlags(&copied[k], cudaEventDisableTiming));
+      HONK_CUDA(cudaEventCreateWithFlags(&done[k], cudaEventDisableTiming));
+    }
+    HONK_CUDA(cudaEventCreateWithFlags(&start, cudaEventDisableTiming));
+    return HONK_OK;
+  }
+  ~HostPipe() {
+    for (int k = 0; k < 2; ++k) {
+      if (copied[k]) cudaEventDestroy(copied[k]);
+      if (done[k]) cudaEventDestroy(done[k]);
+    }
+    if (start) cudaEventDestroy(start);
+    if (copy) cudaStreamDestroy(copy);
+  }
+};
+
+int pcm_elem_bytes(int dtype) { return dtype == HONK_PCM_I16 ? 2 : (dtype == HONK_PCM_F32 ? 4 : 8); }
+
+// Chunk size of the host pipeline: about HONK_HOST_CHUNKS (default 6) pieces, cut on the boundary at which
+// the persistent conv kernel's teams are all busy, so chunking costs no partially filled wave.
+int64_t host_chunk_clips(const honk_model* m, int64_t n_clips) {
+  if (n_clips <= 1024) return n_clips;
+  int pieces = 6;
+  if (const char* e = getenv("HONK_HOST_CHUNKS")) pieces = std::max(1, std::min(64, atoi(e)));
+  const int64_t wave = m->tc2 ? honk::res_tc2_wave_clips(m->tc2) : 128;
+  const int64_t chunk = ((n_clips + pieces - 1) / pieces + wave - 1) / wave * wave;
+  return std::min(chunk, n_clips);
+}
+
+}  // namespace
+
+extern "C" int64_t honk_model_workspace_bytes_pcm_host(const honk_model* m, const honk_frontend* fe, int64_t n_clips,
+                                                       int64_t n_samples, int dtype) {
+  if (!m || !fe || n_clips <= 0) return 0;
+  const int64_t chunk = host_chunk_clips(m, n_clips);
+  const int64_t staging = align_up(chunk * n_samples * pcm_elem_bytes(dtype), 256);
+  const int64_t logits = align_up(n_clips * m->cfg.n_labels * 4, 256);
+  return 2 * staging + logits + honk_model_workspace_bytes_pcm(m, fe, chunk, n_samples);
+}
+
+extern "C" int honk_model_forward_pcm_host(const honk_model* m, const honk_frontend* fe, const void* h_pcm, int dtype,
+                                           int64_t n_clips, int64_t n_samples, int64_t clip_stride, float* h_logits,
+                                           void* d_workspace, int64_t workspace_bytes, void* stream) {
+  HONK_CHECK(m && fe, HONK_ERR_INVALID, "honk_model_forward_pcm_host: null handle");
+  HONK_CHECK(n_clips >= 0 && n_samples > 0 && clip_stride >= n_samples, HONK_ERR_INVALID,
+             "honk_model_forward_pcm_host: bad shape");
+  if (n_clips == 0) return HONK_OK;
+  HONK_CHECK(h_pcm && h_logits, HONK_ERR_INVALID, "honk_model_forward_pcm_host: null buffer");
+  HONK_CHECK(dtype == HONK_PCM_I16 || dtype == HONK_PCM_F32 || dtype == HONK_PCM_F64, HONK_ERR_INVALID, "unknown PCM dtype %d", dtype);
+  HONK_CHECK(d_workspace && workspace_bytes >= honk_model_workspace_bytes_pcm_host(m, fe, n_clips, n_samples, dtype),
+             HONK_ERR_WORKSPACE, "workspace too small");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int eb = pcm_elem_bytes(dtype);
+  const int64_t chunk = host_chunk_clips(m, n_clips);
+  const int64_t staging = align_up(chunk * n_samples * eb, 256);
+  const int64_t logits_bytes = align_up(n_clips * m->cfg.n_labels * 4, 256);
+  char* base = static_cast<char*>(d_workspace);
+  char* stage[2] = {base, base + staging};
+  float* d_logits = reinterpret_cast<float*>(base + 2 * staging);
+  char* inner = base + 2 * staging + logits_bytes;
+  const int64_t inner_bytes = workspace_bytes - 2 * staging - logits_bytes;
+  HostPipe hp;
+  HONK_TRY(hp.init());
+  // the scratch may have been handed out in the order of `s`: the copy stream must not run ahead of that
+  HONK_CUDA(cudaEventRecord(hp.start, s));
+  HONK_CUDA(cudaStreamWaitEvent(hp.copy, hp.start, 0));
+  int i = 0;
+  for (int64_t c0 = 0; c0 < n_clips; c0 += chunk, ++i) {
+    const int64_t nc = std::min(chunk, n_clips - c0);
+    const int b = i & 1;
+    if (i >= 2) HONK_CUDA(cudaStreamWaitEvent(hp.copy, hp.done[b], 0));      // chunk i-2 no longer reads this buffer
+    const char* src = static_cast<const char*>(h_pcm) + c0 * clip_stride * eb;
+    if (clip_stride == n_samples) {
+      HONK_CUDA(cudaMemcpyAsync(stage[b], src, static_cast<size_t>(nc * n_samples * eb), cudaMemcpyHostToDevice, hp.copy));
+    } else {
+      HONK_CUDA(cudaMemcpy2DAsync(stage[b], static_cast<size_t>(n_samples * eb), src, static_cast<size_t>(clip_stride * eb),
+                                  static_cast<size_t>(n_samples * eb), static_cast<size_t>(nc), cudaMemcpyHostToDevice, hp.copy));
+    }
+    HONK_CUDA(cudaEventRecord(hp.copied[b], hp.copy));
+    HONK_CUDA(cudaStreamWaitEvent(s, hp.copied[b], 0));
+    HONK_TRY(honk_model_forward_pcm(m, fe, stage[b], dtype, nc, n_samples, n_samples, d_logits + c0 * m->cfg.n_labels, inner,
+                                    inner_bytes, s));
+    HONK_CUDA(cudaEventRecord(hp.done[b], s));
+  }
+  HONK_CUDA(cudaMemcpyAsync(h_logits, d_logits, static_cast<size_t>(n_clips * m->cfg.n_labels * 4), cudaMemcpyDeviceToHost, s));
+  HONK_CUDA(cudaStreamSynchronize(s));
+  HONK_CUDA(cudaStreamSynchronize(hp.copy));
+  return HONK_OK;
+}

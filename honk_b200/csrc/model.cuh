@@ -53,6 +53,7 @@ int64_t res_tc_workspace_bytes(const honk_model* m, int64_t n_clips);
 // res_tc2.cu: persistent multi-layer kernel for the un-pooled res* models; *out == nullptr when it does not apply.
 int res_tc2_plan_create(honk_model* m, ResTc2Plan** out);
 int64_t res_tc2_workspace_bytes(const ResTc2Plan* p, int64_t n_clips);
+int res_tc2_wave_clips(const ResTc2Plan* p);   // clips all teams process at once: batch cuts on this boundary lose nothing
 int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, float* d_logits, void* ws, int64_t ws_bytes,
                     cudaStream_t s);
 int res_tc_forward(const honk_model* m, const float* d_mfcc, int64_t n_clips, float* d_logits, void* ws,

@@ -797,6 +797,8 @@ static int tc2_teams(const ResTc2Plan* p, int64_t n_clips) {
   return static_cast<int>(std::min<int64_t>(p->max_teams, (n_clips + p->K - 1) / p->K));
 }
 
+int res_tc2_wave_clips(const ResTc2Plan* p) { return p->max_teams * p->K; }
+
 int64_t res_tc2_workspace_bytes(const ResTc2Plan* p, int64_t n_clips) {
   const int n_slots = p->K * tc2_teams(p, n_clips);
   Arena a(nullptr, 0);

@@ -188,6 +188,13 @@ class SerializableModule(nn.Module):
         dev = self._device()
         return ops.model_forward_pcm(pcm, self._ensure_native(dev), audio_processor.handle, self.n_labels)
 
+    def forward_pcm_host(self, pcm, audio_processor, out=None):
+        """Host ``[B, n_samples]`` PCM -> host logits, copies overlapped with the kernels chunk by chunk."""
+        if self.training:
+            raise RuntimeError("honk_b200 implements the inference path only; call model.eval()")
+        dev = self._device()
+        return ops.model_forward_pcm_host(pcm, self._ensure_native(dev), audio_processor.handle, self.n_labels, dev, out)
+
 
 class SpeechResModel(SerializableModule):
     """res8 / res15 / res26 [-narrow] (model.py:82-121).  The torch sub-modules only HOLD the

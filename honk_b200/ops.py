@@ -81,6 +81,34 @@ def _(pcm, model, frontend, n_labels):
     return pcm.new_empty((pcm.shape[0], n_labels), dtype=torch.float32)
 
 
+def model_forward_pcm_host(pcm: torch.Tensor, model: int, frontend: int, n_labels: int, device, out=None) -> torch.Tensor:
+    """Host PCM ``[B, n_samples]`` (pinned memory overlaps the copies) -> host logits ``[B, n_labels]``.
+
+    One C-ABI call (honk_model_forward_pcm_host): chunked double-buffered H2D copies on a second stream
+    under the front-end and conv kernels, then one D2H copy of the logits.  Not a custom op: it takes
+    and returns host tensors and synchronises before returning.
+    """
+    if pcm.is_cuda:
+        raise RuntimeError("honk_b200: model_forward_pcm_host takes a host tensor")
+    if pcm.dim() == 1:
+        pcm = pcm[None]
+    if pcm.stride(-1) != 1:
+        pcm = pcm.contiguous()
+    B = pcm.shape[0]
+    if out is None:
+        out = torch.empty((B, n_labels), dtype=torch.float32, pin_memory=True)
+    if B == 0:
+        return out
+    L = N.lib()
+    code = N.pcm_dtype_code(pcm)
+    ws_bytes = int(L.honk_model_workspace_bytes_pcm_host(model, frontend, B, pcm.shape[1], code))
+    ws = torch.empty((max(ws_bytes, 1),), dtype=torch.uint8, device=device)
+    with torch.cuda.device(device):
+        N.check(L.honk_model_forward_pcm_host(model, frontend, pcm.data_ptr(), code, B, pcm.shape[1], _row_stride(pcm),
+                                              out.data_ptr(), ws.data_ptr(), ws_bytes, N.stream_ptr(device)))
+    return out
+
+
 @torch.library.custom_op("honk_b200::label_from_logits", mutates_args=(), device_types="cuda")
 def label_from_logits(logits: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
     N.require_cuda(logits, "logits")

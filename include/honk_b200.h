@@ -152,6 +152,20 @@ HONK_API int honk_model_forward_pcm(const honk_model* m, const honk_frontend* fe
 HONK_API int64_t honk_model_workspace_bytes_pcm(const honk_model* m, const honk_frontend* fe, int64_t n_clips,
                                        int64_t n_samples);
 
+/* Host-buffer pipeline, the call a serving process makes with audio that sits in host memory
+ * (the role of SpeechDataset.collate_fn + model(...).cpu() in utils/train.py:41-46, 71-80 and of
+ * TorchLabelService.label in service.py:88-104): h_pcm [n_clips, clip_stride] of `dtype` in HOST
+ * memory -> h_logits float32 [n_clips, n_labels] in HOST memory.  The batch is cut into chunks
+ * and the host->device copy of chunk i+1 runs on a second stream while chunk i is in the
+ * kernels; page-locked h_pcm / h_logits make those copies truly asynchronous (pageable memory
+ * works, without the overlap).  Returns after h_logits is complete.  d_workspace is DEVICE
+ * scratch of honk_model_workspace_bytes_pcm_host bytes. */
+HONK_API int honk_model_forward_pcm_host(const honk_model* m, const honk_frontend* fe, const void* h_pcm, int dtype,
+                                int64_t n_clips, int64_t n_samples, int64_t clip_stride, float* h_logits,
+                                void* d_workspace, int64_t workspace_bytes, void* stream);
+HONK_API int64_t honk_model_workspace_bytes_pcm_host(const honk_model* m, const honk_frontend* fe, int64_t n_clips,
+                                            int64_t n_samples, int dtype);
+
 /* softmax + argmax + max-prob per clip: the tail of TorchLabelService.label
  * (service.py:103-104) and print_eval's argmax (utils/train.py:41-46).
  * d_labels int32 [n_clips], d_probs float32 [n_clips] (either may be NULL). */

@@ -78,6 +78,34 @@ def test_against_oracle_batch64(name):
         assert np.allclose(y, y2, rtol=0, atol=1e-5 * np.abs(ref).max())   # fused PCM entry == two-step entry (atomics reorder sums)
 
 
+@pytest.mark.parametrize("name,n", [("res15-narrow", 1500), ("res8-narrow", 70)])
+def test_host_pipeline_matches_device_entry(name, n, monkeypatch):
+    # honk_model_forward_pcm_host: chunked H2D under the kernels == the device-buffer entry, row for row
+    import honk_b200 as hb
+    monkeypatch.setenv("HONK_HOST_CHUNKS", "3")
+    cfg = dict(hb.find_config(name))
+    cfg["n_labels"] = 12
+    base = synth.make_clips(100, start=9000)
+    clips = np.ascontiguousarray(np.tile(base, (n // 100 + 1, 1))[:n])
+    clips[1::2] = clips[1::2][:, ::-1]                 # make neighbouring rows differ
+    pre = hb.AudioPreprocessor()
+    mf = pre.compute_mfccs_batch(torch.from_numpy(clips[:16]).cuda()).cpu().numpy()
+    sd = synth.make_state_dict(name, cfg, seed=5, calib_mfcc=mf)
+    m = build(name, cfg, sd, 0)
+    ref = m.forward_pcm(torch.from_numpy(clips).cuda(), pre).cpu().numpy()
+    scale = np.abs(ref).max()
+    host = torch.from_numpy(clips).pin_memory()
+    y = m.forward_pcm_host(host, pre).numpy()
+    assert y.shape == ref.shape and np.allclose(y, ref, rtol=0, atol=1e-5 * scale)
+    # strided rows (clip_stride > n_samples) and pageable memory take the 2-D copy path
+    wide = np.zeros((n, clips.shape[1] + 37), dtype=clips.dtype)
+    wide[:, :clips.shape[1]] = clips
+    y2 = m.forward_pcm_host(torch.from_numpy(wide)[:, :clips.shape[1]], pre).numpy()
+    assert np.allclose(y2, ref, rtol=0, atol=1e-5 * scale)
+    with pytest.raises(RuntimeError):
+        m.forward_pcm_host(host.cuda(), pre)
+
+
 def test_strict_state_dict_and_reload(golden_dir):
     import honk_b200 as hb
     g, cfg, sd = load_golden(golden_dir, "res8-narrow")

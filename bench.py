@@ -223,6 +223,17 @@ def workload_config(args, world):
     }
 
 
+def recorded_traffic(kernel, clips):
+    """DRAM read+write bytes per launch of `kernel` from the committed ncu capture (profiles/traffic.json),
+    scaled to this run's clips per launch; None when no capture is recorded."""
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")) as f:
+            t = json.load(f)[kernel]
+        return (t["dram_bytes_read"] + t["dram_bytes_write"]) * clips / 8192.0
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
@@ -351,7 +362,8 @@ def main():
                               if persistent else "tc_conv_kernel (dilated 3x3 C->C implicit GEMM, tcgen05)",
                     "achieved": achieved, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
                     "frac": achieved / peaks["tf_sustained"], "peak_source": peaks["source"] + " bf16 sustained",
-                    "traffic": None, "avg_launch_ms": avg_launch_ms, "launches_per_step": n_launch / args.steps,
+                    "traffic": recorded_traffic("tc2_res_kernel", B) if persistent and name == "res15" else None,
+                    "avg_launch_ms": avg_launch_ms, "launches_per_step": n_launch / args.steps,
                     "flops_per_launch": flops_layer_clip * n_layers * clips_done / n_launch,
                     "share_of_step": t_ms / (ms * args.steps)}
         elif "f32_model" in spans:

@@ -368,10 +368,12 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
               if (t + 1 < n_in) {
                 const uint32_t st1 = (st + 1 == T2_NSTAGE) ? 0 : st + 1;
                 const uint32_t par1 = (st + 1 == T2_NSTAGE) ? stpar ^ 1 : stpar;
-                bool ok = mbar_test_wait(a_full + 8 * st1, par1);
+                bool ok;
                 if (jc + 1 < jend) {                                    // next task first-touches block gc + 2
                   const uint32_t g2 = static_cast<uint32_t>(gc + 2);
-                  ok = mbar_test_wait(a_acc_empty + 8 * (g2 % NSLOT), ((g2 / NSLOT) & 1) ^ 1) && ok;
+                  ok = mbar_test_wait2(a_full + 8 * st1, par1, a_acc_empty + 8 * (g2 % NSLOT), ((g2 / NSLOT) & 1) ^ 1);
+                } else {
+                  ok = mbar_test_wait(a_full + 8 * st1, par1);
                 }
                 pre = ok;
                 if (DBG) { n_task += 1; n_hit += ok; }

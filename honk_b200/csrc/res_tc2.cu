@@ -91,6 +91,7 @@ struct T2Params {
   int col_bytes;                  // NCG * plane_rows * 16
   int stage_stride, wbytes;       // wbytes = size of one weight buffer (largest layer)
   long long* dbg;                 // optional [gridDim][T2_NDBG] cycle counters (HONK_TC2_DEBUG)
+  int mode;                       // debug kernel only: 1 = MMA issue alone (no copies, waits or epilogue; results are garbage)
   // Per-layer tables live in the kernel parameter (constant) bank so that the MMA warp's descriptor
   // arithmetic stays on the uniform datapath (no R2UR per tcgen05.mma operand).
   T2Layer layers[T2_MAXL + 1];
@@ -187,6 +188,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
   __shared__ __align__(8) uint64_t bar_acc_full[NSLOT], bar_acc_empty[NSLOT];
   __shared__ __align__(8) uint64_t bar_wfull[2], bar_wfree[2];
   __shared__ __align__(8) uint64_t bar_done[4];        // epilogue -> signaller: this CTA's stores of one (clip, layer) are issued
+  __shared__ __align__(8) uint64_t bar_dbg;            // debug mode 1: pipe drain
   __shared__ uint32_t tmem_base_s;
 
   const int tid = threadIdx.x, lane = tid & 31;
@@ -214,6 +216,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
       mbar_init(a_wfree + 8 * k, 1);
     }
     for (int k = 0; k < 4; ++k) mbar_init(a_done + 8 * k, 8);
+    mbar_init(smem_u32(&bar_dbg), 1);
     fence_mbar_init();
   }
   // conv0's second K half reads stage bytes no copy of that layer wrote: they must be finite f16 from the start
@@ -237,7 +240,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
 
   if (warp == 0) {
     // ======================================= producer =======================================
-    if (lane == 0) {
+    if (lane == 0 && !(DBG && p.mode == 1)) {
       uint32_t it = 0, q = 0;
       int piter = 0;
       long long t_flag = 0, t_empty = 0;
@@ -314,7 +317,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
         const uint32_t d = ly.d;
         const bool conv0 = ly.flags & 4;
         const int nseg = ly.n_seg[rank];
-        T2_TIMED(t_w, mbar_wait(a_wfull + 8 * (q & 1), (q >> 1) & 1));
+        if (!(DBG && p.mode == 1)) T2_TIMED(t_w, mbar_wait(a_wfull + 8 * (q & 1), (q >> 1) & 1));
         const uint32_t b_lo0 = b_lbo | (smem_u32(wbuf + (q & 1) * p.wbytes) >> 4);
         for (int ab = 0; ab < nab; ++ab) {
           for (int s = 0; s < nseg; ++s) {
@@ -333,7 +336,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
               const int n1 = wrap ? static_cast<int>(NSLOT - sf) : n;
               // first-touched outputs need their ring slot handed back (read and zeroed) by the epilogue:
               // block 2, and at t == 0 block 1 too
-              if (!pre) {
+              if (!pre && !(DBG && p.mode == 1)) {
                 const long long tw0 = DBG ? clock64() : 0;
                 if (t == 0 && c_in) {
                   const uint32_t g1 = static_cast<uint32_t>(gc);
@@ -365,7 +368,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
               // Look one task ahead while the queued MMAs drain: probe (never block on) the barriers the next
               // task of this segment needs, so that its issue can start without a serialized poll.
               pre = false;
-              if (t + 1 < n_in) {
+              if (t + 1 < n_in && !(DBG && p.mode == 1)) {
                 const uint32_t st1 = (st + 1 == T2_NSTAGE) ? 0 : st + 1;
                 const uint32_t par1 = (st + 1 == T2_NSTAGE) ? stpar ^ 1 : stpar;
                 bool ok;
@@ -398,11 +401,16 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
         __syncwarp();
       }
     }
+    if (DBG && p.mode == 1) {                   // drain the tensor pipe before reading the clock
+      if (elect_one()) commit(smem_u32(&bar_dbg));
+      __syncwarp();
+      mbar_wait(smem_u32(&bar_dbg), 0);
+    }
     if (DBG && lane == 0) {
       long long* o = p.dbg + blockIdx.x * T2_NDBG;
       o[3] = clock64() - t_start; o[4] = t_acc; o[5] = t_full; o[6] = t_w; o[11] = n_hit; o[12] = n_task;
     }
-  } else if (warp < 10) {
+  } else if (warp < 10 && !(DBG && p.mode == 1)) {
     // ======================================= epilogue =======================================
     // The two groups of 4 warps take alternate output columns (all NB channels each).  Stored activations
     // are the raw x_L = relu(conv) [+ x_{L-2}]; BatchNorm lives in the next layer's weights (scale) and in
@@ -510,7 +518,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
       }
     }
     if (DBG && etid == 0) { long long* o = p.dbg + blockIdx.x * T2_NDBG; o[7] = t_wait; o[8] = clock64() - t_start_e; }
-  } else if (warp == 10) {
+  } else if (warp == 10 && !(DBG && p.mode == 1)) {
     // ======================================= flag signaller =================================
     // Publishes "all stores of this CTA for (clip, layer) are visible" to the team: waits until the eight
     // epilogue warps have arrived, then a gpu-scope fence (cumulative over the stores observed through the
@@ -849,6 +857,7 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
   a.stage_stride = p->stage_stride;
   a.wbytes = p->wbytes;
   a.dbg = nullptr;
+  a.mode = 0;
   static long long* s_dbg = nullptr;
   const char* dbg_env = getenv("HONK_TC2_DEBUG");
   const bool dbg = dbg_env && atoi(dbg_env);
@@ -856,6 +865,7 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
     if (!s_dbg) HONK_CUDA(cudaMalloc(&s_dbg, 160 * T2_NDBG * sizeof(long long)));
     HONK_CUDA(cudaMemsetAsync(s_dbg, 0, 160 * T2_NDBG * sizeof(long long), s));
     a.dbg = s_dbg;
+    if (const char* e = getenv("HONK_TC2_MODE")) a.mode = atoi(e);
   }
   {
     ProfSpan span("res_conv", s);

@@ -110,6 +110,20 @@ __device__ __forceinline__ bool mbar_test_wait2(uint32_t mbar_a, uint32_t parity
       : "memory");
   return ok;
 }
+// Three probes in flight at once (one result: all three phases complete).
+__device__ __forceinline__ bool mbar_test_wait3(uint32_t mbar_a, uint32_t parity_a, uint32_t mbar_b, uint32_t parity_b,
+                                                uint32_t mbar_c, uint32_t parity_c) {
+  uint32_t ok;
+  asm volatile(
+      "{\n.reg .pred p, q, r;\nmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "mbarrier.test_wait.parity.shared::cta.b64 q, [%3], %4;\n"
+      "mbarrier.test_wait.parity.shared::cta.b64 r, [%5], %6;\n"
+      "and.pred p, p, q;\nand.pred p, p, r;\nselp.u32 %0, 1, 0, p;\n}\n"
+      : "=r"(ok)
+      : "r"(mbar_a), "r"(parity_a), "r"(mbar_b), "r"(parity_b), "r"(mbar_c), "r"(parity_c)
+      : "memory");
+  return ok;
+}
 // Bounded wait: a protocol bug (e.g. a TMA byte count that never arrives) traps instead of
 // hanging the GPU.  try_wait suspends in hardware, so the poll count stays small in normal runs.
 __device__ __forceinline__ void mbar_wait(uint32_t mbar, uint32_t parity) {

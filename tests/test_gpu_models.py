@@ -106,6 +106,39 @@ def test_host_pipeline_matches_device_entry(name, n, monkeypatch):
         m.forward_pcm_host(host.cuda(), pre)
 
 
+def test_top1_agreement_trained_res15_16384(golden_dir):
+    # top-1 identical on >= 99.9 % of >= 16384 clips, with briefly trained weights so that the
+    # logit margins are realistic (tests/golden/make_trained.py -> res15_trained.npz).  Three arms on the same clips:
+    # the f16-operand tcgen05 path, the all-FP32 CUDA-core path, and (on a 1024 subset) the CPU oracle in float32
+    # fed by the float64 oracle front end.
+    import honk_b200 as hb
+    from oracle import honk_oracle as orc
+    cfg = dict(hb.find_config("res15"))
+    cfg["n_labels"] = 12
+    sd = dict(np.load(os.path.join(golden_dir, "res15_trained.npz")))
+    lab, _ = synth.make_clips(2048, start=300000, labelled=True)
+    unl = synth.make_clips(2048, start=400000)
+    base = np.concatenate([lab, unl])                                    # 4096 unique clips
+    clips = np.concatenate([base, (-(base.astype(np.int32) // 2)).astype(np.int16), np.ascontiguousarray(base[:, ::-1]),
+                            np.roll(base, 1234, axis=1)])                 # + half-gain inverted, reversed, shifted
+    assert clips.shape == (16384, 16000)
+    pre = hb.AudioPreprocessor()
+    x = torch.from_numpy(clips).cuda()
+    y16 = build("res15", cfg, sd, 0).forward_pcm(x, pre).cpu().numpy()
+    y32 = build("res15", cfg, sd, 1).forward_pcm(x, pre).cpu().numpy()
+    scale = np.abs(y32).max()
+    err = np.abs(y16 - y32).max() / scale
+    agree = float((y16.argmax(1) == y32.argmax(1)).mean())
+    assert err <= TOL["tcgen05-f16"], err
+    assert agree >= 0.999, (agree, err)
+    sub = np.arange(0, 16384, 16)                                        # 1024 clips across all four variants
+    mf = orc.AudioPreprocessorOracle().compute_mfccs_batch([orc.pcm16_to_float(c) for c in clips[sub]])
+    ref = orc.model_forward("res15", sd, cfg, mf, torch.float32).numpy()
+    for y in (y16, y32):
+        assert float((y[sub].argmax(1) == ref.argmax(1)).mean()) >= 0.999
+    assert np.abs(y32[sub] - ref).max() / np.abs(ref).max() <= 1e-3
+
+
 def test_strict_state_dict_and_reload(golden_dir):
     import honk_b200 as hb
     g, cfg, sd = load_golden(golden_dir, "res8-narrow")

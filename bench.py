@@ -310,7 +310,7 @@ def main():
         N.profile_enable(False)
         ms = e0.elapsed_time(e1) / max(1, args.steps)
         spans = {}
-        for sp in ("frontend", "res_pack_x0", "res_conv0", "res_conv", "res_tail", "f32_model"):
+        for sp in ("frontend", "res_pack_x0", "res_conv0", "res_conv", "res_tail", "cnn_pack_x8", "cnn_conv", "cnn_fc", "f32_model"):
             t, n = N.profile_get(sp)
             if n:
                 spans[sp] = (t, n)
@@ -366,6 +366,14 @@ def main():
                     "avg_launch_ms": avg_launch_ms, "launches_per_step": n_launch / args.steps,
                     "flops_per_launch": flops_layer_clip * n_layers * clips_done / n_launch,
                     "share_of_step": t_ms / (ms * args.steps)}
+        elif "cnn_conv" in spans:
+            t_ms, n_spans = spans["cnn_conv"]
+            fl = orc.conv_flops_per_clip(name, cfg)                # conv1 + conv2 + Linear, unpadded 2*MAC
+            achieved = fl * B * args.steps / (t_ms * 1e-3) / 1e12
+            roof = {"bound": "tensor", "kernel": "cnn_tc_kernel (persistent: conv1 + maxpool + conv2 per clip, tcgen05 implicit GEMM)",
+                    "achieved": achieved, "peak": peaks["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / peaks["tf_sustained"],
+                    "peak_source": peaks["source"] + " bf16 sustained", "traffic": None, "avg_launch_ms": t_ms / n_spans,
+                    "launches_per_step": n_spans / args.steps, "share_of_step": t_ms / (ms * args.steps)}
         elif "f32_model" in spans:
             t_ms, n_spans = spans["f32_model"]
             fl = orc.conv_flops_per_clip(name, cfg)

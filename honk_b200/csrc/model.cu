@@ -279,6 +279,9 @@ extern "C" int honk_model_create(const honk_model_config* cfg, const honk_tensor
       if (!m->tc2) HONK_TRY(res_tc_plan_create(m.get()));
       if (m->tc || m->tc2) m->path = "tcgen05-f16";
     }
+  } else if (cfg->precision == 0) {
+    HONK_TRY(cnn_tc_plan_create(m.get(), &m->ctc));
+    if (m->ctc) m->path = "tcgen05-f16";
   }
   *out = m.release();
   return HONK_OK;
@@ -288,6 +291,7 @@ extern "C" int honk_model_destroy(honk_model* m) {
   if (!m) return HONK_OK;
   if (m->tc) res_tc_plan_free(m->tc);
   if (m->tc2) res_tc2_plan_free(m->tc2);
+  if (m->ctc) cnn_tc_plan_free(m->ctc);
   for (void* p : m->owned) cudaFree(p);
   delete m;
   return HONK_OK;
@@ -298,6 +302,7 @@ extern "C" const char* honk_model_path(const honk_model* m) { return m ? m->path
 extern "C" int64_t honk_model_workspace_bytes(const honk_model* m, int64_t n_clips) {
   if (!m || n_clips <= 0) return 0;
   if (m->tc2) return res_tc2_workspace_bytes(m->tc2, n_clips);
+  if (m->ctc) return cnn_tc_workspace_bytes(m->ctc, n_clips);
   return m->tc ? res_tc_workspace_bytes(m, n_clips) : f32_workspace(m, n_clips);
 }
 
@@ -312,6 +317,7 @@ extern "C" int honk_model_forward(const honk_model* m, const float* d_mfcc, int6
              static_cast<long long>(honk_model_workspace_bytes(m, n_clips)));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (m->tc2) return res_tc2_forward(m->tc2, d_mfcc, n_clips, d_logits, d_workspace, workspace_bytes, s);
+  if (m->ctc) return cnn_tc_forward(m->ctc, d_mfcc, n_clips, d_logits, d_workspace, workspace_bytes, s);
   if (m->tc) return res_tc_forward(m, d_mfcc, n_clips, d_logits, d_workspace, workspace_bytes, s);
   ProfSpan span("f32_model", s);
   const int64_t in_per = static_cast<int64_t>(m->H0) * m->W0;

@@ -24,6 +24,8 @@ struct ResTcPlan;   // res_tc.cu
 void res_tc_plan_free(ResTcPlan*);
 struct ResTc2Plan;  // res_tc2.cu
 void res_tc2_plan_free(ResTc2Plan*);
+struct CnnTcPlan;   // cnn_tc.cu
+void cnn_tc_plan_free(CnnTcPlan*);
 
 }  // namespace honk
 
@@ -37,6 +39,7 @@ struct honk_model {
   std::vector<void*> owned;                          // every cudaMalloc of this handle
   honk::ResTcPlan* tc = nullptr;                     // non-null => per-layer tcgen05 path (pooled res8/res26)
   honk::ResTc2Plan* tc2 = nullptr;                   // non-null => persistent multi-layer tcgen05 path (res15)
+  honk::CnnTcPlan* ctc = nullptr;                    // non-null => tcgen05 path for the cnn-trad-pool2 geometry
   std::string path = "cuda-core-f32";
   // geometry derived from cfg
   int H0 = 101, W0 = 40;                             // input
@@ -56,6 +59,11 @@ int64_t res_tc2_workspace_bytes(const ResTc2Plan* p, int64_t n_clips);
 int res_tc2_wave_clips(const ResTc2Plan* p);   // clips all teams process at once: batch cuts on this boundary lose nothing
 int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, float* d_logits, void* ws, int64_t ws_bytes,
                     cudaStream_t s);
+// cnn_tc.cu: tcgen05 conv1 + conv2 for cnn-trad-pool2; *out == nullptr when the geometry differs.
+int cnn_tc_plan_create(honk_model* m, CnnTcPlan** out);
+int64_t cnn_tc_workspace_bytes(const CnnTcPlan* p, int64_t n_clips);
+int cnn_tc_forward(const CnnTcPlan* p, const float* d_mfcc, int64_t n_clips, float* d_logits, void* ws, int64_t ws_bytes,
+                   cudaStream_t s);
 int res_tc_forward(const honk_model* m, const float* d_mfcc, int64_t n_clips, float* d_logits, void* ws,
                    int64_t ws_bytes, cudaStream_t s);
 

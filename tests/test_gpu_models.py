@@ -139,6 +139,19 @@ def test_top1_agreement_trained_res15_16384(golden_dir):
     assert np.abs(y32[sub] - ref).max() / np.abs(ref).max() <= 1e-3
 
 
+@pytest.mark.parametrize("n", [1, 3, 149, 300])
+def test_cnn_trad_pool2_tensor_path_batch_sizes(golden_dir, n):
+    # persistent one-CTA-per-SM kernel: fewer clips than SMs, a ragged last round, several rounds per CTA
+    g, cfg, sd = load_golden(golden_dir, "cnn-trad-pool2")
+    rng = np.random.default_rng(n)
+    x = torch.from_numpy((rng.standard_normal((n, 101, 40)) * np.abs(g["x"]).std()).astype(np.float32)).cuda()
+    m16, m32 = build("cnn-trad-pool2", cfg, sd, 0), build("cnn-trad-pool2", cfg, sd, 1)
+    assert m16.native_path == "tcgen05-f16" and m32.native_path == "cuda-core-f32"
+    y16, y32 = m16(x).cpu().numpy(), m32(x).cpu().numpy()
+    assert np.abs(y16 - y32).max() / np.abs(y32).max() <= 5e-3
+    assert np.array_equal(m16(x).cpu().numpy(), y16)          # deterministic (no atomics on this path)
+
+
 def test_strict_state_dict_and_reload(golden_dir):
     import honk_b200 as hb
     g, cfg, sd = load_golden(golden_dir, "res8-narrow")
@@ -170,6 +183,7 @@ def test_save_load_roundtrip(tmp_path, golden_dir):
     m.save(f)
     m2 = hb.SpeechModel(cfg)
     m2.load(f)
+    m2.precision = 1                  # same arithmetic path as m: the round trip must be bit-exact
     m2.cuda().eval()
     x = torch.from_numpy(g["x"]).cuda()
     assert torch.equal(m(x), m2(x))

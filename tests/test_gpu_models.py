@@ -146,8 +146,8 @@ def test_cnn_trad_pool2_tensor_path_batch_sizes(golden_dir, n):
     rng = np.random.default_rng(n)
     x = torch.from_numpy((rng.standard_normal((n, 101, 40)) * np.abs(g["x"]).std()).astype(np.float32)).cuda()
     m16, m32 = build("cnn-trad-pool2", cfg, sd, 0), build("cnn-trad-pool2", cfg, sd, 1)
-    assert m16.native_path == "tcgen05-f16" and m32.native_path == "cuda-core-f32"
     y16, y32 = m16(x).cpu().numpy(), m32(x).cpu().numpy()
+    assert m16.native_path == "tcgen05-f16" and m32.native_path == "cuda-core-f32"
     assert np.abs(y16 - y32).max() / np.abs(y32).max() <= 5e-3
     assert np.array_equal(m16(x).cpu().numpy(), y16)          # deterministic (no atomics on this path)
 

@@ -255,6 +255,10 @@ def main():
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # NCCL writes its version banner to stdout when the communicator is created: keep fd 1 for the JSON line only
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
     N.lib()                                            # fails loudly if the extension is missing
 
@@ -337,6 +341,10 @@ def main():
         dist.all_reduce(lt)
         launches = int(lt[0])
 
+    if world > 1:
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        os.close(saved_stdout)
     if rank == 0:
         from oracle import honk_oracle as orc          # checker / CPU baseline only
         peaks = measured_peaks()

@@ -91,7 +91,8 @@ struct T2Params {
   int col_bytes;                  // NCG * plane_rows * 16
   int stage_stride, wbytes;       // wbytes = size of one weight buffer (largest layer)
   long long* dbg;                 // optional [gridDim][T2_NDBG] cycle counters (HONK_TC2_DEBUG)
-  int mode;                       // debug kernel only: 1 = MMA issue alone (no copies, waits or epilogue; results are garbage)
+  int mode;                       // debug kernel only (results are garbage): 1 = MMA issue alone (no copies, waits or epilogue),
+                                  // 2 = epilogue without its global loads/stores and math, 3 = epilogue without its TMEM loads/stores
   // Per-layer tables live in the kernel parameter (constant) bank so that the MMA warp's descriptor
   // arithmetic stays on the uniform datapath (no R2UR per tcgen05.mma operand).
   T2Layer layers[T2_MAXL + 1];
@@ -173,6 +174,40 @@ __device__ __forceinline__ void issue_mmas(uint64_t a_hi, uint32_t a_lo, uint32_
     mma_f16_ss(d1, ad, bd, id1, 1);
     if (WRAP) mma_f16_ss(d2, ad, bd + static_cast<uint64_t>(b2), id2, 1);
   }
+}
+
+// Second half of a task in ONE instruction sequence: the two look-ahead probes are issued first, then (one elected
+// lane) four MMAs and up to three commits, and only then are the probe results combined - so the probes' latency
+// overlaps the MMA issue instead of stalling this warp between the two halves of a task.
+__device__ __forceinline__ uint32_t probe_issue4_commit(uint32_t pa, uint32_t pap, uint32_t pb, uint32_t pbp, uint32_t d1,
+                                                        uint32_t id1, uint64_t a0, uint64_t a1, uint64_t a2, uint64_t a3, uint64_t b0,
+                                                        uint64_t b1, uint64_t b2, uint64_t b3, uint32_t c_empty, uint32_t c_f1,
+                                                        uint32_t c_f2) {
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred p, q, pe, pt, pc1, pc2;\n"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "mbarrier.test_wait.parity.shared::cta.b64 q, [%3], %4;\n"
+      "elect.sync _|pe, 0xFFFFFFFF;\n"
+      "setp.eq.u32 pt, %5, %5;\n"
+      "setp.ne.and.b32 pc1, %16, 0, pe;\n"
+      "setp.ne.and.b32 pc2, %17, 0, pe;\n"
+      "@pe tcgen05.mma.cta_group::1.kind::f16 [%5], %7, %11, %6, pt;\n"
+      "@pe tcgen05.mma.cta_group::1.kind::f16 [%5], %8, %12, %6, pt;\n"
+      "@pe tcgen05.mma.cta_group::1.kind::f16 [%5], %9, %13, %6, pt;\n"
+      "@pe tcgen05.mma.cta_group::1.kind::f16 [%5], %10, %14, %6, pt;\n"
+      "@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%15];\n"
+      "@pc1 tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%16];\n"
+      "@pc2 tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%17];\n"
+      "and.pred p, p, q;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(pa), "r"(pap), "r"(pb), "r"(pbp), "r"(d1), "r"(id1), "l"(a0), "l"(a1), "l"(a2), "l"(a3), "l"(b0), "l"(b1), "l"(b2),
+        "l"(b3), "r"(c_empty), "r"(c_f1), "r"(c_f2)
+      : "memory");
+  return ok;
 }
 
 template <int NCG, bool DBG>
@@ -368,6 +403,31 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
               // Look one task ahead while the queued MMAs drain: probe (never block on) the barriers the next
               // task of this segment needs, so that its issue can start without a serialized poll.
               pre = false;
+              if (NMMA - NSPLIT == 4 && !conv0 && !wrap && !(DBG && p.mode == 1)) {
+                // fast path (every regular task of res15): probes, second-half MMAs and commits in one sequence
+                const bool has_next = t + 1 < n_in;
+                const uint32_t st1 = (st + 1 == T2_NSTAGE) ? 0 : st + 1;
+                const uint32_t par1 = (st + 1 == T2_NSTAGE) ? stpar ^ 1 : stpar;
+                const uint32_t g2 = static_cast<uint32_t>(gc + 2);
+                const bool touch = jc + 1 < jend;                        // next task first-touches block gc + 2
+                const uint32_t pa = has_next ? a_full + 8 * st1 : a_full + 8 * st, pap = has_next ? par1 : stpar;
+                const uint32_t pb = (has_next && touch) ? a_acc_empty + 8 * (g2 % NSLOT) : pa;
+                const uint32_t pbp = (has_next && touch) ? ((g2 / NSLOT) & 1) ^ 1 : pap;
+                uint64_t ad[4], bd[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  const int ii = NSPLIT + i, kh = ii / NKC, kc = ii - kh * NKC;
+                  ad[i] = a_hi | static_cast<uint64_t>(a_st + kc * pr2 + kh * d);
+                  bd[i] = b_hi | static_cast<uint64_t>(b_f + ii * 6 * NB);
+                }
+                const uint32_t ok = probe_issue4_commit(
+                    pa, pap, pb, pbp, d1, id1, ad[0], ad[1], ad[2], ad[3], bd[0], bd[1], bd[2], bd[3], a_empty + 8 * st,
+                    lo_in ? a_acc_full + 8 * (static_cast<uint32_t>(gc - 1) % NSLOT) : 0u,
+                    (t == n_in - 1 && c_in) ? a_acc_full + 8 * (static_cast<uint32_t>(gc) % NSLOT) : 0u);
+                __syncwarp();
+                pre = ok && has_next;
+                if (DBG && has_next) { n_task += 1; n_hit += pre; }
+              } else {
               if (t + 1 < n_in && !(DBG && p.mode == 1)) {
                 const uint32_t st1 = (st + 1 == T2_NSTAGE) ? 0 : st + 1;
                 const uint32_t par1 = (st + 1 == T2_NSTAGE) ? stpar ^ 1 : stpar;
@@ -391,6 +451,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
                 if (t == n_in - 1 && c_in) commit(a_acc_full + 8 * (static_cast<uint32_t>(gc) % NSLOT));
               }
               __syncwarp();
+              }
               a_st += stage16;
               if (++st == T2_NSTAGE) { st = 0; stpar ^= 1; a_st = a_st0; }
             }
@@ -435,7 +496,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
           unsigned char* Qs = p.Q + static_cast<long long>(slot) * p.slot_stride + (T2_PAD + h) * 16;
           unsigned char* Ps = p.P + static_cast<long long>(slot) * p.slot_stride + (T2_PAD + h) * 16;
           unsigned char* outb = (L & 1) ? Ps : Qs;            // conv0 -> Q; odd: Q -> P; even: P (+Q residual) -> Q in place
-          const bool ld_res = add_res && valid;
+          const bool ld_res = add_res && valid && !(DBG && p.mode == 2);
           float psum[NB];
           if (last) {
 #pragma unroll
@@ -468,12 +529,18 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
               fence_after();
               uint32_t v[NB];
               const uint32_t taddr = tmem + (static_cast<uint32_t>(quad * 32) << 16) + sl * NB;
+              if (DBG && p.mode == 3) {
 #pragma unroll
-              for (int c = 0; c < NB / 16; ++c) tmem_ld16(taddr + c * 16, *reinterpret_cast<uint32_t(*)[16]>(&v[c * 16]));
-              tmem_ld_wait();
+                for (int c = 0; c < NB; ++c) v[c] = 0;
+              } else {
 #pragma unroll
-              for (int c = 0; c < NB / 16; ++c) tmem_zero16(taddr + c * 16);   // the slot goes back cleared (completes below)
-              if (!last) {
+                for (int c = 0; c < NB / 16; ++c) tmem_ld16(taddr + c * 16, *reinterpret_cast<uint32_t(*)[16]>(&v[c * 16]));
+                tmem_ld_wait();
+#pragma unroll
+                for (int c = 0; c < NB / 16; ++c) tmem_zero16(taddr + c * 16);   // the slot goes back cleared (completes below)
+              }
+              if (DBG && p.mode == 2) {
+              } else if (!last) {
 #pragma unroll
                 for (int c = 0; c < NCG; ++c) {
                   uint32_t w4[4];

@@ -29,13 +29,13 @@
 // their per-tap weights are the hi/lo f16 halves of -sum_ci W*scale*mean, so exactly the in-range
 // taps subtract the mean - the same result as zero padding applied after bn_i.
 //
-// Scheduling.  A team of 4 CTAs (consecutive blockIdx) owns K = 3 clips at a time and runs them
-// through all layers in lockstep (A.L, B.L, C.L, A.L+1, ...), so the team-wide "layer L of clip A
+// Scheduling.  A team of 4 CTAs (consecutive blockIdx) owns K = 2 clips at a time and runs them
+// through all layers in lockstep (A.L, B.L, A.L+1, ...), so the team-wide "layer L of clip A
 // done" flag (a release counter in global memory) is hidden behind the other clips' work.  Each
 // CTA owns whole chains (or chain segments with one halo input column per cut).  Roles: warp 0 =
 // bulk-copy (TMA) producer, warp 1 = MMA issuer, warps 2-9 = epilogue (TMEM -> ReLU + residual ->
 // f16 -> L2; two groups of 4 warps take alternate columns), warp 10 = flag signaller.
-// Working set: 37 teams x 3 clips x 2 buffers x 449 KB = 100 MB.
+// Working set: 37 teams x 2 clips x 2 buffers x 449 KB = 66 MB, L2-resident.
 #include "res_tc.cuh"
 #include "umma.cuh"
 
@@ -655,7 +655,8 @@ struct ResTc2Plan {
   int plane_rows = 117, col_bytes = 0, stage_stride = 0, wbytes = 0, smem_bytes = 0;
   long long slot_stride = 0, x0_clip_stride = 0;
   int max_teams = 37;
-  int K = 3;                      // clips per team in flight: 37 teams x 3 x 2 buffers x 449 KB = 100 MB of L2
+  int K = 2;                      // clips per team in flight: 37 teams x 2 x 2 buffers x 449 KB = 66 MB of L2 (K = 3: 100 MB starts
+                                  // evicting dirty activations to HBM, and the extra DRAM power costs SM clock under the power cap)
   std::vector<T2Layer> layers;    // [0] = conv0, [1..n_layers] = the C->C layers
   unsigned char* d_wpack = nullptr;
   float* d_wout = nullptr;

@@ -3,7 +3,9 @@
 #include "model.cuh"
 
 #include <cmath>
+#include <algorithm>
 #include <cstdlib>
+#include <vector>
 
 using namespace honk;
 
@@ -364,23 +366,20 @@ extern "C" int honk_model_forward_pcm(const honk_model* m, const honk_frontend* 
 // ------------------------------------------------------------------------------------------
 namespace {
 
-struct HostPipe {                       // second stream + events of one call, released on every exit path
+struct HostPipe {                       // copy stream + events of one call, released on every exit path
   cudaStream_t copy = nullptr;
-  cudaEvent_t copied[2] = {nullptr, nullptr}, done[2] = {nullptr, nullptr}, start = nullptr;
-  int init() {
+  std::vector<cudaEvent_t> copied;
+  cudaEvent_t start = nullptr;
+  int init(size_t n_chunks) {
     HONK_CUDA(cudaStreamCreateWithFlags(&copy, cudaStreamNonBlocking));
-    for (int k = 0; k < 2; ++k) {
-      HONK_CUDA(cudaEventCreateWithFlags(&copied[k], cudaEventDisableTiming));
-      HONK_CUDA(cudaEventCreateWithFlags(&done[k], cudaEventDisableTiming));
-    }
+    copied.assign(n_chunks, nullptr);
+    for (size_t k = 0; k < n_chunks; ++k) HONK_CUDA(cudaEventCreateWithFlags(&copied[k], cudaEventDisableTiming));
     HONK_CUDA(cudaEventCreateWithFlags(&start, cudaEventDisableTiming));
     return HONK_OK;
   }
   ~HostPipe() {
-    for (int k = 0; k < 2; ++k) {
-      if (copied[k]) cudaEventDestroy(copied[k]);
-      if (done[k]) cudaEventDestroy(done[k]);
-    }
+    for (cudaEvent_t e : copied)
+      if (e) cudaEventDestroy(e);
     if (start) cudaEventDestroy(start);
     if (copy) cudaStreamDestroy(copy);
   }
@@ -388,15 +387,34 @@ struct HostPipe {                       // second stream + events of one call, r
 
 int pcm_elem_bytes(int dtype) { return dtype == HONK_PCM_I16 ? 2 : (dtype == HONK_PCM_F32 ? 4 : 8); }
 
-// Chunk size of the host pipeline: about HONK_HOST_CHUNKS (default 6) pieces, cut on the boundary at which
-// the persistent conv kernel's teams are all busy, so chunking costs no partially filled wave.
-int64_t host_chunk_clips(const honk_model* m, int64_t n_clips) {
-  if (n_clips <= 1024) return n_clips;
-  int pieces = 6;
-  if (const char* e = getenv("HONK_HOST_CHUNKS")) pieces = std::max(1, std::min(64, atoi(e)));
+// Chunk schedule of the host pipeline.  The whole batch is staged in device memory, so the copy stream never waits
+// for a buffer; PCIe moves a clip about four times faster than the kernels consume it, so only the FIRST chunk's copy
+// is exposed.  It is therefore small (HONK_HOST_FIRST_WAVES, default 4 waves) and the following chunks grow by 3x
+// (each one's copy still ends before the previous one's kernels do), up to half the batch.  Every chunk is a whole
+// number of waves - the clip count at which all teams of the persistent conv kernel are busy - so chunking costs no
+// partially filled wave.  HONK_HOST_CHUNKS=n forces n equal chunks instead.
+std::vector<int64_t> host_chunk_plan(const honk_model* m, int64_t n_clips) {
+  std::vector<int64_t> plan;
+  if (n_clips <= 0) return plan;
   const int64_t wave = m->tc2 ? honk::res_tc2_wave_clips(m->tc2) : 128;
-  const int64_t chunk = ((n_clips + pieces - 1) / pieces + wave - 1) / wave * wave;
-  return std::min(chunk, n_clips);
+  if (const char* e = getenv("HONK_HOST_CHUNKS")) {
+    const int pieces = std::max(1, std::min(64, atoi(e)));
+    const int64_t chunk = std::min(n_clips, ((n_clips + pieces - 1) / pieces + wave - 1) / wave * wave);
+    for (int64_t c0 = 0; c0 < n_clips; c0 += chunk) plan.push_back(std::min(chunk, n_clips - c0));
+    return plan;
+  }
+  int64_t first = 4;
+  if (const char* e = getenv("HONK_HOST_FIRST_WAVES")) first = std::max(1, std::min(1 << 20, atoi(e)));
+  const int64_t cap = std::max(wave, (n_clips / 2 + wave - 1) / wave * wave);
+  int64_t next = first * wave, left = n_clips;
+  while (left > 0) {
+    int64_t c = std::min(std::min(next, cap), left);
+    if (left - c < first * wave) c = left;                 // no sliver at the end
+    plan.push_back(c);
+    left -= c;
+    next *= 3;
+  }
+  return plan;
 }
 
 }  // namespace
@@ -404,10 +422,11 @@ int64_t host_chunk_clips(const honk_model* m, int64_t n_clips) {
 extern "C" int64_t honk_model_workspace_bytes_pcm_host(const honk_model* m, const honk_frontend* fe, int64_t n_clips,
                                                        int64_t n_samples, int dtype) {
   if (!m || !fe || n_clips <= 0) return 0;
-  const int64_t chunk = host_chunk_clips(m, n_clips);
-  const int64_t staging = align_up(chunk * n_samples * pcm_elem_bytes(dtype), 256);
+  const std::vector<int64_t> plan = host_chunk_plan(m, n_clips);
+  const int64_t largest = *std::max_element(plan.begin(), plan.end());
+  const int64_t staging = align_up(n_clips * n_samples * pcm_elem_bytes(dtype), 256);
   const int64_t logits = align_up(n_clips * m->cfg.n_labels * 4, 256);
-  return 2 * staging + logits + honk_model_workspace_bytes_pcm(m, fe, chunk, n_samples);
+  return staging + logits + honk_model_workspace_bytes_pcm(m, fe, largest, n_samples);
 }
 
 extern "C" int honk_model_forward_pcm_host(const honk_model* m, const honk_frontend* fe, const void* h_pcm, int dtype,
@@ -423,36 +442,39 @@ extern "C" int honk_model_forward_pcm_host(const honk_model* m, const honk_front
              HONK_ERR_WORKSPACE, "workspace too small");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int eb = pcm_elem_bytes(dtype);
-  const int64_t chunk = host_chunk_clips(m, n_clips);
-  const int64_t staging = align_up(chunk * n_samples * eb, 256);
+  const std::vector<int64_t> plan = host_chunk_plan(m, n_clips);
+  const int64_t staging = align_up(n_clips * n_samples * eb, 256);
   const int64_t logits_bytes = align_up(n_clips * m->cfg.n_labels * 4, 256);
   char* base = static_cast<char*>(d_workspace);
-  char* stage[2] = {base, base + staging};
-  float* d_logits = reinterpret_cast<float*>(base + 2 * staging);
-  char* inner = base + 2 * staging + logits_bytes;
-  const int64_t inner_bytes = workspace_bytes - 2 * staging - logits_bytes;
+  float* d_logits = reinterpret_cast<float*>(base + staging);
+  char* inner = base + staging + logits_bytes;
+  const int64_t inner_bytes = workspace_bytes - staging - logits_bytes;
   HostPipe hp;
-  HONK_TRY(hp.init());
+  HONK_TRY(hp.init(plan.size()));
   // the scratch may have been handed out in the order of `s`: the copy stream must not run ahead of that
   HONK_CUDA(cudaEventRecord(hp.start, s));
   HONK_CUDA(cudaStreamWaitEvent(hp.copy, hp.start, 0));
-  int i = 0;
-  for (int64_t c0 = 0; c0 < n_clips; c0 += chunk, ++i) {
-    const int64_t nc = std::min(chunk, n_clips - c0);
-    const int b = i & 1;
-    if (i >= 2) HONK_CUDA(cudaStreamWaitEvent(hp.copy, hp.done[b], 0));      // chunk i-2 no longer reads this buffer
+  int64_t c0 = 0;
+  for (size_t i = 0; i < plan.size(); ++i) {                // all copies are queued first: the copy engine runs ahead
+    const int64_t nc = plan[i];
     const char* src = static_cast<const char*>(h_pcm) + c0 * clip_stride * eb;
+    char* dst = base + c0 * n_samples * eb;
     if (clip_stride == n_samples) {
-      HONK_CUDA(cudaMemcpyAsync(stage[b], src, static_cast<size_t>(nc * n_samples * eb), cudaMemcpyHostToDevice, hp.copy));
+      HONK_CUDA(cudaMemcpyAsync(dst, src, static_cast<size_t>(nc * n_samples * eb), cudaMemcpyHostToDevice, hp.copy));
     } else {
-      HONK_CUDA(cudaMemcpy2DAsync(stage[b], static_cast<size_t>(n_samples * eb), src, static_cast<size_t>(clip_stride * eb),
+      HONK_CUDA(cudaMemcpy2DAsync(dst, static_cast<size_t>(n_samples * eb), src, static_cast<size_t>(clip_stride * eb),
                                   static_cast<size_t>(n_samples * eb), static_cast<size_t>(nc), cudaMemcpyHostToDevice, hp.copy));
     }
-    HONK_CUDA(cudaEventRecord(hp.copied[b], hp.copy));
-    HONK_CUDA(cudaStreamWaitEvent(s, hp.copied[b], 0));
-    HONK_TRY(honk_model_forward_pcm(m, fe, stage[b], dtype, nc, n_samples, n_samples, d_logits + c0 * m->cfg.n_labels, inner,
-                                    inner_bytes, s));
-    HONK_CUDA(cudaEventRecord(hp.done[b], s));
+    HONK_CUDA(cudaEventRecord(hp.copied[i], hp.copy));
+    c0 += nc;
+  }
+  c0 = 0;
+  for (size_t i = 0; i < plan.size(); ++i) {
+    const int64_t nc = plan[i];
+    HONK_CUDA(cudaStreamWaitEvent(s, hp.copied[i], 0));
+    HONK_TRY(honk_model_forward_pcm(m, fe, base + c0 * n_samples * eb, dtype, nc, n_samples, n_samples,
+                                    d_logits + c0 * m->cfg.n_labels, inner, inner_bytes, s));
+    c0 += nc;
   }
   HONK_CUDA(cudaMemcpyAsync(h_logits, d_logits, static_cast<size_t>(n_clips * m->cfg.n_labels * 4), cudaMemcpyDeviceToHost, s));
   HONK_CUDA(cudaStreamSynchronize(s));

@@ -215,7 +215,10 @@ def run_reference(args):
 def workload_config(args, world):
     return {
         "workload": "%s MFCC+CNN inference, %d synthetic 1-s 16 kHz int16 clips per GPU "
-                    "(BASELINE configs[3]: res15 batch 65536 over 8 GPUs = 8192/GPU)" % (args.model, args.clips_per_gpu),
+                    "(%s)" % (args.model, args.clips_per_gpu,
+                              "BASELINE configs[3]: res15 batch 65536 over 8 GPUs = 8192/GPU" if args.model == "res15" else
+                              "BASELINE configs[2]: res8 batch 16384 at 1/2/4/8 GPUs" if args.model == "res8" else
+                              "not the headline configuration"),
         "clips_per_gpu": args.clips_per_gpu, "global_clips": args.clips_per_gpu * world,
         "n_samples": 16000, "n_labels": 12, "parallelism": "clip shards, %d independent rank(s), one all_gather of logits" % world,
         "l2": "inputs %.0f MB per GPU per step > 126 MB L2 (no flush needed)" % (args.clips_per_gpu * 32000 / 1e6),
@@ -366,7 +369,9 @@ def main():
             avg_launch_ms = t_ms / n_launch
             achieved = flops_layer_clip * n_layers * clips_done / (t_ms * 1e-3) / 1e12
             roof = {"bound": "tensor",
-                    "kernel": ("tc2_res_kernel (persistent: conv0 + %d dilated 3x3 C->C layers, tcgen05 ring-accumulate)" % n_layers)
+                    "kernel": (("tc2_res_kernel (persistent: %d 3x3 C->C layers on %d-clip time-stacked tiles, tcgen05 ring-accumulate)"
+                                % (n_layers, 113 // (H + 1)) if "res_pool" in cfg else
+                                "tc2_res_kernel (persistent: conv0 + %d dilated 3x3 C->C layers, tcgen05 ring-accumulate)" % n_layers))
                               if persistent else "tc_conv_kernel (dilated 3x3 C->C implicit GEMM, tcgen05)",
                     "achieved": achieved, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
                     "frac": achieved / peaks["tf_sustained"], "peak_source": peaks["source"] + " bf16 sustained",

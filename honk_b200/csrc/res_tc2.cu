@@ -68,7 +68,8 @@ struct T2Seg {                    // a run of output columns of one chain, owned
 
 struct T2Layer {
   int d;                          // dilation
-  int flags;                      // bit0: add residual, bit1: last layer (pool, no store), bit2: conv0 (input = x0 image)
+  int flags;                      // bit0: add residual, bit1: last layer (pool, no store), bit2: conv0 (input = x0 image),
+                                  // bit3: input = y0 (pooled conv0 output of a stacked group), bit4: residual = y0
   int w_off;                      // byte offset of this layer's packed weights
   int w_bytes;                    // 3 * nkc B tiles
   int n_seg[T2_G];
@@ -78,6 +79,7 @@ struct T2Layer {
 struct T2Params {
   const unsigned char* wpack;
   const unsigned char* x0;        // [n_clips][W][H+2][8] f16: (hi, lo, hi, 0...) of the MFCCs, zero first/last row
+  const unsigned char* y0;        // pooled models: [n_clips] buffers in the activation layout holding avgpool(relu(conv0))
   unsigned char* P;               // [n_slots] activation buffers
   unsigned char* Q;               // [n_slots]
   float* pool;                    // [n_clips][NB]
@@ -86,6 +88,11 @@ struct T2Params {
   long long x0_clip_stride;
   int n_layers, n_clips, n_slots; // n_layers counts the C->C layers; layers[0] is conv0
   int K;                          // clips per team in flight
+  int G;                          // CTAs per team (<= T2_G)
+  int L0;                         // first layer the kernel runs: 0 = conv0 (un-pooled), 1 = conv1 (pooled: conv0 + pool ran before)
+  int S, Hp1;                     // pooled models stack S clips along the time axis with one zero row between them: a "clip"
+                                  // of this kernel is such a group, rows h with h % Hp1 == Hp1 - 1 are the separators (never
+                                  // stored, so they stay zero = the time padding of both neighbours); un-pooled: S = 1, Hp1 = H + 1
   int H, W;
   int plane_rows;                 // H + T2_PAD
   int col_bytes;                  // NCG * plane_rows * 16
@@ -232,7 +239,8 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
   const uint32_t a_acc_full = keep(smem_u32(&bar_acc_full[0])), a_acc_empty = keep(smem_u32(&bar_acc_empty[0]));
   const uint32_t a_wfull = keep(smem_u32(&bar_wfull[0])), a_wfree = keep(smem_u32(&bar_wfree[0]));
   const uint32_t a_done = keep(smem_u32(&bar_done[0]));
-  const int team = blockIdx.x / T2_G, rank = blockIdx.x % T2_G, n_teams = gridDim.x / T2_G;
+  const int G = p.G, L0 = p.L0;
+  const int team = blockIdx.x / G, rank = blockIdx.x % G, n_teams = gridDim.x / G;
   unsigned char* stages = smem;
   unsigned char* wbuf = smem + T2_NSTAGE * p.stage_stride;
 
@@ -282,7 +290,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
       const long long t_start = clock64();
       for (int pair = team; pair < n_pairs; pair += n_teams, ++piter) {
         const int nab = min(K, p.n_clips - K * pair);
-        for (int L = 0; L <= p.n_layers; ++L, ++q) {
+        for (int L = L0; L <= p.n_layers; ++L, ++q) {
           const T2Layer& ly = p.layers[L];
           if (q == 0) {
             mbar_expect_tx(a_wfull, ly.w_bytes);
@@ -299,10 +307,14 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
             if (from_x0) {
               in = p.x0 + static_cast<long long>(clip) * p.x0_clip_stride;
               // conv0 writes Q[slot]: the team's last-layer MMAs of the previous clip in this slot still read it
-              if (piter > 0) T2_TIMED(t_flag, wait_flag(p.flags + (clip - K * n_teams), T2_G * (p.n_layers + 1)));
+              if (piter > 0) T2_TIMED(t_flag, wait_flag(p.flags + (clip - K * n_teams), G * (p.n_layers + 1)));
+            } else if (ly.flags & 8) {
+              in = p.y0 + static_cast<long long>(clip) * p.slot_stride + (T2_PAD - d) * 16;
+              // this layer writes P[slot]: the team's last layers of the previous group in this slot still read P and Q
+              if (piter > 0) T2_TIMED(t_flag, wait_flag(p.flags + (clip - K * n_teams), G * (p.n_layers + 1 - L0)));
             } else {
               in = ((L & 1) ? p.Q : p.P) + static_cast<long long>(slot) * p.slot_stride + (T2_PAD - d) * 16;
-              T2_TIMED(t_flag, wait_flag(p.flags + clip, T2_G * L));        // every CTA of the team finished layer L-1
+              T2_TIMED(t_flag, wait_flag(p.flags + clip, G * (L - L0)));    // every CTA of the team finished layer L-1
               fence_proxy_async_global();
             }
             for (int s = 0; s < nseg; ++s) {
@@ -321,7 +333,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
           const bool more = (L < p.n_layers) || (pair + n_teams < n_pairs);
           if (more) {
             const uint32_t qn = q + 1;
-            const T2Layer& nl = p.layers[L < p.n_layers ? L + 1 : 0];
+            const T2Layer& nl = p.layers[L < p.n_layers ? L + 1 : L0];
             if (qn >= 2) mbar_wait(a_wfree + 8 * (qn & 1), ((qn - 2) >> 1) & 1);
             mbar_expect_tx(a_wfull + 8 * (qn & 1), nl.w_bytes);
             bulk_load(smem_u32(wbuf + (qn & 1) * p.wbytes), p.wpack + nl.w_off, nl.w_bytes, a_wfull + 8 * (qn & 1));
@@ -347,7 +359,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
     const long long t_start = clock64();
     for (int pair = team; pair < n_pairs; pair += n_teams) {
       const int nab = min(K, p.n_clips - K * pair);
-      for (int L = 0; L <= p.n_layers; ++L, ++q) {
+      for (int L = L0; L <= p.n_layers; ++L, ++q) {
         const T2Layer& ly = p.layers[L];
         const uint32_t d = ly.d;
         const bool conv0 = ly.flags & 4;
@@ -478,14 +490,15 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
     // its two constant-one input channels (mean shift, exact at the zero-padded borders).
     const int ew = warp - 2, quad = warp & 3, half = ew >> 2;
     const int h = quad * 32 + lane;
-    const bool valid = h < p.H;
+    const int sub = h / p.Hp1;                              // clip of a stacked group this row belongs to
+    const bool valid = h < p.H && (h - sub * p.Hp1) < p.Hp1 - 1;
     const int etid = ew * 32 + lane;
     uint32_t g = 0, ev = 0;
     long long t_wait = 0;
     const long long t_start_e = clock64();
     for (int pair = team; pair < n_pairs; pair += n_teams) {
       const int nab = min(K, p.n_clips - K * pair);
-      for (int L = 0; L <= p.n_layers; ++L) {
+      for (int L = L0; L <= p.n_layers; ++L) {
         const T2Layer& ly = p.layers[L];
         const int d = ly.d, flags = ly.flags;
         const bool add_res = flags & 1, last = flags & 2;
@@ -496,6 +509,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
           unsigned char* Qs = p.Q + static_cast<long long>(slot) * p.slot_stride + (T2_PAD + h) * 16;
           unsigned char* Ps = p.P + static_cast<long long>(slot) * p.slot_stride + (T2_PAD + h) * 16;
           unsigned char* outb = (L & 1) ? Ps : Qs;            // conv0 -> Q; odd: Q -> P; even: P (+Q residual) -> Q in place
+          const unsigned char* resb = (flags & 16) ? p.y0 + static_cast<long long>(clip) * p.slot_stride + (T2_PAD + h) * 16 : Qs;
           const bool ld_res = add_res && valid && !(DBG && p.mode == 2);
           float psum[NB];
           if (last) {
@@ -514,7 +528,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
             for (int c = 0; c < NCG; ++c) rv[c] = make_uint4(0, 0, 0, 0);
             if (ld_res && o0 < jlim) {
 #pragma unroll
-              for (int c = 0; c < NCG; ++c) rv[c] = ldcg16(Qs + off + c * plane_bytes);
+              for (int c = 0; c < NCG; ++c) rv[c] = ldcg16(resb + off + c * plane_bytes);
             }
             for (int o = o0; o < jlim; o += 2, gi += 2, off += cstep) {
               const uint32_t sl = gi % NSLOT;
@@ -523,7 +537,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
               for (int c = 0; c < NCG; ++c) rc[c] = rv[c];
               if (ld_res && o + 2 < jlim) {
 #pragma unroll
-                for (int c = 0; c < NCG; ++c) rv[c] = ldcg16(Qs + off + cstep + c * plane_bytes);
+                for (int c = 0; c < NCG; ++c) rv[c] = ldcg16(resb + off + cstep + c * plane_bytes);
               }
               T2_TIMED(t_wait, mbar_wait(a_acc_full + 8 * sl, (gi / NSLOT) & 1));
               fence_after();
@@ -570,12 +584,16 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
             }
           }
           if (last) {
+            // rows of one warp belong to at most two clips of a stacked group (un-pooled: S = 1, one pass)
+            const int s_lo = __shfl_sync(0xffffffffu, sub, 0), s_hi = min(__shfl_sync(0xffffffffu, sub, 31), p.S - 1);
+            for (int sc = s_lo; sc <= s_hi; ++sc) {
 #pragma unroll
-            for (int k = 0; k < NB; ++k) {
-              float sum = psum[k];
+              for (int k = 0; k < NB; ++k) {
+                float sum = (sub == sc) ? psum[k] : 0.f;          // invalid rows never accumulated
 #pragma unroll
-              for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-              if (lane == 0) atomicAdd(p.pool + static_cast<long long>(clip) * NB + k, sum);
+                for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                if (lane == 0) atomicAdd(p.pool + (static_cast<long long>(clip) * p.S + sc) * NB + k, sum);
+              }
             }
           }
           __syncwarp();
@@ -594,7 +612,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
       uint32_t ev = 0;
       for (int pair = team; pair < n_pairs; pair += n_teams) {
         const int nab = min(K, p.n_clips - K * pair);
-        for (int L = 0; L <= p.n_layers; ++L) {             // L = 0 is conv0
+        for (int L = L0; L <= p.n_layers; ++L) {            // L = 0 is conv0
           for (int ab = 0; ab < nab; ++ab, ++ev) {
             mbar_wait(a_done + 8 * (ev & 3), (ev >> 2) & 1);
             fence_proxy_async_global();
@@ -633,6 +651,74 @@ __global__ void __launch_bounds__(256) tc2_pack_x0_kernel(const float* __restric
   }
 }
 
+// Pooled models: conv0 (1 -> C, 3x3, pad 1, bias-free) + ReLU + AvgPool(ph, pw) in FP32 (model.py:107-111), written as
+// the persistent kernel's input image y0[group][w][cg][plane_rows][8] f16: S clips stacked along the time axis, one zero
+// row between them, T2_PAD zero rows above every plane, constant-one in the two spare channels at real positions.
+// One CTA per group; every 16-byte unit of the group's buffer is written (zeros included), so y0 needs no memset.
+// Thread t serves channel group t / 64 with its 72 weights in registers.
+template <int NCG>
+__global__ void __launch_bounds__(NCG * 64) tc2_conv0_pool_kernel(const float* __restrict__ mfcc, const float* __restrict__ w0,
+                                                                  unsigned char* __restrict__ y0, int n_clips, int H0, int W0, int ph,
+                                                                  int pw, int Hc, int Wc, int S, int plane_rows, long long slot_stride) {
+  constexpr int N = NCG * 8;
+  extern __shared__ float xs[];                          // [S][(H0+2)][(W0+2)] zero-bordered MFCC images
+  const int group = blockIdx.x, tid = threadIdx.x;
+  const int Wp = W0 + 2, img = (H0 + 2) * Wp;
+  for (int i = tid; i < S * img; i += NCG * 64) {
+    const int sc = i / img, r = i - sc * img;
+    const int y = r / Wp - 1, x = r % Wp - 1;
+    const long long clip = static_cast<long long>(group) * S + sc;
+    xs[i] = (clip < n_clips && y >= 0 && y < H0 && x >= 0 && x < W0) ? __ldg(mfcc + (clip * H0 + y) * W0 + x) : 0.f;
+  }
+  const int cg = tid >> 6, t64 = tid & 63;
+  float wr[9][8];
+#pragma unroll
+  for (int tap = 0; tap < 9; ++tap)
+#pragma unroll
+    for (int k = 0; k < 8; ++k) wr[tap][k] = __ldg(w0 + tap * N + cg * 8 + k);
+  __syncthreads();
+  const float inv = 1.f / static_cast<float>(ph * pw);
+  const int Hp1 = Hc + 1, Hk = S * Hp1 - 1;
+  uint4* dst = reinterpret_cast<uint4*>(y0 + static_cast<long long>(group) * slot_stride);
+  for (int j = t64; j < Wc * plane_rows; j += 64) {
+    const int w = j / plane_rows, prow = j - w * plane_rows;
+    const int hk = prow - T2_PAD;
+    uint4 o = make_uint4(0, 0, 0, 0);
+    if (hk >= 0 && hk < Hk) {
+      const int sc = hk / Hp1, h = hk - sc * Hp1;
+      if (h < Hc && static_cast<long long>(group) * S + sc < n_clips) {
+        const float* xi = xs + sc * img;
+        float acc[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+        for (int py = 0; py < ph; ++py)
+          for (int px = 0; px < pw; ++px) {
+            const int y = h * ph + py, x = w * pw + px;    // conv output position (time, coefficient)
+            float t[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) t[k] = 0.f;
+#pragma unroll
+            for (int tap = 0; tap < 9; ++tap) {
+              const float v = xi[(y + tap / 3) * Wp + x + tap % 3];
+#pragma unroll
+              for (int k = 0; k < 8; ++k) t[k] = fmaf(v, wr[tap][k], t[k]);
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[k] += fmaxf(t[k], 0.f);
+          }
+        o.x = pack_h2(acc[0] * inv, acc[1] * inv);
+        o.y = pack_h2(acc[2] * inv, acc[3] * inv);
+        o.z = pack_h2(acc[4] * inv, acc[5] * inv);
+        o.w = pack_h2(acc[6] * inv, acc[7] * inv);
+        if (cg == NCG - 1) o.w = 0x3C003C00u;              // the two constant-one channels
+      }
+    }
+    dst[(static_cast<long long>(w) * NCG + cg) * plane_rows + prow] = o;
+  }
+  // zero rows below the last plane of the last column (its bottom padding) up to the end of the buffer
+  for (long long i = static_cast<long long>(Wc) * NCG * plane_rows + tid; i < slot_stride / 16; i += NCG * 64) dst[i] = make_uint4(0, 0, 0, 0);
+}
+
 // logits = W'(pool / HW) + b' with the last BatchNorm folded into W', b'
 __global__ void tc2_tail_kernel(const float* __restrict__ pool, const float* __restrict__ wout,
                                 const float* __restrict__ bout, float* __restrict__ logits, int n_clips, int N, int L,
@@ -655,6 +741,10 @@ struct ResTc2Plan {
   int plane_rows = 117, col_bytes = 0, stage_stride = 0, wbytes = 0, smem_bytes = 0;
   long long slot_stride = 0, x0_clip_stride = 0;
   int max_teams = 37;
+  int G = T2_G;                   // CTAs per team
+  int S = 1, Hc = 101;            // pooled models: S clips of Hc rows stacked along time per kernel "clip" (H = S*(Hc+1)-1)
+  int pool_h = 0, pool_w = 0, H0 = 101, W0 = 40;
+  float* d_w0 = nullptr;          // pooled models: conv0 weights [9][NB] float (conv0 + pool run in tc2_conv0_pool_kernel)
   int K = 2;                      // clips per team in flight: 37 teams x 2 x 2 buffers x 449 KB = 66 MB of L2 (K = 3: 100 MB starts
                                   // evicting dirty activations to HBM, and the extra DRAM power costs SM clock under the power cap)
   std::vector<T2Layer> layers;    // [0] = conv0, [1..n_layers] = the C->C layers
@@ -684,7 +774,7 @@ int up(ResTc2Plan* p, const std::vector<T>& h, T** d) {
 
 // Distributes the chains of dilation d over the T2_G CTAs of a team: whole chains by longest-
 // processing-time first; when there are fewer chains than CTAs each chain is cut into equal runs.
-bool plan_segments(T2Layer& ly, int W, int d) {
+bool plan_segments(T2Layer& ly, int W, int d, int G) {
   for (int k = 0; k < T2_G; ++k) ly.n_seg[k] = 0;
   const int n_chain = std::min(d, W);
   auto add = [&](int rank, int r, int j0, int n_out, int len) {
@@ -699,8 +789,8 @@ bool plan_segments(T2Layer& ly, int W, int d) {
     s.pad[0] = s.pad[1] = s.pad[2] = 0;
     return true;
   };
-  if (n_chain < T2_G) {
-    const int pieces = T2_G / n_chain;             // n_chain is 1 or 2 here
+  if (n_chain < G) {
+    const int pieces = G / n_chain;                // n_chain is 1 or 2 here
     for (int r = 0; r < n_chain; ++r) {
       const int len = (W - r + d - 1) / d;
       for (int k = 0; k < pieces; ++k) {
@@ -716,7 +806,7 @@ bool plan_segments(T2Layer& ly, int W, int d) {
   int load[T2_G] = {0, 0, 0, 0};
   for (auto& c : chains) {
     int best = 0;
-    for (int k = 1; k < T2_G; ++k)
+    for (int k = 1; k < G; ++k)
       if (load[k] < load[best]) best = k;
     if (!add(best, c.second, 0, c.first, c.first)) return false;
     load[best] += c.first;
@@ -736,16 +826,40 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
   *out = nullptr;
   const honk_model_config& c = m->cfg;
   const int C = c.n_feature_maps;
-  if (c.family != HONK_FAMILY_RES || C > 46 || c.res_pool[0] > 0) return HONK_OK;   // two spare channels carry the mean shift
-  if (m->H0 > 112 || m->H0 < 8 || m->W0 < T2_G || m->W0 > 1024 || c.n_layers < 1 || c.n_layers > T2_MAXL) return HONK_OK;
+  if (c.family != HONK_FAMILY_RES || C > 46) return HONK_OK;   // two spare channels carry the mean shift
+  const bool pooled = c.res_pool[0] > 0;
+  // Pooled models (res8: 25 x 13, res26: 50 x 20 maps): S clips are stacked along the time axis with one zero row
+  // between them, so one 128-row MMA tile carries S clips (res26: 50+1+50 = 101 rows, res8: 4*26-1 = 103 rows) and the
+  // kernel sees an un-dilated "clip" of H = S*(Hc+1)-1 rows whose separator rows are never stored.
+  const int S = pooled ? std::max(1, std::min(8, 113 / (m->Hr + 1))) : 1;
+  const int Hk = pooled ? S * (m->Hr + 1) - 1 : m->H0, Wk = pooled ? m->Wr : m->W0;
+  int G = T2_G;
+  if (pooled) {
+    // measured (scripts/pooled_sweep.py, profiles/r03_pooled_sweep.json): res8's 13 columns are too few to share (one CTA
+    // per group, no cross-CTA halo), res26's 20 columns run best on pairs of CTAs
+    G = Wk <= 16 ? 1 : 2;
+    if (const char* e = getenv("HONK_TC2_G")) {
+      const int g = atoi(e);
+      if (g == 1 || g == 2 || g == 4) G = g;
+    }
+    if (c.use_dilation && c.n_layers > 3) return HONK_OK;   // no reference config pools and dilates; one separator row = d 1
+  }
+  if (Hk > 112 || Hk < 8 || Wk < G || Wk > 1024 || c.n_layers < 1 || c.n_layers > T2_MAXL) return HONK_OK;
   for (int i = 1; i <= c.n_layers; ++i)
     if ((c.use_dilation ? (1 << ((i - 1) / 3)) : 1) > T2_PAD) return HONK_OK;
   std::unique_ptr<ResTc2Plan, void (*)(ResTc2Plan*)> p(new ResTc2Plan(), res_tc2_plan_free);
   p->C = C;
   p->ncg = C <= 30 ? 4 : 6;
   p->NB = p->ncg * 8;
-  p->H = m->H0;
-  p->W = m->W0;
+  p->H = Hk;
+  p->W = Wk;
+  p->G = G;
+  p->S = S;
+  p->Hc = pooled ? m->Hr : m->H0;
+  p->pool_h = pooled ? c.res_pool[0] : 0;
+  p->pool_w = pooled ? c.res_pool[1] : 0;
+  p->H0 = m->H0;
+  p->W0 = m->W0;
   p->n_layers = c.n_layers;
   p->n_labels = c.n_labels;
   p->plane_rows = p->H + T2_PAD;
@@ -755,13 +869,13 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
   // a stage holds planes 0..ncg-1 of one column; the kh taps over-read up to 127 + 2*16 rows of the last plane
   p->stage_stride = static_cast<int>(align_up((p->ncg - 1) * p->plane_rows * 16 + (128 + 2 * T2_PAD) * 16, 128));
   const int tile_bytes = 6 * p->NB * 16;                       // one (kh, kc) B tile: 2 K halves x 3NB rows x 8 halves
-  const int w0_bytes = 3 * tile_bytes;
+  const int w0_bytes = pooled ? 0 : 3 * tile_bytes;
   p->wbytes = 3 * (p->ncg / 2) * tile_bytes;
   p->smem_bytes = T2_NSTAGE * p->stage_stride + 2 * p->wbytes;
   int max_smem = 0;
   HONK_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, m->device));
   if (p->smem_bytes + 2048 > max_smem) return HONK_OK;
-  p->max_teams = std::max(1, m->n_sms / T2_G);
+  p->max_teams = std::max(1, m->n_sms / G);
   if (const char* e = getenv("HONK_TC2_K")) p->K = std::max(1, std::min(8, atoi(e)));
   const int N = p->NB, ncg = p->ncg, NKC = ncg / 2;
 
@@ -777,7 +891,15 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
   }
   std::vector<T2Layer> layers(c.n_layers + 1);
   std::vector<unsigned char> wpack(static_cast<size_t>(w0_bytes) + static_cast<size_t>(c.n_layers) * p->wbytes, 0);
-  {
+  if (pooled) {
+    // conv0 + ReLU + AvgPool run before the persistent kernel, in FP32 (tc2_conv0_pool_kernel): weights [tap][NB]
+    memset(&layers[0], 0, sizeof(T2Layer));
+    const HostTensor& w = m->host.at("conv0.weight");
+    std::vector<float> w0(9 * N, 0.f);
+    for (int co = 0; co < C; ++co)
+      for (int tap = 0; tap < 9; ++tap) w0[tap * N + co] = w.data[co * 9 + tap];
+    HONK_TRY(up(p.get(), w0, &p->d_w0));
+  } else {
     // conv0 (bias-free, model.py:107): B tile kh = [K half][n = blk*NB + co][8]; input channels 0..2 = (x_hi, x_lo, x_hi)
     // meet (w_hi, w_hi, w_lo); everything else (the whole second K half included) is zero.
     T2Layer& ly = layers[0];
@@ -786,7 +908,7 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
     ly.flags = 4;
     ly.w_off = 0;
     ly.w_bytes = w0_bytes;
-    if (!plan_segments(ly, p->W, 1)) return HONK_OK;
+    if (!plan_segments(ly, p->W, 1, G)) return HONK_OK;
     const HostTensor& w = m->host.at("conv0.weight");
     __half* hw = reinterpret_cast<__half*>(wpack.data());
     for (int kh = 0; kh < 3; ++kh)
@@ -808,10 +930,10 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
     memset(&ly, 0, sizeof(ly));
     ly.d = c.use_dilation ? (1 << ((L - 1) / 3)) : 1;
     const bool even = (L % 2 == 0), last = (L == c.n_layers);
-    ly.flags = (even ? 1 : 0) | (last ? 2 : 0);
+    ly.flags = (even ? 1 : 0) | (last ? 2 : 0) | ((pooled && L == 1) ? 8 : 0) | ((pooled && L == 2) ? 16 : 0);
     ly.w_off = w0_bytes + (L - 1) * p->wbytes;
     ly.w_bytes = p->wbytes;
-    if (!plan_segments(ly, p->W, ly.d)) return HONK_OK;
+    if (!plan_segments(ly, p->W, ly.d, G)) return HONK_OK;
     // B operand: [i = kh*NKC + kc][K half][n = blk*NB + co][ci % 8], blk <-> kw = 2 - blk.
     //   ci <  C       : W[co][ci][kh][kw] * scale_{L-1}[ci]                 (BatchNorm scale of the producer)
     //   ci = NB-1/NB-2: hi / lo halves of  -sum_ci W*scale*mean_{L-1}[ci]   per TAP; these input channels hold
@@ -860,6 +982,12 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
     HONK_TRY(up(p.get(), hwv, &p->d_wout));
     HONK_TRY(up(p.get(), hb, &p->d_bout));
   }
+  if (pooled) {
+    const int sm0 = S * (p->H0 + 2) * (p->W0 + 2) * static_cast<int>(sizeof(float));
+    if (sm0 + 1024 > max_smem) return HONK_OK;
+    HONK_TRY(set_smem(tc2_conv0_pool_kernel<6>, sm0));
+    HONK_TRY(set_smem(tc2_conv0_pool_kernel<4>, sm0));
+  }
   if (ncg == 6) {
     HONK_TRY(set_smem(tc2_res_kernel<6, false>, p->smem_bytes));
     HONK_TRY(set_smem(tc2_res_kernel<6, true>, p->smem_bytes));
@@ -871,35 +999,52 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
   return HONK_OK;
 }
 
-static int tc2_teams(const ResTc2Plan* p, int64_t n_clips) {
-  return static_cast<int>(std::min<int64_t>(p->max_teams, (n_clips + p->K - 1) / p->K));
+// kernel "clips": groups of S stacked clips for the pooled models
+static int64_t tc2_groups(const ResTc2Plan* p, int64_t n_clips) { return (n_clips + p->S - 1) / p->S; }
+static int tc2_teams(const ResTc2Plan* p, int64_t n_groups) {
+  return static_cast<int>(std::min<int64_t>(p->max_teams, (n_groups + p->K - 1) / p->K));
 }
 
-int res_tc2_wave_clips(const ResTc2Plan* p) { return p->max_teams * p->K; }
+int res_tc2_wave_clips(const ResTc2Plan* p) { return p->max_teams * p->K * p->S; }
 
 int64_t res_tc2_workspace_bytes(const ResTc2Plan* p, int64_t n_clips) {
-  const int n_slots = p->K * tc2_teams(p, n_clips);
+  const int64_t n_groups = tc2_groups(p, n_clips);
+  const int n_slots = p->K * tc2_teams(p, n_groups);
   Arena a(nullptr, 0);
   a.take<unsigned char>(2ll * n_slots * p->slot_stride);
-  a.take<float>(n_clips * p->NB);
-  a.take<unsigned int>(n_clips);
-  a.take<unsigned char>(n_clips * p->x0_clip_stride);
+  a.take<float>(n_groups * p->S * p->NB);
+  a.take<unsigned int>(n_groups);
+  if (p->pool_h > 0) a.take<unsigned char>(n_groups * p->slot_stride);
+  else a.take<unsigned char>(n_clips * p->x0_clip_stride);
   return align_up(a.off, 256);
 }
 
 int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, float* d_logits, void* ws, int64_t ws_bytes,
                     cudaStream_t s) {
-  const int teams = tc2_teams(p, n_clips), n_slots = p->K * teams;
+  const bool pooled = p->pool_h > 0;
+  const int64_t n_groups = tc2_groups(p, n_clips);
+  const int teams = tc2_teams(p, n_groups), n_slots = p->K * teams;
   Arena ar(ws, ws_bytes);
   unsigned char* act = ar.take<unsigned char>(2ll * n_slots * p->slot_stride);
-  float* pool = ar.take<float>(n_clips * p->NB);
-  unsigned int* flags = ar.take<unsigned int>(n_clips);
+  float* pool = ar.take<float>(n_groups * p->S * p->NB);
+  unsigned int* flags = ar.take<unsigned int>(n_groups);
   const int64_t zero_bytes = ar.off;
-  unsigned char* x0 = ar.take<unsigned char>(n_clips * p->x0_clip_stride);
+  unsigned char* x0 = pooled ? ar.take<unsigned char>(n_groups * p->slot_stride) : ar.take<unsigned char>(n_clips * p->x0_clip_stride);
   HONK_CHECK(ar.ok(), HONK_ERR_WORKSPACE, "internal: tcgen05 workspace overrun");
   // zero rows between planes must be zero; pool sums and layer counters start at zero
   HONK_CUDA(cudaMemsetAsync(act, 0, static_cast<size_t>(zero_bytes), s));
-  {
+  if (pooled) {
+    ProfSpan span("res_conv0_pool", s);
+    const size_t smem = static_cast<size_t>(p->S) * (p->H0 + 2) * (p->W0 + 2) * sizeof(float);
+    const dim3 grid(static_cast<unsigned>(n_groups));
+    if (p->ncg == 6)
+      tc2_conv0_pool_kernel<6><<<grid, 6 * 64, smem, s>>>(d_mfcc, p->d_w0, x0, static_cast<int>(n_clips), p->H0, p->W0, p->pool_h, p->pool_w,
+                                                         p->Hc, p->W, p->S, p->plane_rows, p->slot_stride);
+    else
+      tc2_conv0_pool_kernel<4><<<grid, 4 * 64, smem, s>>>(d_mfcc, p->d_w0, x0, static_cast<int>(n_clips), p->H0, p->W0, p->pool_h, p->pool_w,
+                                                         p->Hc, p->W, p->S, p->plane_rows, p->slot_stride);
+    HONK_LAUNCH_CHECK();
+  } else {
     ProfSpan span("res_pack_x0", s);
     tc2_pack_x0_kernel<<<static_cast<unsigned>(n_clips), 256, p->H * (p->W + 1) * sizeof(float), s>>>(d_mfcc, x0, p->H, p->W);
     HONK_LAUNCH_CHECK();
@@ -908,6 +1053,11 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
   for (size_t i = 0; i < p->layers.size(); ++i) a.layers[i] = p->layers[i];
   a.wpack = p->d_wpack;
   a.x0 = x0;
+  a.y0 = x0;
+  a.G = p->G;
+  a.L0 = pooled ? 1 : 0;
+  a.S = p->S;
+  a.Hp1 = pooled ? p->Hc + 1 : p->H + 1;
   a.P = act;
   a.Q = act + static_cast<long long>(n_slots) * p->slot_stride;
   a.pool = pool;
@@ -915,7 +1065,7 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
   a.slot_stride = p->slot_stride;
   a.x0_clip_stride = p->x0_clip_stride;
   a.n_layers = p->n_layers;
-  a.n_clips = static_cast<int>(n_clips);
+  a.n_clips = static_cast<int>(n_groups);
   a.n_slots = n_slots;
   a.K = p->K;
   a.H = p->H;
@@ -937,7 +1087,7 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
   }
   {
     ProfSpan span("res_conv", s);
-    const dim3 grid(teams * T2_G);
+    const dim3 grid(teams * p->G);
     if (p->ncg == 6) {
       if (dbg) tc2_res_kernel<6, true><<<grid, T2_THREADS, p->smem_bytes, s>>>(a);
       else tc2_res_kernel<6, false><<<grid, T2_THREADS, p->smem_bytes, s>>>(a);
@@ -952,7 +1102,7 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
     HONK_CUDA(cudaStreamSynchronize(s));
     HONK_CUDA(cudaMemcpy(h.data(), a.dbg, h.size() * sizeof(long long), cudaMemcpyDeviceToHost));
     double m[T2_NDBG] = {0};
-    const int nb = teams * T2_G;
+    const int nb = teams * p->G;
     for (int b = 0; b < nb; ++b)
       for (int k = 0; k < T2_NDBG; ++k) m[k] += static_cast<double>(h[b * T2_NDBG + k]) / nb;
     fprintf(stderr, "tc2 dbg (mean cycles/CTA, %d CTAs, %lld clips): producer total %.0f flag-wait %.0f stage-empty-wait %.0f | "
@@ -964,7 +1114,7 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
     ProfSpan span("res_tail", s);
     const int total = static_cast<int>(n_clips) * p->n_labels;
     tc2_tail_kernel<<<(total + 127) / 128, 128, 0, s>>>(pool, p->d_wout, p->d_bout, d_logits, static_cast<int>(n_clips), p->NB,
-                                                        p->n_labels, 1.0f / static_cast<float>(p->H * p->W));
+                                                        p->n_labels, 1.0f / static_cast<float>(p->Hc * p->W));
     HONK_LAUNCH_CHECK();
   }
   return HONK_OK;

@@ -219,3 +219,34 @@ def test_res_depth_sweep(n_layers, pool, maps):
     y = m(torch.from_numpy(mf).cuda()).cpu().numpy()
     err = np.abs(y - ref).max() / np.abs(ref).max()
     assert err <= TOL[m.native_path], (n_layers, pool, maps, m.native_path, err)
+
+
+@pytest.mark.parametrize("G,K", [("1", "3"), ("2", "2"), ("4", "4")])
+@pytest.mark.parametrize("name,n", [("res8", 1), ("res8", 7), ("res8", 2500), ("res26", 3), ("res26", 1000),
+                                    ("res8-narrow", 1301), ("res26-narrow", 66)])
+def test_pooled_stacked_groups(name, n, G, K, monkeypatch):
+    # pooled res8 / res26 on the persistent kernel: S clips stacked along time per 128-row tile (res8: 4, res26: 2).
+    # Ragged last groups, several waves of groups per team (slot reuse) and every team size, row for row against
+    # the FP32 CUDA-core path (itself pinned to the golden logits above).
+    import honk_b200 as hb
+    monkeypatch.setenv("HONK_TC2_G", G)
+    monkeypatch.setenv("HONK_TC2_K", K)
+    cfg = dict(hb.find_config(name))
+    cfg["n_labels"] = 12
+    base = synth.make_clips(64, start=7000)
+    pre = hb.AudioPreprocessor()
+    mf64 = pre.compute_mfccs_batch(torch.from_numpy(base).cuda())
+    sd = synth.make_state_dict(name, cfg, seed=11, calib_mfcc=mf64[:16].cpu().numpy())
+    reps = n // 64 + 1
+    mf = mf64.repeat(reps, 1, 1)[:n].contiguous()
+    mf[1::3] = mf[1::3].flip(1) * 0.5                     # neighbouring clips of a group differ
+    m32 = build(name, cfg, sd, 1)
+    m16 = build(name, cfg, sd, 0)
+    ref = m32(mf).cpu().numpy()
+    y = m16(mf).cpu().numpy()
+    assert m16.native_path == "tcgen05-f16" and m32.native_path == "cuda-core-f32"
+    err = np.abs(y - ref).max() / np.abs(ref).max()
+    assert err <= TOL["tcgen05-f16"], (name, n, err)
+    # the same clip gives the same logits wherever it sits in a group and whichever team ran it
+    if n > 64 * 3:
+        assert np.abs(y[0] - y[192]).max() <= 1e-4 * np.abs(ref).max()

@@ -317,7 +317,7 @@ def main():
         N.profile_enable(False)
         ms = e0.elapsed_time(e1) / max(1, args.steps)
         spans = {}
-        for sp in ("frontend", "res_pack_x0", "res_conv0", "res_conv", "res_tail", "cnn_pack_x8", "cnn_conv", "cnn_fc", "f32_model"):
+        for sp in ("frontend", "res_pack_x0", "res_conv0_pool", "res_conv0", "res_conv", "res_tail", "cnn_pack_x8", "cnn_conv", "cnn_fc", "f32_model"):
             t, n = N.profile_get(sp)
             if n:
                 spans[sp] = (t, n)
@@ -375,7 +375,8 @@ def main():
                               if persistent else "tc_conv_kernel (dilated 3x3 C->C implicit GEMM, tcgen05)",
                     "achieved": achieved, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
                     "frac": achieved / peaks["tf_sustained"], "peak_source": peaks["source"] + " bf16 sustained",
-                    "traffic": recorded_traffic("tc2_res_kernel", B) if persistent and name == "res15" else None,
+                    "traffic": (recorded_traffic("tc2_res_kernel" if name == "res15" else "tc2_res_kernel:" + name, B)
+                                if persistent else None),
                     "avg_launch_ms": avg_launch_ms, "launches_per_step": n_launch / args.steps,
                     "flops_per_launch": flops_layer_clip * n_layers * clips_done / n_launch,
                     "share_of_step": t_ms / (ms * args.steps)}

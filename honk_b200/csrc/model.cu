@@ -362,6 +362,87 @@ extern "C" int honk_model_forward_pcm(const honk_model* m, const honk_frontend* 
 }
 
 // ------------------------------------------------------------------------------------------
+// /listen: sliding windows over one buffer (server.py:99-112, service.py:106-110)
+// ------------------------------------------------------------------------------------------
+namespace {
+
+// One thread per label sums the max-probabilities of the windows it won, in window order and in double like
+// the Python loop's float accumulation (server.py:105-108); thread 0 also finds the first window that would
+// have ended the command_tagging loop (server.py:109-110).
+__global__ void listen_reduce_kernel(const int* __restrict__ labels, const float* __restrict__ probs, long long n_windows,
+                                     int n_labels, int keyword, float min_prob, double* __restrict__ sums,
+                                     int* __restrict__ counts, int* __restrict__ first_hit) {
+  const int l = blockIdx.x * blockDim.x + threadIdx.x;
+  if (l < n_labels) {
+    double acc = 0.0;
+    int cnt = 0;
+    for (long long w = 0; w < n_windows; ++w)
+      if (labels[w] == l) {
+        acc += static_cast<double>(probs[w]);
+        ++cnt;
+      }
+    sums[l] = acc;
+    counts[l] = cnt;
+  }
+  if (l == 0) {
+    int hit = -1;
+    for (long long w = 0; w < n_windows && hit < 0; ++w)
+      if (labels[w] == keyword && probs[w] >= min_prob) hit = static_cast<int>(w);
+    *first_hit = hit;
+  }
+}
+
+int64_t listen_windows(int64_t n_total, int64_t window, int64_t hop) {
+  return (window > 0 && hop > 0 && n_total >= window) ? 1 + (n_total - window) / hop : 0;
+}
+
+}  // namespace
+
+extern "C" int64_t honk_listen_num_windows(int64_t n_total_samples, int64_t window, int64_t hop) {
+  return listen_windows(n_total_samples, window, hop);
+}
+
+extern "C" int64_t honk_listen_workspace_bytes(const honk_model* m, const honk_frontend* fe, int64_t n_total_samples,
+                                               int64_t window, int64_t hop) {
+  const int64_t nw = listen_windows(n_total_samples, window, hop);
+  if (!m || !fe || nw <= 0) return 0;
+  return align_up(nw * m->cfg.n_labels * 4, 256) + 2 * align_up(nw * 4, 256) + honk_model_workspace_bytes_pcm(m, fe, nw, window);
+}
+
+extern "C" int honk_listen(const honk_model* m, const honk_frontend* fe, const void* d_pcm, int dtype, int64_t n_total_samples,
+                           int64_t window, int64_t hop, int32_t keyword, float min_keyword_prob, double* d_sums,
+                           int32_t* d_counts, int32_t* d_first_hit, void* d_workspace, int64_t workspace_bytes, void* stream) {
+  HONK_CHECK(m && fe, HONK_ERR_INVALID, "honk_listen: null handle");
+  HONK_CHECK(window > 0 && hop > 0 && n_total_samples >= 0, HONK_ERR_INVALID, "honk_listen: bad window/hop");
+  HONK_CHECK(d_sums && d_counts && d_first_hit, HONK_ERR_INVALID, "honk_listen: null output");
+  const int64_t nw = listen_windows(n_total_samples, window, hop);
+  const int L = m->cfg.n_labels;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (nw == 0) {                                  // shorter than one window: the reference loop runs zero times
+    HONK_CUDA(cudaMemsetAsync(d_sums, 0, sizeof(double) * L, s));
+    HONK_CUDA(cudaMemsetAsync(d_counts, 0, sizeof(int32_t) * L, s));
+    HONK_CUDA(cudaMemsetAsync(d_first_hit, 0xFF, sizeof(int32_t), s));
+    return HONK_OK;
+  }
+  HONK_CHECK(d_pcm, HONK_ERR_INVALID, "honk_listen: null buffer");
+  HONK_CHECK(d_workspace && workspace_bytes >= honk_listen_workspace_bytes(m, fe, n_total_samples, window, hop),
+             HONK_ERR_WORKSPACE, "workspace too small");
+  Arena ar(d_workspace, workspace_bytes);
+  float* logits = ar.take<float>(nw * L);
+  int* labels = ar.take<int>(nw);
+  float* probs = ar.take<float>(nw);
+  const int64_t used = align_up(ar.off, 256);
+  char* inner = static_cast<char*>(d_workspace) + used;
+  // window w = samples [w*hop, w*hop + window): rows of the same buffer with clip_stride = hop
+  HONK_TRY(honk_model_forward_pcm(m, fe, d_pcm, dtype, nw, window, hop, logits, inner, workspace_bytes - used, stream));
+  HONK_TRY(honk_label_from_logits(logits, nw, L, labels, probs, stream));
+  listen_reduce_kernel<<<(L + 127) / 128, 128, 0, s>>>(labels, probs, nw, L, keyword, min_keyword_prob, d_sums, d_counts,
+                                                       d_first_hit);
+  HONK_LAUNCH_CHECK();
+  return HONK_OK;
+}
+
+// ------------------------------------------------------------------------------------------
 // host-buffer pipeline
 // ------------------------------------------------------------------------------------------
 namespace {

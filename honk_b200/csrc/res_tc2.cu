@@ -655,8 +655,9 @@ __global__ void __launch_bounds__(256) tc2_pack_x0_kernel(const float* __restric
 // the persistent kernel's input image y0[group][w][cg][plane_rows][8] f16: S clips stacked along the time axis, one zero
 // row between them, T2_PAD zero rows above every plane, constant-one in the two spare channels at real positions.
 // One CTA per group; every 16-byte unit of the group's buffer is written (zeros included), so y0 needs no memset.
-// Thread t serves channel group t / 64 with its 72 weights in registers.
-template <int NCG>
+// Thread t serves channel group t / 64 with its 72 weights in registers; a pooled cell's (PH+2) x (PW+2) input patch is
+// read from shared memory once and reused by its PH*PW conv positions.  PH = 0: pool window taken from ph, pw at run time.
+template <int NCG, int PH, int PW>
 __global__ void __launch_bounds__(NCG * 64) tc2_conv0_pool_kernel(const float* __restrict__ mfcc, const float* __restrict__ w0,
                                                                   unsigned char* __restrict__ y0, int n_clips, int H0, int W0, int ph,
                                                                   int pw, int Hc, int Wc, int S, int plane_rows, long long slot_stride) {
@@ -664,11 +665,12 @@ __global__ void __launch_bounds__(NCG * 64) tc2_conv0_pool_kernel(const float* _
   extern __shared__ float xs[];                          // [S][(H0+2)][(W0+2)] zero-bordered MFCC images
   const int group = blockIdx.x, tid = threadIdx.x;
   const int Wp = W0 + 2, img = (H0 + 2) * Wp;
+  const int n_here = static_cast<int>(min(static_cast<long long>(S), n_clips - static_cast<long long>(group) * S));
   for (int i = tid; i < S * img; i += NCG * 64) {
     const int sc = i / img, r = i - sc * img;
     const int y = r / Wp - 1, x = r % Wp - 1;
     const long long clip = static_cast<long long>(group) * S + sc;
-    xs[i] = (clip < n_clips && y >= 0 && y < H0 && x >= 0 && x < W0) ? __ldg(mfcc + (clip * H0 + y) * W0 + x) : 0.f;
+    xs[i] = (sc < n_here && y >= 0 && y < H0 && x >= 0 && x < W0) ? __ldg(mfcc + (clip * H0 + y) * W0 + x) : 0.f;
   }
   const int cg = tid >> 6, t64 = tid & 63;
   float wr[9][8];
@@ -676,47 +678,77 @@ __global__ void __launch_bounds__(NCG * 64) tc2_conv0_pool_kernel(const float* _
   for (int tap = 0; tap < 9; ++tap)
 #pragma unroll
     for (int k = 0; k < 8; ++k) wr[tap][k] = __ldg(w0 + tap * N + cg * 8 + k);
-  __syncthreads();
-  const float inv = 1.f / static_cast<float>(ph * pw);
   const int Hp1 = Hc + 1, Hk = S * Hp1 - 1;
   uint4* dst = reinterpret_cast<uint4*>(y0 + static_cast<long long>(group) * slot_stride);
-  for (int j = t64; j < Wc * plane_rows; j += 64) {
-    const int w = j / plane_rows, prow = j - w * plane_rows;
-    const int hk = prow - T2_PAD;
-    uint4 o = make_uint4(0, 0, 0, 0);
-    if (hk >= 0 && hk < Hk) {
-      const int sc = hk / Hp1, h = hk - sc * Hp1;
-      if (h < Hc && static_cast<long long>(group) * S + sc < n_clips) {
-        const float* xi = xs + sc * img;
-        float acc[8];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) acc[k] = 0.f;
-        for (int py = 0; py < ph; ++py)
-          for (int px = 0; px < pw; ++px) {
-            const int y = h * ph + py, x = w * pw + px;    // conv output position (time, coefficient)
-            float t[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) t[k] = 0.f;
-#pragma unroll
-            for (int tap = 0; tap < 9; ++tap) {
-              const float v = xi[(y + tap / 3) * Wp + x + tap % 3];
-#pragma unroll
-              for (int k = 0; k < 8; ++k) t[k] = fmaf(v, wr[tap][k], t[k]);
-            }
-#pragma unroll
-            for (int k = 0; k < 8; ++k) acc[k] += fmaxf(t[k], 0.f);
-          }
-        o.x = pack_h2(acc[0] * inv, acc[1] * inv);
-        o.y = pack_h2(acc[2] * inv, acc[3] * inv);
-        o.z = pack_h2(acc[4] * inv, acc[5] * inv);
-        o.w = pack_h2(acc[6] * inv, acc[7] * inv);
-        if (cg == NCG - 1) o.w = 0x3C003C00u;              // the two constant-one channels
+  // every unit that is not a real position of a present clip is zero: padding rows, separators, missing clips, tail
+  const int n_units = static_cast<int>(slot_stride / 16), n_plane_units = Wc * NCG * plane_rows;
+  for (int i = tid; i < n_units; i += NCG * 64) {
+    bool real = false;
+    if (i < n_plane_units) {
+      const int hk = i % plane_rows - T2_PAD;
+      if (hk >= 0 && hk < Hk) {
+        const int sc = hk / Hp1;
+        real = (hk - sc * Hp1) < Hc && sc < n_here;
       }
     }
-    dst[(static_cast<long long>(w) * NCG + cg) * plane_rows + prow] = o;
+    if (!real) dst[i] = make_uint4(0, 0, 0, 0);
   }
-  // zero rows below the last plane of the last column (its bottom padding) up to the end of the buffer
-  for (long long i = static_cast<long long>(Wc) * NCG * plane_rows + tid; i < slot_stride / 16; i += NCG * 64) dst[i] = make_uint4(0, 0, 0, 0);
+  __syncthreads();
+  const float inv = 1.f / static_cast<float>(ph * pw);
+  const int rows = n_here * Hc;                          // real rows of one column of the group
+  for (int j = t64; j < Wc * rows; j += 64) {
+    const int w = j / rows, r = j - w * rows;
+    const int sc = r / Hc, h = r - sc * Hc;
+    const float* xi = xs + sc * img + (h * ph) * Wp + w * pw;     // top-left of the cell's input patch (bordered image)
+    float acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+    if (PH > 0) {
+      float patch[(PH > 0 ? PH : 1) + 2][(PW > 0 ? PW : 1) + 2];
+#pragma unroll
+      for (int y = 0; y < PH + 2; ++y)
+#pragma unroll
+        for (int x = 0; x < PW + 2; ++x) patch[y][x] = xi[y * Wp + x];
+#pragma unroll
+      for (int py = 0; py < PH; ++py)
+#pragma unroll
+        for (int px = 0; px < PW; ++px) {
+          float t[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) t[k] = 0.f;
+#pragma unroll
+          for (int tap = 0; tap < 9; ++tap) {
+            const float v = patch[py + tap / 3][px + tap % 3];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) t[k] = fmaf(v, wr[tap][k], t[k]);
+          }
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[k] += fmaxf(t[k], 0.f);
+        }
+    } else {
+      for (int py = 0; py < ph; ++py)
+        for (int px = 0; px < pw; ++px) {
+          float t[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) t[k] = 0.f;
+#pragma unroll
+          for (int tap = 0; tap < 9; ++tap) {
+            const float v = xi[(py + tap / 3) * Wp + px + tap % 3];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) t[k] = fmaf(v, wr[tap][k], t[k]);
+          }
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[k] += fmaxf(t[k], 0.f);
+        }
+    }
+    uint4 o;
+    o.x = pack_h2(acc[0] * inv, acc[1] * inv);
+    o.y = pack_h2(acc[2] * inv, acc[3] * inv);
+    o.z = pack_h2(acc[4] * inv, acc[5] * inv);
+    o.w = pack_h2(acc[6] * inv, acc[7] * inv);
+    if (cg == NCG - 1) o.w = 0x3C003C00u;                // the two constant-one channels
+    dst[(static_cast<long long>(w) * NCG + cg) * plane_rows + T2_PAD + sc * Hp1 + h] = o;
+  }
 }
 
 // logits = W'(pool / HW) + b' with the last BatchNorm folded into W', b'
@@ -985,8 +1017,12 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
   if (pooled) {
     const int sm0 = S * (p->H0 + 2) * (p->W0 + 2) * static_cast<int>(sizeof(float));
     if (sm0 + 1024 > max_smem) return HONK_OK;
-    HONK_TRY(set_smem(tc2_conv0_pool_kernel<6>, sm0));
-    HONK_TRY(set_smem(tc2_conv0_pool_kernel<4>, sm0));
+    HONK_TRY(set_smem(tc2_conv0_pool_kernel<6, 4, 3>, sm0));
+    HONK_TRY(set_smem(tc2_conv0_pool_kernel<4, 4, 3>, sm0));
+    HONK_TRY(set_smem(tc2_conv0_pool_kernel<6, 2, 2>, sm0));
+    HONK_TRY(set_smem(tc2_conv0_pool_kernel<4, 2, 2>, sm0));
+    HONK_TRY(set_smem(tc2_conv0_pool_kernel<6, 0, 0>, sm0));
+    HONK_TRY(set_smem(tc2_conv0_pool_kernel<4, 0, 0>, sm0));
   }
   if (ncg == 6) {
     HONK_TRY(set_smem(tc2_res_kernel<6, false>, p->smem_bytes));
@@ -1037,12 +1073,16 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
     ProfSpan span("res_conv0_pool", s);
     const size_t smem = static_cast<size_t>(p->S) * (p->H0 + 2) * (p->W0 + 2) * sizeof(float);
     const dim3 grid(static_cast<unsigned>(n_groups));
-    if (p->ncg == 6)
-      tc2_conv0_pool_kernel<6><<<grid, 6 * 64, smem, s>>>(d_mfcc, p->d_w0, x0, static_cast<int>(n_clips), p->H0, p->W0, p->pool_h, p->pool_w,
-                                                         p->Hc, p->W, p->S, p->plane_rows, p->slot_stride);
-    else
-      tc2_conv0_pool_kernel<4><<<grid, 4 * 64, smem, s>>>(d_mfcc, p->d_w0, x0, static_cast<int>(n_clips), p->H0, p->W0, p->pool_h, p->pool_w,
-                                                         p->Hc, p->W, p->S, p->plane_rows, p->slot_stride);
+#define T2_C0(NCG_, PH_, PW_)                                                                                                   \
+  tc2_conv0_pool_kernel<NCG_, PH_, PW_><<<grid, NCG_ * 64, smem, s>>>(d_mfcc, p->d_w0, x0, static_cast<int>(n_clips), p->H0, p->W0, \
+                                                                      p->pool_h, p->pool_w, p->Hc, p->W, p->S, p->plane_rows, p->slot_stride)
+    const int pk = (p->pool_h == 4 && p->pool_w == 3) ? 1 : ((p->pool_h == 2 && p->pool_w == 2) ? 2 : 0);
+    if (p->ncg == 6) {
+      if (pk == 1) T2_C0(6, 4, 3); else if (pk == 2) T2_C0(6, 2, 2); else T2_C0(6, 0, 0);
+    } else {
+      if (pk == 1) T2_C0(4, 4, 3); else if (pk == 2) T2_C0(4, 2, 2); else T2_C0(4, 0, 0);
+    }
+#undef T2_C0
     HONK_LAUNCH_CHECK();
   } else {
     ProfSpan span("res_pack_x0", s);

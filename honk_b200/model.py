@@ -188,6 +188,15 @@ class SerializableModule(nn.Module):
         dev = self._device()
         return ops.model_forward_pcm(pcm, self._ensure_native(dev), audio_processor.handle, self.n_labels)
 
+    def listen(self, pcm, audio_processor, window=16000, hop=8000, keyword=-1, min_keyword_prob=0.85):
+        """One 1-D device buffer of samples -> ``(sums float64 [L], counts int32 [L], first_hit int32 [1])`` over
+        all sliding windows (server.py:99-112): the windows are read in place as overlapping rows."""
+        if self.training:
+            raise RuntimeError("honk_b200 implements the inference path only; call model.eval()")
+        dev = self._device()
+        return ops.listen(pcm, self._ensure_native(dev), audio_processor.handle, self.n_labels, int(window), int(hop),
+                          int(keyword), float(min_keyword_prob))
+
     def forward_pcm_host(self, pcm, audio_processor, out=None):
         """Host ``[B, n_samples]`` PCM -> host logits, copies overlapped with the kernels chunk by chunk."""
         if self.training:

@@ -125,3 +125,31 @@ def label_from_logits(logits: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]
 def _(logits):
     return (logits.new_empty((logits.shape[0],), dtype=torch.int32),
             logits.new_empty((logits.shape[0],), dtype=torch.float32))
+
+
+@torch.library.custom_op("honk_b200::listen", mutates_args=(), device_types="cuda")
+def listen(pcm: torch.Tensor, model: int, frontend: int, n_labels: int, window: int, hop: int, keyword: int,
+           min_keyword_prob: float) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """One device buffer of samples -> per-label probability sums (float64), per-label window counts and the
+    first window that ends the ``command_tagging`` loop (-1: none); server.py:99-112 in one C-ABI call."""
+    N.require_cuda(pcm, "pcm")
+    if pcm.dim() != 1:
+        raise ValueError("honk_b200: listen takes one 1-D buffer of samples")
+    pcm = pcm.contiguous()
+    sums = torch.empty((n_labels,), dtype=torch.float64, device=pcm.device)
+    counts = torch.empty((n_labels,), dtype=torch.int32, device=pcm.device)
+    first = torch.empty((1,), dtype=torch.int32, device=pcm.device)
+    L = N.lib()
+    ws_bytes = int(L.honk_listen_workspace_bytes(model, frontend, pcm.shape[0], window, hop))
+    ws = torch.empty((max(ws_bytes, 1),), dtype=torch.uint8, device=pcm.device)
+    with torch.cuda.device(pcm.device):
+        N.check(L.honk_listen(model, frontend, pcm.data_ptr(), N.pcm_dtype_code(pcm), pcm.shape[0], window, hop, keyword,
+                              min_keyword_prob, sums.data_ptr(), counts.data_ptr(), first.data_ptr(), ws.data_ptr(),
+                              ws_bytes, N.stream_ptr(pcm.device)))
+    return sums, counts, first
+
+
+@listen.register_fake
+def _(pcm, model, frontend, n_labels, window, hop, keyword, min_keyword_prob):
+    return (pcm.new_empty((n_labels,), dtype=torch.float64), pcm.new_empty((n_labels,), dtype=torch.int32),
+            pcm.new_empty((1,), dtype=torch.int32))

@@ -100,9 +100,28 @@ class TorchLabelService(LabelService):
         return self.label_batch([wav_data])[0]
 
     def listen(self, wav_data, stride_ms=500, min_keyword_prob=0.85, keyword="command", method="all_label"):
-        """Batched form of ``ListenEndpoint.POST`` (server.py:99-112): all 1-s windows at once."""
-        step = int(2 * 16000 * stride_ms / 1000)
-        windows = list(stride(wav_data, step, 2 * 16000))
+        """Batched form of ``ListenEndpoint.POST`` (server.py:99-112): the decompressed int16 buffer is copied to
+        the GPU once, its 1-s windows are read in place as overlapping rows (no window copies), and softmax,
+        argmax, the per-label sums and the ``command_tagging`` early-exit test run on the device (honk_listen);
+        one small device->host read returns the result."""
+        step = int(2 * 16000 * stride_ms / 1000)           # bytes, like the reference's stride() over the byte string
+        if step <= 0 or step % 2 or self.n_samples != 16000:
+            return self._listen_host(wav_data, step, min_keyword_prob, keyword, method)
+        a = np.frombuffer(wav_data, dtype=np.int16, count=len(wav_data) // 2)
+        if len(a) < self.n_samples:
+            return dict(contains_command=False) if method == "command_tagging" else {}
+        kw = self.labels.index(keyword) if keyword in self.labels else -1
+        with torch.no_grad():
+            pcm = torch.from_numpy(a.copy()).pin_memory().to(self.audio_processor.device, non_blocking=True)
+            sums, counts, first = self.model.listen(pcm, self.audio_processor, self.n_samples, step // 2, kw, min_keyword_prob)
+            sums, counts, first = sums.cpu().numpy(), counts.cpu().numpy(), int(first.cpu()[0])
+        if method == "command_tagging":
+            return dict(contains_command=first >= 0)
+        return {self.labels[i]: float(sums[i]) for i in range(len(self.labels)) if counts[i] > 0}
+
+    def _listen_host(self, wav_data, step, min_keyword_prob, keyword, method):
+        """Window extraction on the host for strides the in-place path does not cover (odd byte steps)."""
+        windows = list(stride(wav_data, max(step, 1), 2 * 16000))
         labels = {}
         for label, prob in self.label_batch(windows):
             labels[label] = labels.get(label, 0.0) + float(prob)

@@ -83,7 +83,8 @@ HONK_API int64_t honk_frontend_num_frames(const honk_frontend* fe, int64_t n_sam
 HONK_API int honk_frontend_get_dct(const honk_frontend* fe, double* h_out);
 HONK_API int honk_frontend_get_mel(const honk_frontend* fe, double* h_out);
 
-/* d_pcm: [n_clips, clip_stride] elements of `dtype`, first n_samples of each row used.
+/* d_pcm: [n_clips, clip_stride] elements of `dtype`, first n_samples of each row used; clip_stride <
+ * n_samples is allowed (overlapping rows = sliding windows over one buffer, service.py:106-110).
  * d_mfcc: float32 [n_clips, n_frames, n_dct_filters] (time-major, the layout
  * collate_fn's reshape(1,-1,40) and service.py's squeeze(2) give the model). */
 HONK_API int honk_frontend_mfcc(const honk_frontend* fe, const void* d_pcm, int dtype, int64_t n_clips,
@@ -171,6 +172,23 @@ HONK_API int64_t honk_model_workspace_bytes_pcm_host(const honk_model* m, const 
  * d_labels int32 [n_clips], d_probs float32 [n_clips] (either may be NULL). */
 HONK_API int honk_label_from_logits(const float* d_logits, int64_t n_clips, int32_t n_labels, int32_t* d_labels,
                            float* d_probs, void* stream);
+
+/* Batched form of ListenEndpoint.POST (server.py:99-112) over service.py:106-110's stride():
+ * d_pcm is ONE buffer of n_total_samples on the device; window w = samples [w*hop, w*hop + window)
+ * (n = honk_listen_num_windows = 1 + (n_total - window) / hop, 0 when shorter than a window) is read
+ * in place as a row of clip_stride = hop, so overlapping windows are never copied.  All windows go
+ * through front end + model + softmax/argmax in one pass; then, in window order,
+ *   d_sums[l]   float64 [n_labels]  sum of the winning probabilities of label l   (server.py:105-108)
+ *   d_counts[l] int32   [n_labels]  windows won by label l (0 => the label is absent from the dict)
+ *   d_first_hit int32   [1]         first window with label == keyword && prob >= min_keyword_prob,
+ *                                   -1 if none (method "command_tagging", server.py:109-110). */
+HONK_API int64_t honk_listen_num_windows(int64_t n_total_samples, int64_t window, int64_t hop);
+HONK_API int64_t honk_listen_workspace_bytes(const honk_model* m, const honk_frontend* fe, int64_t n_total_samples,
+                                    int64_t window, int64_t hop);
+HONK_API int honk_listen(const honk_model* m, const honk_frontend* fe, const void* d_pcm, int dtype,
+                int64_t n_total_samples, int64_t window, int64_t hop, int32_t keyword, float min_keyword_prob,
+                double* d_sums, int32_t* d_counts, int32_t* d_first_hit, void* d_workspace,
+                int64_t workspace_bytes, void* stream);
 
 /* Number of kernels the library has launched in this process (for bench.py's gpu_launches). */
 HONK_API int64_t honk_launch_count(void);

@@ -46,5 +46,20 @@ def test_listen_windows_and_model_type():
     for lab, p in per:
         ref[lab] = ref.get(lab, 0.0) + p
     assert set(agg) == set(ref) and all(abs(agg[k] - ref[k]) < 1e-5 for k in ref)
+    # the in-place device path (honk_listen: overlapping rows of one buffer) == the host-window path, for every
+    # stride, both methods, thresholds on either side of the winning probabilities, and the degenerate lengths
+    for ms in (500, 250, 100, 37):
+        step = int(2 * 16000 * ms / 1000)
+        host = svc._listen_host(long, step, 0.85, "command", "all_label")
+        dev = svc.listen(long, stride_ms=ms)
+        assert set(dev) == set(host) and all(abs(dev[k] - host[k]) < 1e-5 for k in host), ms
+    top = max(per, key=lambda lp: lp[1])
+    for thr in (top[1] - 1e-3, top[1] + 1e-3):
+        for kw in (top[0], "not-a-label"):
+            host = svc._listen_host(long, 16000, thr, kw, "command_tagging")
+            assert svc.listen(long, min_keyword_prob=thr, keyword=kw, method="command_tagging") == host
+    assert svc.listen(long[:31998]) == {} and svc.listen(long[:32000]) == svc._listen_host(long[:32000], 16000, 0.85, "x", "all_label")
+    assert svc.listen(long[:100], method="command_tagging") == dict(contains_command=False)
+    assert svc.listen(long[:32001]).keys() == svc.listen(long[:32000]).keys()
     with pytest.raises(RuntimeError):
         TorchLabelService(tsd, no_cuda=True, labels=LABELS, model_type=hb.ConfigType.RES8_NARROW)

@@ -23,7 +23,7 @@ EXPORTS = [
     "honk_frontend_mfcc", "honk_model_create", "honk_model_destroy", "honk_model_workspace_bytes",
     "honk_model_forward", "honk_model_forward_pcm", "honk_model_workspace_bytes_pcm",
     "honk_model_forward_pcm_host", "honk_model_workspace_bytes_pcm_host",
-    "honk_label_from_logits", "honk_listen", "honk_listen_num_windows", "honk_listen_workspace_bytes", "honk_launch_count", "honk_model_path", "honk_profile_enable",
+    "honk_label_from_logits", "honk_eval_metrics", "honk_load_audio", "honk_listen", "honk_listen_num_windows", "honk_listen_workspace_bytes", "honk_launch_count", "honk_model_path", "honk_profile_enable",
     "honk_profile_reset", "honk_profile_get",
 ]
 
@@ -88,6 +88,8 @@ def lib():
         L.honk_model_workspace_bytes_pcm_host.argtypes = [vp, vp, i64, i64, C.c_int]
         L.honk_model_workspace_bytes_pcm_host.restype = i64
         L.honk_label_from_logits.argtypes = [vp, i64, i32, vp, vp, vp]
+        L.honk_eval_metrics.argtypes = [vp, vp, i64, i32, vp, vp, vp, vp]
+        L.honk_load_audio.argtypes = [vp, i64, i64, vp, vp, vp, vp, vp, i32, vp, vp]
         L.honk_listen_num_windows.argtypes = [i64, i64, i64]
         L.honk_listen_num_windows.restype = i64
         L.honk_listen_workspace_bytes.argtypes = [vp, vp, i64, i64, i64]

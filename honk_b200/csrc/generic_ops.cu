@@ -173,6 +173,77 @@ __global__ void label_kernel(const float* __restrict__ logits, long long n, int 
   }
 }
 
+// print_eval's argmax == label count and CrossEntropyLoss's per-clip term (utils/train.py:41-46, 66-83): one warp
+// per clip, block-level reduction in a fixed order, one atomic per block.
+__global__ void __launch_bounds__(256) eval_metrics_kernel(const float* __restrict__ logits, const long long* __restrict__ labels,
+                                                           long long n, int L, int* __restrict__ pred,
+                                                           unsigned long long* __restrict__ correct, double* __restrict__ loss_sum) {
+  __shared__ double s_loss[8];
+  __shared__ int s_ok[8];
+  const long long clip = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  double loss = 0.0;
+  int ok = 0;
+  if (clip < n) {
+    const float* z = logits + clip * L;
+    float best = -INFINITY;
+    int arg = 0x7fffffff;
+    for (int i = lane; i < L; i += 32) {
+      const float v = z[i];
+      if (v > best) { best = v; arg = i; }
+    }
+    for (int o = 16; o; o >>= 1) {
+      const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+      if (ob > best || (ob == best && oa < arg)) { best = ob; arg = oa; }      // first maximum, like torch.max
+    }
+    double sum = 0.0;
+    for (int i = lane; i < L; i += 32) sum += exp(static_cast<double>(z[i]) - static_cast<double>(best));
+    for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const long long y = labels[clip];
+    if (lane == 0) {
+      if (pred) pred[clip] = arg;
+      ok = (static_cast<long long>(arg) == y);
+      if (y >= 0 && y < L) loss = log(sum) + static_cast<double>(best) - static_cast<double>(z[y]);   // logsumexp(z) - z[y]
+    }
+  }
+  if (lane == 0) { s_loss[wib] = loss; s_ok[wib] = ok; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    int c = 0;
+    for (int k = 0; k < 8; ++k) { t += s_loss[k]; c += s_ok[k]; }
+    atomicAdd(loss_sum, t);
+    atomicAdd(correct, static_cast<unsigned long long>(c));
+  }
+}
+
+// SpeechDataset.load_audio's arithmetic (utils/model.py:281-303) for a batch, given the random draws:
+// zero-pad to in_len (:297), time shift (:267-273: out[t] = x[t + shift], zero outside), then, where gain >= 0,
+// clip(gain * bg[off + t] + x, -1, 1) in float32 with separately rounded multiply and add like numpy (:299-303).
+__global__ void __launch_bounds__(256) load_audio_kernel(const float* __restrict__ x, long long x_stride, const int* __restrict__ lens,
+                                                         const int* __restrict__ shifts, const float* __restrict__ gains,
+                                                         const long long* __restrict__ noise_off, const float* __restrict__ bg,
+                                                         float* __restrict__ out, int in_len) {
+  const long long clip = blockIdx.y;
+  const int len = lens ? min(lens[clip], in_len) : in_len;        // samples past in_len never reach the output
+  const int shift = shifts ? shifts[clip] : 0;
+  const float g = gains ? gains[clip] : -1.f;
+  const bool noisy = g >= 0.f;                                    // NaN or negative: no noise, no clip
+  const float* xi = x + clip * x_stride;
+  const float* bi = (noisy && bg) ? bg + noise_off[clip] : nullptr;
+  float* o = out + clip * in_len;
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < in_len; t += gridDim.x * blockDim.x) {
+    const int src = t + shift;
+    float v = (src >= 0 && src < len) ? __ldg(xi + src) : 0.f;
+    if (noisy) {
+      const float nz = bi ? __fmul_rn(g, __ldg(bi + t)) : 0.f;
+      v = fminf(fmaxf(__fadd_rn(nz, v), -1.f), 1.f);
+    }
+    o[t] = v;
+  }
+}
+
 }  // namespace
 
 int conv2d_f32(const float* in, const float* w, const float* bias, float* out, const ConvGeom& g, bool relu,
@@ -225,6 +296,37 @@ extern "C" int honk_label_from_logits(const float* d_logits, int64_t n_clips, in
   const long long threads = n_clips * 32;
   label_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       d_logits, n_clips, n_labels, d_labels, d_probs);
+  HONK_LAUNCH_CHECK();
+  return HONK_OK;
+}
+
+extern "C" int honk_eval_metrics(const float* d_logits, const int64_t* d_labels, int64_t n_clips, int32_t n_labels,
+                                 int32_t* d_pred, int64_t* d_correct, double* d_loss_sum, void* stream) {
+  HONK_CHECK(n_clips >= 0 && n_labels >= 1, HONK_ERR_INVALID, "bad n_clips/n_labels");
+  HONK_CHECK(d_correct && d_loss_sum, HONK_ERR_INVALID, "honk_eval_metrics: null output");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  HONK_CUDA(cudaMemsetAsync(d_correct, 0, sizeof(int64_t), s));
+  HONK_CUDA(cudaMemsetAsync(d_loss_sum, 0, sizeof(double), s));
+  if (n_clips == 0) return HONK_OK;
+  HONK_CHECK(d_logits && d_labels, HONK_ERR_INVALID, "honk_eval_metrics: null input");
+  eval_metrics_kernel<<<static_cast<unsigned>((n_clips + 7) / 8), 256, 0, s>>>(
+      d_logits, reinterpret_cast<const long long*>(d_labels), n_clips, n_labels, d_pred,
+      reinterpret_cast<unsigned long long*>(d_correct), d_loss_sum);
+  HONK_LAUNCH_CHECK();
+  return HONK_OK;
+}
+
+extern "C" int honk_load_audio(const float* d_pcm, int64_t n_clips, int64_t clip_stride, const int32_t* d_lengths,
+                               const int32_t* d_shifts, const float* d_noise_gain, const int64_t* d_noise_offset,
+                               const float* d_bg_noise, int32_t input_length, float* d_out, void* stream) {
+  HONK_CHECK(n_clips >= 0 && n_clips <= 65535 && input_length >= 1, HONK_ERR_INVALID, "bad n_clips (<= 65535) / input_length");
+  if (n_clips == 0) return HONK_OK;
+  HONK_CHECK(d_pcm && d_out, HONK_ERR_INVALID, "honk_load_audio: null buffer");
+  HONK_CHECK(!d_noise_gain || !d_bg_noise || d_noise_offset, HONK_ERR_INVALID, "noise offsets missing");
+  dim3 grid(static_cast<unsigned>(std::min(16, (input_length + 1023) / 1024)), static_cast<unsigned>(n_clips));
+  load_audio_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      d_pcm, clip_stride, d_lengths, d_shifts, d_noise_gain, reinterpret_cast<const long long*>(d_noise_offset), d_bg_noise,
+      d_out, input_length);
   HONK_LAUNCH_CHECK();
   return HONK_OK;
 }

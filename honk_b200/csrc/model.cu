@@ -474,10 +474,32 @@ int pcm_elem_bytes(int dtype) { return dtype == HONK_PCM_I16 ? 2 : (dtype == HON
 // (each one's copy still ends before the previous one's kernels do), up to half the batch.  Every chunk is a whole
 // number of waves - the clip count at which all teams of the persistent conv kernel are busy - so chunking costs no
 // partially filled wave.  HONK_HOST_CHUNKS=n forces n equal chunks instead.
-std::vector<int64_t> host_chunk_plan(const honk_model* m, int64_t n_clips) {
+// Rough device time per clip in microseconds (front end 0.3 + convolutions at ~700 algorithmic TFLOP/s on the
+// tcgen05 paths), only used to tell copy-bound models from compute-bound ones.
+double est_device_us_per_clip(const honk_model* m) {
+  const honk_model_config& c = m->cfg;
+  if (m->tc2 || m->tc) return 0.3 + 18.0 * c.n_feature_maps * c.n_feature_maps * m->Hr * m->Wr * c.n_layers / 7e8;
+  if (m->ctc) return 0.6;
+  return 20.0;
+}
+
+std::vector<int64_t> host_chunk_plan(const honk_model* m, int64_t n_clips, int64_t clip_bytes = 32000) {
   std::vector<int64_t> plan;
   if (n_clips <= 0) return plan;
   const int64_t wave = m->tc2 ? honk::res_tc2_wave_clips(m->tc2) : 128;
+  if (!getenv("HONK_HOST_CHUNKS") && !getenv("HONK_HOST_FIRST_WAVES") &&
+      est_device_us_per_clip(m) < 1.5 * static_cast<double>(clip_bytes) / 50e3) {
+    // Copy-bound (res8, cnn-trad-pool2: PCIe at ~50 GB/s needs longer per clip than the kernels): the call ends one
+    // chunk's kernels after the last copy, so the chunks are equal and small - eight, each a whole number of waves.
+    const int64_t chunk = std::max(wave, (n_clips / 8 + wave - 1) / wave * wave);
+    for (int64_t c0 = 0; c0 < n_clips; c0 += chunk) plan.push_back(std::min(chunk, n_clips - c0));
+    if (plan.size() > 1 && plan.back() < wave / 2) {         // no sliver at the end
+      const int64_t last = plan.back();
+      plan.pop_back();
+      plan.back() += last;
+    }
+    return plan;
+  }
   if (const char* e = getenv("HONK_HOST_CHUNKS")) {
     const int pieces = std::max(1, std::min(64, atoi(e)));
     const int64_t chunk = std::min(n_clips, ((n_clips + pieces - 1) / pieces + wave - 1) / wave * wave);
@@ -503,7 +525,7 @@ std::vector<int64_t> host_chunk_plan(const honk_model* m, int64_t n_clips) {
 extern "C" int64_t honk_model_workspace_bytes_pcm_host(const honk_model* m, const honk_frontend* fe, int64_t n_clips,
                                                        int64_t n_samples, int dtype) {
   if (!m || !fe || n_clips <= 0) return 0;
-  const std::vector<int64_t> plan = host_chunk_plan(m, n_clips);
+  const std::vector<int64_t> plan = host_chunk_plan(m, n_clips, n_samples * pcm_elem_bytes(dtype));
   const int64_t largest = *std::max_element(plan.begin(), plan.end());
   const int64_t staging = align_up(n_clips * n_samples * pcm_elem_bytes(dtype), 256);
   const int64_t logits = align_up(n_clips * m->cfg.n_labels * 4, 256);
@@ -523,7 +545,7 @@ extern "C" int honk_model_forward_pcm_host(const honk_model* m, const honk_front
              HONK_ERR_WORKSPACE, "workspace too small");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int eb = pcm_elem_bytes(dtype);
-  const std::vector<int64_t> plan = host_chunk_plan(m, n_clips);
+  const std::vector<int64_t> plan = host_chunk_plan(m, n_clips, n_samples * eb);
   const int64_t staging = align_up(n_clips * n_samples * eb, 256);
   const int64_t logits_bytes = align_up(n_clips * m->cfg.n_labels * 4, 256);
   char* base = static_cast<char*>(d_workspace);

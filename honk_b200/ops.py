@@ -153,3 +153,70 @@ def listen(pcm: torch.Tensor, model: int, frontend: int, n_labels: int, window: 
 def _(pcm, model, frontend, n_labels, window, hop, keyword, min_keyword_prob):
     return (pcm.new_empty((n_labels,), dtype=torch.float64), pcm.new_empty((n_labels,), dtype=torch.int32),
             pcm.new_empty((1,), dtype=torch.int32))
+
+
+@torch.library.custom_op("honk_b200::eval_metrics", mutates_args=(), device_types="cuda")
+def eval_metrics(logits: torch.Tensor, labels: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """``(pred int32 [B], correct int64 [1], loss_sum float64 [1])``: print_eval's argmax == label count and
+    CrossEntropyLoss's sum (utils/train.py:41-46, 66-83) in one kernel."""
+    N.require_cuda(logits, "logits")
+    N.require_cuda(labels, "labels")
+    z = logits.to(torch.float32).contiguous()
+    y = labels.to(torch.int64).contiguous()
+    if y.dim() != 1 or z.dim() != 2 or y.shape[0] != z.shape[0]:
+        raise ValueError("honk_b200: eval_metrics takes logits [B, L] and labels [B]")
+    pred = torch.empty((z.shape[0],), dtype=torch.int32, device=z.device)
+    correct = torch.empty((1,), dtype=torch.int64, device=z.device)
+    loss = torch.empty((1,), dtype=torch.float64, device=z.device)
+    with torch.cuda.device(z.device):
+        N.check(N.lib().honk_eval_metrics(z.data_ptr(), y.data_ptr(), z.shape[0], z.shape[1], pred.data_ptr(),
+                                          correct.data_ptr(), loss.data_ptr(), N.stream_ptr(z.device)))
+    return pred, correct, loss
+
+
+@eval_metrics.register_fake
+def _(logits, labels):
+    return (logits.new_empty((logits.shape[0],), dtype=torch.int32), logits.new_empty((1,), dtype=torch.int64),
+            logits.new_empty((1,), dtype=torch.float64))
+
+
+def load_audio(pcm, lengths=None, shifts=None, noise_gain=None, noise_offset=None, bg_noise=None, input_length=16000):
+    """Batched arithmetic of ``SpeechDataset.load_audio`` (utils/model.py:281-303) on the device; the caller
+    makes the random draws.  ``pcm`` float32 ``[B, >=1]`` CUDA; returns float32 ``[B, input_length]``."""
+    N.require_cuda(pcm, "pcm")
+    if pcm.dim() != 2 or pcm.dtype != torch.float32:
+        raise ValueError("honk_b200: load_audio takes float32 pcm [B, n]")
+    if pcm.stride(1) != 1:
+        pcm = pcm.contiguous()
+    dev = pcm.device
+    B = pcm.shape[0]
+
+    def arg(t, dtype, what):
+        if t is None:
+            return None
+        t = torch.as_tensor(t, dtype=dtype, device=dev).contiguous()
+        if t.shape != (B,):
+            raise ValueError("honk_b200: %s must have one entry per clip" % what)
+        return t
+    if lengths is None:
+        lengths = torch.full((B,), pcm.shape[1], dtype=torch.int32, device=dev)
+    lengths = arg(lengths, torch.int32, "lengths").clamp(max=pcm.shape[1])
+    shifts = arg(shifts, torch.int32, "shifts")
+    noise_gain = arg(noise_gain, torch.float32, "noise_gain")
+    noise_offset = arg(noise_offset, torch.int64, "noise_offset")
+    if noise_gain is not None and bg_noise is not None:
+        N.require_cuda(bg_noise, "bg_noise")
+        bg_noise = bg_noise.to(torch.float32).contiguous()
+        if noise_offset is None:
+            raise ValueError("honk_b200: noise_offset is required with bg_noise")
+        if int(noise_offset.min()) < 0 or int(noise_offset.max()) + input_length > bg_noise.numel():
+            raise ValueError("honk_b200: noise window outside bg_noise")
+    else:
+        bg_noise = None
+    out = torch.empty((B, input_length), dtype=torch.float32, device=dev)
+    ptr = lambda t: t.data_ptr() if t is not None else None      # noqa: E731
+    with torch.cuda.device(dev):
+        N.check(N.lib().honk_load_audio(pcm.data_ptr(), B, pcm.stride(0) if B > 1 else pcm.shape[1], ptr(lengths), ptr(shifts),
+                                        ptr(noise_gain), ptr(noise_offset), ptr(bg_noise), input_length, out.data_ptr(),
+                                        N.stream_ptr(dev)))
+    return out

@@ -190,6 +190,25 @@ HONK_API int honk_listen(const honk_model* m, const honk_frontend* fe, const voi
                 double* d_sums, int32_t* d_counts, int32_t* d_first_hit, void* d_workspace,
                 int64_t workspace_bytes, void* stream);
 
+/* print_eval's accuracy numerator and nn.CrossEntropyLoss's sum for one batch of evaluate()
+ * (utils/train.py:41-46, 66-83): d_correct[0] = #(argmax(logits_i) == labels_i) (first maximum, like
+ * torch.max), d_loss_sum[0] = sum_i (logsumexp(logits_i) - logits_i[labels_i]) in float64; the caller
+ * divides by n_clips.  d_labels int64 [n_clips] (torch.tensor(y), model.py:265); d_pred int32
+ * [n_clips] may be NULL. */
+HONK_API int honk_eval_metrics(const float* d_logits, const int64_t* d_labels, int64_t n_clips, int32_t n_labels,
+                      int32_t* d_pred, int64_t* d_correct, double* d_loss_sum, void* stream);
+
+/* The arithmetic of SpeechDataset.load_audio for a batch (utils/model.py:281-303), with the random
+ * draws made by the caller: row i of d_pcm (float32, d_lengths[i] valid samples, NULL = all) is
+ * zero-padded to input_length (:297), shifted by d_shifts[i] samples (_timeshift_audio, :267-273:
+ * out[t] = x[t + shift], zeros outside; NULL = no shift), and where d_noise_gain[i] >= 0 mixed as
+ * clip(gain * bg[offset_i + t] + x, -1, 1) (:299-303) in float32 with separately rounded multiply
+ * and add, exactly like numpy; a negative gain leaves the clip unmixed and unclipped.  A silence
+ * example (:293) is a row with d_lengths[i] = 0.  d_out float32 [n_clips, input_length]. */
+HONK_API int honk_load_audio(const float* d_pcm, int64_t n_clips, int64_t clip_stride, const int32_t* d_lengths,
+                    const int32_t* d_shifts, const float* d_noise_gain, const int64_t* d_noise_offset,
+                    const float* d_bg_noise, int32_t input_length, float* d_out, void* stream);
+
 /* Number of kernels the library has launched in this process (for bench.py's gpu_launches). */
 HONK_API int64_t honk_launch_count(void);
 

@@ -270,6 +270,58 @@ def softmax_label(logits_row):
 
 
 # --------------------------------------------------------------------------
+# Evaluation data path: PINNED by tests/golden/eval_golden.npz, which
+# tests/golden/make_eval_golden.py produced by running the reference's own
+# SpeechDataset._timeshift_audio / load_audio, print_eval and nn.CrossEntropyLoss.
+# --------------------------------------------------------------------------
+
+def timeshift_audio(data, shift):
+    """``SpeechDataset._timeshift_audio`` with the drawn ``shift`` given (model.py:267-273)."""
+    a = -min(0, shift)
+    b = max(0, shift)
+    data = np.pad(data, (a, b), "constant")
+    return data[:len(data) - a] if a else data[b:]
+
+
+def load_audio(data, in_len=16000, shift=0, noise_gain=None, bg_noise=None):
+    """The arithmetic of ``SpeechDataset.load_audio`` (model.py:296-303) with the random draws given:
+    zero-pad to ``in_len``, time shift, and, when ``noise_gain`` is not None,
+    ``clip(noise_gain * bg_noise + data, -1, 1)`` (``bg_noise`` already cut to ``in_len`` samples)."""
+    data = np.asarray(data, dtype=np.float32)
+    data = np.pad(data, (0, max(0, in_len - len(data))), "constant")
+    data = timeshift_audio(data, shift)
+    if noise_gain is not None:
+        bg = np.zeros(in_len, dtype=np.float32) if bg_noise is None else np.asarray(bg_noise, dtype=np.float32)
+        data = np.clip(np.float32(noise_gain) * bg + data, -1, 1)
+    return data[:in_len]
+
+
+def eval_metrics(scores, labels):
+    """``print_eval``'s accuracy and ``nn.CrossEntropyLoss`` (train.py:41-46, 66-83) -> (accuracy, mean loss)."""
+    z = np.asarray(scores, dtype=np.float64)
+    y = np.asarray(labels, dtype=np.int64)
+    acc = float((z.argmax(1) == y).sum()) / len(y)
+    m = z.max(1)
+    lse = np.log(np.exp(z - m[:, None]).sum(1)) + m
+    return acc, float((lse - z[np.arange(len(y)), y]).mean())
+
+
+def listen(label_fn, wav_bytes, stride_ms=500, min_keyword_prob=0.85, keyword="command", method="all_label"):
+    """``ListenEndpoint.POST`` (server.py:99-112) over ``stride`` (service.py:106-110); ``label_fn(bytes)`` is
+    ``label_service.label``."""
+    step, window = int(2 * 16000 * stride_ms / 1000), 2 * 16000
+    labels = {}
+    i = 0
+    while i + window <= len(wav_bytes):
+        label, prob = label_fn(wav_bytes[i:i + window])
+        labels[label] = labels.get(label, 0.0) + float(prob)
+        if label == keyword and prob >= min_keyword_prob and method == "command_tagging":
+            return dict(contains_command=True)
+        i += step
+    return dict(contains_command=False) if method == "command_tagging" else labels
+
+
+# --------------------------------------------------------------------------
 # Algorithmic work (SURVEY.md §8d) used by bench.py for roofline arithmetic
 # --------------------------------------------------------------------------
 

@@ -100,3 +100,22 @@ def test_flops_table():
     for name, fl in exp.items():
         got = orc.conv_flops_per_clip(name, mod.find_config(name))
         assert abs(got - fl) / fl < 2e-3, (name, got)
+
+
+def test_eval_path_oracle_matches_reference_golden(golden_dir):
+    # the restated load_audio / _timeshift_audio / print_eval arithmetic against outputs of the
+    # reference's own functions (tests/golden/make_eval_golden.py), bit for bit
+    g = np.load(os.path.join(golden_dir, "eval_golden.npz"))
+    bg = g["bg_noise"]
+    for k, (n, shift, noisy, gain, off) in enumerate(g["load_audio/params"]):
+        x = g["load_audio/%d/x" % k]
+        y = orc.load_audio(x, 16000, int(shift), gain if noisy else None, bg[int(off):int(off) + 16000])
+        ref = g["load_audio/%d/y" % k]
+        assert y.dtype == ref.dtype == np.float32 and np.array_equal(y, ref), k
+    gain, off = g["load_audio/silence/params"]
+    y = orc.load_audio(np.zeros(0, np.float32), 16000, 0, gain, bg[int(off):int(off) + 16000])
+    assert np.array_equal(y, g["load_audio/silence/y"])
+    for sh in (-1600, -1, 0, 1, 1600):
+        assert np.array_equal(orc.timeshift_audio(g["timeshift/x"], sh), g["timeshift/%d" % sh])
+    acc, loss = orc.eval_metrics(g["eval/scores"], g["eval/labels"])
+    assert abs(acc - float(g["eval/accuracy"])) < 1e-6 and abs(loss - float(g["eval/loss"])) < 1e-5

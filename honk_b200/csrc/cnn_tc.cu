@@ -337,11 +337,12 @@ __global__ void __launch_bounds__(256) cnn_pack_x8_kernel(const float* __restric
 }
 
 // Linear(26624 -> L) in FP32: logits[clip][l] = b[l] + sum_k act[clip][k] * w[l][k]  (w already in act's k order).
-// One CTA = 32 clips; K in slabs of 256 staged in shared memory; thread = (clip, 32-wide k slice).
-constexpr int FC_CLIPS = 32, FC_KS = 256, FC_ASTRIDE = FC_KS * 2 + 16, FC_MAXL = 16;
+// One CTA = 32 clips x one K slice (blockIdx.y; split-K keeps small batches off a 104-slab serial loop; the slices'
+// partial sums go to part[slice][clip][l] and cnn_fc_reduce_kernel adds them in a fixed order: deterministic);
+// K in slabs of 256 staged in shared memory; thread = (clip, 32-wide k slice).
+constexpr int FC_CLIPS = 32, FC_KS = 256, FC_ASTRIDE = FC_KS * 2 + 16, FC_MAXL = 16, FC_SPLIT = 13;
 __global__ void __launch_bounds__(256) cnn_fc_kernel(const unsigned char* __restrict__ act, const float* __restrict__ w,
-                                                     const float* __restrict__ bias, float* __restrict__ logits, int n_clips,
-                                                     int K, int L) {
+                                                     float* __restrict__ part, int n_clips, int K, int L, int k_per) {
   __shared__ __align__(16) unsigned char As[FC_CLIPS * FC_ASTRIDE];
   __shared__ __align__(16) float Ws[FC_MAXL * FC_KS];
   const int tid = threadIdx.x, c = tid & 31, ks = tid >> 5;
@@ -349,7 +350,8 @@ __global__ void __launch_bounds__(256) cnn_fc_kernel(const unsigned char* __rest
   float acc[FC_MAXL];
 #pragma unroll
   for (int l = 0; l < FC_MAXL; ++l) acc[l] = 0.f;
-  for (int k0 = 0; k0 < K; k0 += FC_KS) {
+  const int k_begin = blockIdx.y * k_per, k_end = min(K, k_begin + k_per);
+  for (int k0 = k_begin; k0 < k_end; k0 += FC_KS) {
     __syncthreads();
     for (int i = tid; i < FC_CLIPS * (FC_KS / 8); i += 256) {          // 16-byte units, coalesced per clip row
       const int cc = i / (FC_KS / 8), u = i - cc * (FC_KS / 8);
@@ -392,10 +394,19 @@ __global__ void __launch_bounds__(256) cnn_fc_kernel(const unsigned char* __rest
   __syncthreads();
   for (int i = tid; i < FC_CLIPS * L; i += 256) {
     const int cc = i / L, l = i - cc * L;
-    float sum = __ldg(bias + l);
+    float sum = 0.f;
     for (int s = 0; s < 8; ++s) sum += red[s][cc][l];
-    if (clip0 + cc < n_clips) logits[(clip0 + cc) * L + l] = sum;
+    if (clip0 + cc < n_clips) part[(static_cast<long long>(blockIdx.y) * n_clips + clip0 + cc) * L + l] = sum;
   }
+}
+
+__global__ void cnn_fc_reduce_kernel(const float* __restrict__ part, const float* __restrict__ bias, float* __restrict__ logits,
+                                     long long n_clips, int L) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n_clips * L) return;
+  float sum = __ldg(bias + static_cast<int>(i % L));
+  for (int s = 0; s < FC_SPLIT; ++s) sum += part[s * n_clips * L + i];
+  logits[i] = sum;
 }
 
 }  // namespace
@@ -503,6 +514,7 @@ int64_t cnn_tc_workspace_bytes(const CnnTcPlan*, int64_t n_clips) {
   Arena a(nullptr, 0);
   a.take<unsigned char>(n_clips * CT_X8_BYTES);
   a.take<unsigned char>(n_clips * CT_ACT_BYTES);
+  a.take<float>(n_clips * FC_SPLIT * FC_MAXL);
   return align_up(a.off, 256);
 }
 
@@ -511,6 +523,7 @@ int cnn_tc_forward(const CnnTcPlan* p, const float* d_mfcc, int64_t n_clips, flo
   Arena ar(ws, ws_bytes);
   unsigned char* x8 = ar.take<unsigned char>(n_clips * CT_X8_BYTES);
   unsigned char* act = ar.take<unsigned char>(n_clips * CT_ACT_BYTES);
+  float* part = ar.take<float>(n_clips * FC_SPLIT * FC_MAXL);
   HONK_CHECK(ar.ok(), HONK_ERR_WORKSPACE, "internal: tcgen05 workspace overrun");
   {
     ProfSpan span("cnn_pack_x8", s);
@@ -533,9 +546,13 @@ int cnn_tc_forward(const CnnTcPlan* p, const float* d_mfcc, int64_t n_clips, flo
   }
   {
     ProfSpan span("cnn_fc", s);
-    cnn_fc_kernel<<<static_cast<unsigned>((n_clips + FC_CLIPS - 1) / FC_CLIPS), 256, 0, s>>>(act, p->d_wfc, p->d_bfc, d_logits,
-                                                                                           static_cast<int>(n_clips), CT_NPOS * CT_C,
-                                                                                           p->n_labels);
+    constexpr int K = CT_NPOS * CT_C;
+    static_assert(K % (FC_SPLIT * FC_KS) == 0, "K slices must be whole slabs");
+    const dim3 grid(static_cast<unsigned>((n_clips + FC_CLIPS - 1) / FC_CLIPS), FC_SPLIT);
+    cnn_fc_kernel<<<grid, 256, 0, s>>>(act, p->d_wfc, part, static_cast<int>(n_clips), K, p->n_labels, K / FC_SPLIT);
+    HONK_LAUNCH_CHECK();
+    const long long total = n_clips * p->n_labels;
+    cnn_fc_reduce_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, s>>>(part, p->d_bfc, d_logits, n_clips, p->n_labels);
     HONK_LAUNCH_CHECK();
   }
   return HONK_OK;

@@ -486,7 +486,7 @@ double est_device_us_per_clip(const honk_model* m) {
 std::vector<int64_t> host_chunk_plan(const honk_model* m, int64_t n_clips, int64_t clip_bytes = 32000) {
   std::vector<int64_t> plan;
   if (n_clips <= 0) return plan;
-  const int64_t wave = m->tc2 ? honk::res_tc2_wave_clips(m->tc2) : 128;
+  const int64_t wave = m->tc2 ? honk::res_tc2_wave_clips(m->tc2) : (m->ctc ? m->n_sms : 128);   // cnn_tc_kernel: one clip per CTA at a time
   if (!getenv("HONK_HOST_CHUNKS") && !getenv("HONK_HOST_FIRST_WAVES") &&
       est_device_us_per_clip(m) < 1.5 * static_cast<double>(clip_bytes) / 50e3) {
     // Copy-bound (res8, cnn-trad-pool2: PCIe at ~50 GB/s needs longer per clip than the kernels): the call ends one

@@ -22,7 +22,7 @@ EXPORTS = [
     "honk_frontend_destroy", "honk_frontend_num_frames", "honk_frontend_get_dct", "honk_frontend_get_mel",
     "honk_frontend_mfcc", "honk_model_create", "honk_model_destroy", "honk_model_workspace_bytes",
     "honk_model_forward", "honk_model_forward_pcm", "honk_model_workspace_bytes_pcm",
-    "honk_model_forward_pcm_host", "honk_model_workspace_bytes_pcm_host",
+    "honk_model_forward_pcm_host", "honk_model_label_pcm_host", "honk_model_workspace_bytes_pcm_host",
     "honk_label_from_logits", "honk_eval_metrics", "honk_load_audio", "honk_listen", "honk_listen_num_windows", "honk_listen_workspace_bytes", "honk_launch_count", "honk_model_path", "honk_profile_enable",
     "honk_profile_reset", "honk_profile_get",
 ]
@@ -85,6 +85,7 @@ def lib():
         L.honk_model_workspace_bytes_pcm.argtypes = [vp, vp, i64, i64]
         L.honk_model_workspace_bytes_pcm.restype = i64
         L.honk_model_forward_pcm_host.argtypes = [vp, vp, vp, C.c_int, i64, i64, i64, vp, vp, i64, vp]
+        L.honk_model_label_pcm_host.argtypes = [vp, vp, vp, C.c_int, i64, i64, i64, vp, vp, vp, i64, vp]
         L.honk_model_workspace_bytes_pcm_host.argtypes = [vp, vp, i64, i64, C.c_int]
         L.honk_model_workspace_bytes_pcm_host.restype = i64
         L.honk_label_from_logits.argtypes = [vp, i64, i32, vp, vp, vp]

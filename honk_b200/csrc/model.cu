@@ -529,17 +529,19 @@ extern "C" int64_t honk_model_workspace_bytes_pcm_host(const honk_model* m, cons
   const int64_t largest = *std::max_element(plan.begin(), plan.end());
   const int64_t staging = align_up(n_clips * n_samples * pcm_elem_bytes(dtype), 256);
   const int64_t logits = align_up(n_clips * m->cfg.n_labels * 4, 256);
-  return staging + logits + honk_model_workspace_bytes_pcm(m, fe, largest, n_samples);
+  return staging + logits + 2 * align_up(n_clips * 4, 256) + honk_model_workspace_bytes_pcm(m, fe, largest, n_samples);
 }
 
-extern "C" int honk_model_forward_pcm_host(const honk_model* m, const honk_frontend* fe, const void* h_pcm, int dtype,
-                                           int64_t n_clips, int64_t n_samples, int64_t clip_stride, float* h_logits,
-                                           void* d_workspace, int64_t workspace_bytes, void* stream) {
+namespace {
+// host PCM -> host logits and / or host (label, prob): the body of both host-buffer entry points
+int forward_pcm_host_impl(const honk_model* m, const honk_frontend* fe, const void* h_pcm, int dtype, int64_t n_clips,
+                          int64_t n_samples, int64_t clip_stride, float* h_logits, int32_t* h_labels, float* h_probs,
+                          void* d_workspace, int64_t workspace_bytes, void* stream) {
   HONK_CHECK(m && fe, HONK_ERR_INVALID, "honk_model_forward_pcm_host: null handle");
   HONK_CHECK(n_clips >= 0 && n_samples > 0 && clip_stride >= n_samples, HONK_ERR_INVALID,
              "honk_model_forward_pcm_host: bad shape");
   if (n_clips == 0) return HONK_OK;
-  HONK_CHECK(h_pcm && h_logits, HONK_ERR_INVALID, "honk_model_forward_pcm_host: null buffer");
+  HONK_CHECK(h_pcm && (h_logits || (h_labels && h_probs)), HONK_ERR_INVALID, "honk_model_forward_pcm_host: null buffer");
   HONK_CHECK(dtype == HONK_PCM_I16 || dtype == HONK_PCM_F32 || dtype == HONK_PCM_F64, HONK_ERR_INVALID, "unknown PCM dtype %d", dtype);
   HONK_CHECK(d_workspace && workspace_bytes >= honk_model_workspace_bytes_pcm_host(m, fe, n_clips, n_samples, dtype),
              HONK_ERR_WORKSPACE, "workspace too small");
@@ -550,8 +552,33 @@ extern "C" int honk_model_forward_pcm_host(const honk_model* m, const honk_front
   const int64_t logits_bytes = align_up(n_clips * m->cfg.n_labels * 4, 256);
   char* base = static_cast<char*>(d_workspace);
   float* d_logits = reinterpret_cast<float*>(base + staging);
-  char* inner = base + staging + logits_bytes;
-  const int64_t inner_bytes = workspace_bytes - staging - logits_bytes;
+  const int64_t lab_bytes = align_up(n_clips * 4, 256);
+  int32_t* d_labels = reinterpret_cast<int32_t*>(base + staging + logits_bytes);
+  float* d_probs = reinterpret_cast<float*>(base + staging + logits_bytes + lab_bytes);
+  char* inner = base + staging + logits_bytes + 2 * lab_bytes;
+  const int64_t inner_bytes = workspace_bytes - staging - logits_bytes - 2 * lab_bytes;
+  auto finish = [&]() -> int {
+    if (h_logits)
+      HONK_CUDA(cudaMemcpyAsync(h_logits, d_logits, static_cast<size_t>(n_clips * m->cfg.n_labels * 4), cudaMemcpyDeviceToHost, s));
+    if (h_labels && h_probs) {                               // labels and probs are adjacent: one copy when the host side is too
+      HONK_TRY(honk_label_from_logits(d_logits, n_clips, m->cfg.n_labels, d_labels, d_probs, stream));
+      HONK_CUDA(cudaMemcpyAsync(h_labels, d_labels, static_cast<size_t>(n_clips * 4), cudaMemcpyDeviceToHost, s));
+      HONK_CUDA(cudaMemcpyAsync(h_probs, d_probs, static_cast<size_t>(n_clips * 4), cudaMemcpyDeviceToHost, s));
+    }
+    HONK_CUDA(cudaStreamSynchronize(s));
+    return HONK_OK;
+  };
+  if (plan.size() == 1) {
+    // a request-sized batch: one copy and the kernels on the caller's stream, no second stream or events
+    if (clip_stride == n_samples) {
+      HONK_CUDA(cudaMemcpyAsync(base, h_pcm, static_cast<size_t>(n_clips * n_samples * eb), cudaMemcpyHostToDevice, s));
+    } else {
+      HONK_CUDA(cudaMemcpy2DAsync(base, static_cast<size_t>(n_samples * eb), h_pcm, static_cast<size_t>(clip_stride * eb),
+                                  static_cast<size_t>(n_samples * eb), static_cast<size_t>(n_clips), cudaMemcpyHostToDevice, s));
+    }
+    HONK_TRY(honk_model_forward_pcm(m, fe, base, dtype, n_clips, n_samples, n_samples, d_logits, inner, inner_bytes, s));
+    return finish();
+  }
   HostPipe hp;
   HONK_TRY(hp.init(plan.size()));
   // the scratch may have been handed out in the order of `s`: the copy stream must not run ahead of that
@@ -579,8 +606,24 @@ extern "C" int honk_model_forward_pcm_host(const honk_model* m, const honk_front
                                     d_logits + c0 * m->cfg.n_labels, inner, inner_bytes, s));
     c0 += nc;
   }
-  HONK_CUDA(cudaMemcpyAsync(h_logits, d_logits, static_cast<size_t>(n_clips * m->cfg.n_labels * 4), cudaMemcpyDeviceToHost, s));
-  HONK_CUDA(cudaStreamSynchronize(s));
+  HONK_TRY(finish());
   HONK_CUDA(cudaStreamSynchronize(hp.copy));
   return HONK_OK;
+}
+}  // namespace
+
+extern "C" int honk_model_forward_pcm_host(const honk_model* m, const honk_frontend* fe, const void* h_pcm, int dtype,
+                                           int64_t n_clips, int64_t n_samples, int64_t clip_stride, float* h_logits,
+                                           void* d_workspace, int64_t workspace_bytes, void* stream) {
+  if (n_clips > 0) HONK_CHECK(h_logits, HONK_ERR_INVALID, "honk_model_forward_pcm_host: null buffer");
+  return forward_pcm_host_impl(m, fe, h_pcm, dtype, n_clips, n_samples, clip_stride, h_logits, nullptr, nullptr, d_workspace,
+                               workspace_bytes, stream);
+}
+
+extern "C" int honk_model_label_pcm_host(const honk_model* m, const honk_frontend* fe, const void* h_pcm, int dtype,
+                                         int64_t n_clips, int64_t n_samples, int64_t clip_stride, int32_t* h_labels,
+                                         float* h_probs, void* d_workspace, int64_t workspace_bytes, void* stream) {
+  if (n_clips > 0) HONK_CHECK(h_labels && h_probs, HONK_ERR_INVALID, "honk_model_label_pcm_host: null buffer");
+  return forward_pcm_host_impl(m, fe, h_pcm, dtype, n_clips, n_samples, clip_stride, nullptr, h_labels, h_probs, d_workspace,
+                               workspace_bytes, stream);
 }

@@ -780,6 +780,9 @@ struct ResTc2Plan {
   int K = 2;                      // clips per team in flight: 37 teams x 2 x 2 buffers x 449 KB = 66 MB of L2 (K = 3: 100 MB starts
                                   // evicting dirty activations to HBM, and the extra DRAM power costs SM clock under the power cap)
   std::vector<T2Layer> layers;    // [0] = conv0, [1..n_layers] = the C->C layers
+  std::vector<T2Layer> layers_lat; // same layers cut for teams of T2_G CTAs: request-sized batches (latency mode)
+  int n_sms = 148;
+  bool tuned_by_env = false;      // HONK_TC2_G / HONK_TC2_K given: no automatic latency mode
   unsigned char* d_wpack = nullptr;
   float* d_wout = nullptr;
   float* d_bout = nullptr;
@@ -908,6 +911,8 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
   HONK_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, m->device));
   if (p->smem_bytes + 2048 > max_smem) return HONK_OK;
   p->max_teams = std::max(1, m->n_sms / G);
+  p->n_sms = m->n_sms;
+  p->tuned_by_env = getenv("HONK_TC2_K") || getenv("HONK_TC2_G");
   if (const char* e = getenv("HONK_TC2_K")) p->K = std::max(1, std::min(8, atoi(e)));
   const int N = p->NB, ncg = p->ncg, NKC = ncg / 2;
 
@@ -996,6 +1001,11 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
       }
   }
   p->layers = layers;
+  if (G != T2_G && p->W >= T2_G) {
+    p->layers_lat = layers;
+    for (int L = pooled ? 1 : 0; L <= c.n_layers; ++L)
+      if (!plan_segments(p->layers_lat[L], p->W, p->layers_lat[L].d, T2_G)) { p->layers_lat.clear(); break; }
+  }
   HONK_TRY(up(p.get(), wpack, &p->d_wpack));
   {
     // logits = W_o (s (.) (mean_hw(x_n) - mu_n)) + b_o  (last BN commutes with the mean)
@@ -1037,15 +1047,30 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
 
 // kernel "clips": groups of S stacked clips for the pooled models
 static int64_t tc2_groups(const ResTc2Plan* p, int64_t n_clips) { return (n_clips + p->S - 1) / p->S; }
-static int tc2_teams(const ResTc2Plan* p, int64_t n_groups) {
-  return static_cast<int>(std::min<int64_t>(p->max_teams, (n_groups + p->K - 1) / p->K));
+// Team size, groups in flight per team and segment table for a batch.  Throughput mode: the plan's (G, K).  When every
+// group fits on its own team anyway, one group per team (K = 1) finishes sooner than pairs in lockstep; and a
+// request-sized batch of a pooled model spreads each group over T2_G CTAs (latency mode: label(), /listen).
+struct T2Mode {
+  int G, K, max_teams;
+  const std::vector<T2Layer>* layers;
+};
+static T2Mode tc2_mode(const ResTc2Plan* p, int64_t n_groups) {
+  if (!p->tuned_by_env) {
+    if (!p->layers_lat.empty() && n_groups <= p->n_sms / T2_G) return {T2_G, 1, p->n_sms / T2_G, &p->layers_lat};
+    if (n_groups <= p->max_teams) return {p->G, 1, p->max_teams, &p->layers};
+  }
+  return {p->G, p->K, p->max_teams, &p->layers};
+}
+static int tc2_teams(const T2Mode& md, int64_t n_groups) {
+  return static_cast<int>(std::min<int64_t>(md.max_teams, (n_groups + md.K - 1) / md.K));
 }
 
 int res_tc2_wave_clips(const ResTc2Plan* p) { return p->max_teams * p->K * p->S; }
 
 int64_t res_tc2_workspace_bytes(const ResTc2Plan* p, int64_t n_clips) {
   const int64_t n_groups = tc2_groups(p, n_clips);
-  const int n_slots = p->K * tc2_teams(p, n_groups);
+  const T2Mode md = tc2_mode(p, n_groups);
+  const int n_slots = md.K * tc2_teams(md, n_groups);
   Arena a(nullptr, 0);
   a.take<unsigned char>(2ll * n_slots * p->slot_stride);
   a.take<float>(n_groups * p->S * p->NB);
@@ -1059,7 +1084,8 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
                     cudaStream_t s) {
   const bool pooled = p->pool_h > 0;
   const int64_t n_groups = tc2_groups(p, n_clips);
-  const int teams = tc2_teams(p, n_groups), n_slots = p->K * teams;
+  const T2Mode md = tc2_mode(p, n_groups);
+  const int teams = tc2_teams(md, n_groups), n_slots = md.K * teams;
   Arena ar(ws, ws_bytes);
   unsigned char* act = ar.take<unsigned char>(2ll * n_slots * p->slot_stride);
   float* pool = ar.take<float>(n_groups * p->S * p->NB);
@@ -1090,11 +1116,11 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
     HONK_LAUNCH_CHECK();
   }
   T2Params a{};
-  for (size_t i = 0; i < p->layers.size(); ++i) a.layers[i] = p->layers[i];
+  for (size_t i = 0; i < md.layers->size(); ++i) a.layers[i] = (*md.layers)[i];
   a.wpack = p->d_wpack;
   a.x0 = x0;
   a.y0 = x0;
-  a.G = p->G;
+  a.G = md.G;
   a.L0 = pooled ? 1 : 0;
   a.S = p->S;
   a.Hp1 = pooled ? p->Hc + 1 : p->H + 1;
@@ -1107,7 +1133,7 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
   a.n_layers = p->n_layers;
   a.n_clips = static_cast<int>(n_groups);
   a.n_slots = n_slots;
-  a.K = p->K;
+  a.K = md.K;
   a.H = p->H;
   a.W = p->W;
   a.plane_rows = p->plane_rows;
@@ -1127,7 +1153,7 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
   }
   {
     ProfSpan span("res_conv", s);
-    const dim3 grid(teams * p->G);
+    const dim3 grid(teams * md.G);
     if (p->ncg == 6) {
       if (dbg) tc2_res_kernel<6, true><<<grid, T2_THREADS, p->smem_bytes, s>>>(a);
       else tc2_res_kernel<6, false><<<grid, T2_THREADS, p->smem_bytes, s>>>(a);
@@ -1142,7 +1168,7 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
     HONK_CUDA(cudaStreamSynchronize(s));
     HONK_CUDA(cudaMemcpy(h.data(), a.dbg, h.size() * sizeof(long long), cudaMemcpyDeviceToHost));
     double m[T2_NDBG] = {0};
-    const int nb = teams * p->G;
+    const int nb = teams * md.G;
     for (int b = 0; b < nb; ++b)
       for (int k = 0; k < T2_NDBG; ++k) m[k] += static_cast<double>(h[b * T2_NDBG + k]) / nb;
     fprintf(stderr, "tc2 dbg (mean cycles/CTA, %d CTAs, %lld clips): producer total %.0f flag-wait %.0f stage-empty-wait %.0f | "

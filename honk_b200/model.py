@@ -197,6 +197,14 @@ class SerializableModule(nn.Module):
         return ops.listen(pcm, self._ensure_native(dev), audio_processor.handle, self.n_labels, int(window), int(hop),
                           int(keyword), float(min_keyword_prob))
 
+    def label_pcm_host(self, rows, audio_processor):
+        """Host numpy PCM ``[B, n_samples]`` -> numpy ``(labels, probs)``: ``TorchLabelService.label`` for a batch in
+        one native call (service.py:88-104)."""
+        if self.training:
+            raise RuntimeError("honk_b200 implements the inference path only; call model.eval()")
+        dev = self._device()
+        return ops.model_label_pcm_host(rows, self._ensure_native(dev), audio_processor.handle, dev)
+
     def forward_pcm_host(self, pcm, audio_processor, out=None):
         """Host ``[B, n_samples]`` PCM -> host logits, copies overlapped with the kernels chunk by chunk."""
         if self.training:

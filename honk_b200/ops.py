@@ -121,6 +121,20 @@ def label_from_logits(logits: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]
     return labels, probs
 
 
+def labels_to_host(logits):
+    """``(labels int32 [B], probs float32 [B])`` as numpy arrays through ONE device->host copy (the serving path's
+    tail: both outputs of honk_label_from_logits share a buffer)."""
+    N.require_cuda(logits, "logits")
+    z = logits.to(torch.float32).contiguous()
+    B = z.shape[0]
+    buf = torch.empty((2, B), dtype=torch.int32, device=z.device)
+    with torch.cuda.device(z.device):
+        N.check(N.lib().honk_label_from_logits(z.data_ptr(), B, z.shape[1], buf[0].data_ptr(), buf[1].data_ptr(),
+                                               N.stream_ptr(z.device)))
+    h = buf.cpu().numpy()
+    return h[0], h[1].view("float32")
+
+
 @label_from_logits.register_fake
 def _(logits):
     return (logits.new_empty((logits.shape[0],), dtype=torch.int32),
@@ -220,3 +234,33 @@ def load_audio(pcm, lengths=None, shifts=None, noise_gain=None, noise_offset=Non
                                         ptr(noise_gain), ptr(noise_offset), ptr(bg_noise), input_length, out.data_ptr(),
                                         N.stream_ptr(dev)))
     return out
+
+
+_ws_cache = __import__("threading").local()
+
+
+def model_label_pcm_host(rows, model: int, frontend: int, device):
+    """Host int16/float32/float64 numpy ``[B, n_samples]`` -> ``(labels int32 [B], probs float32 [B])`` numpy arrays
+    through ONE C-ABI call (honk_model_label_pcm_host: copy in, front end, model, softmax/argmax, copy out, one
+    synchronisation).  The serving path: no custom-op dispatch, the device scratch is cached per thread."""
+    import numpy as np
+    if rows.ndim != 2 or not rows.flags.c_contiguous:
+        raise ValueError("honk_b200: label_pcm_host takes a C-contiguous [B, n_samples] array")
+    code = {np.dtype(np.int16): 0, np.dtype(np.float32): 1, np.dtype(np.float64): 2}.get(rows.dtype)
+    if code is None:
+        raise ValueError("honk_b200: PCM must be int16, float32 or float64")
+    B, n = rows.shape
+    labels = np.empty((B,), dtype=np.int32)
+    probs = np.empty((B,), dtype=np.float32)
+    if B == 0:
+        return labels, probs
+    L = N.lib()
+    need = int(L.honk_model_workspace_bytes_pcm_host(model, frontend, B, n, code))
+    ws = getattr(_ws_cache, "ws", None)
+    if ws is None or ws.device != device or ws.numel() < need:
+        ws = torch.empty((max(need, 1 << 20),), dtype=torch.uint8, device=device)
+        _ws_cache.ws = ws
+    with torch.cuda.device(device):
+        N.check(L.honk_model_label_pcm_host(model, frontend, rows.ctypes.data, code, B, n, n, labels.ctypes.data,
+                                            probs.ctypes.data, ws.data_ptr(), ws.numel(), N.stream_ptr(device)))
+    return labels, probs

@@ -9,6 +9,7 @@ handle is immutable and every call allocates its own workspace on the caller's s
 from __future__ import annotations
 
 import os
+import threading
 import wave
 
 import numpy as np
@@ -64,6 +65,7 @@ class TorchLabelService(LabelService):
         self.model_type = model_type      # extension: the reference hard-codes cnn-trad-pool2 (service.py:81)
         self.n_samples = n_samples
         self.audio_processor = AudioPreprocessor()
+        self._tls = threading.local()
         self.reload()
 
     def reload(self):
@@ -77,22 +79,35 @@ class TorchLabelService(LabelService):
             self.model.load(self.model_filename)
         self.model.eval()
 
-    def _pcm_tensor(self, clips):
-        rows = np.zeros((len(clips), self.n_samples), dtype=np.int16)
+    def _pcm_rows(self, clips):
+        """Request bodies -> int16 rows.  Request-sized batches are assembled in a page-locked buffer kept per thread
+        (CherryPy calls label() from a thread pool, server.py:144-146), so the copy to the GPU needs no staging."""
+        B = len(clips)
+        rows = None
+        if B <= 1024:
+            pinned = getattr(self._tls, "pinned", None)
+            if pinned is None or pinned.shape[0] < B or pinned.shape[1] != self.n_samples:
+                pinned = torch.empty((max(32, B), self.n_samples), dtype=torch.int16).pin_memory()
+                self._tls.pinned = pinned
+            rows = pinned.numpy()[:B]
+        else:
+            rows = np.empty((B, self.n_samples), dtype=np.int16)
         for i, c in enumerate(clips):
             a = np.frombuffer(c, dtype=np.int16) if isinstance(c, (bytes, bytearray, memoryview)) else np.asarray(c, dtype=np.int16)
             n = min(len(a), self.n_samples)
-            rows[i, :n] = a[:n]                        # short clips are zero-padded (model.py:297)
-        return torch.from_numpy(rows).pin_memory().to(self.audio_processor.device, non_blocking=True)
+            rows[i, :n] = a[:n]
+            rows[i, n:] = 0                            # short clips are zero-padded (model.py:297)
+        return rows
+
+    def _pcm_tensor(self, clips):
+        return torch.from_numpy(self._pcm_rows(clips)).to(self.audio_processor.device)
 
     def label_batch(self, clips):
-        """List of int16 PCM byte strings -> list of ``(label, prob)``."""
+        """List of int16 PCM byte strings -> list of ``(label, prob)``; one native call (copy in, front end, model,
+        softmax/argmax, copy out, one synchronisation)."""
         if len(clips) == 0:
             return []
-        with torch.no_grad():
-            logits = self.model.forward_pcm(self._pcm_tensor(clips), self.audio_processor)
-            idx, prob = ops.label_from_logits(logits)
-            idx, prob = idx.cpu().numpy(), prob.cpu().numpy()
+        idx, prob = self.model.label_pcm_host(self._pcm_rows(clips), self.audio_processor)
         return [(self.labels[int(i)], float(p)) for i, p in zip(idx, prob)]
 
     def label(self, wav_data):

@@ -164,6 +164,12 @@ HONK_API int64_t honk_model_workspace_bytes_pcm(const honk_model* m, const honk_
 HONK_API int honk_model_forward_pcm_host(const honk_model* m, const honk_frontend* fe, const void* h_pcm, int dtype,
                                 int64_t n_clips, int64_t n_samples, int64_t clip_stride, float* h_logits,
                                 void* d_workspace, int64_t workspace_bytes, void* stream);
+/* TorchLabelService.label for a batch of requests in ONE call (service.py:88-104): host PCM in, host
+ * (argmax label, softmax probability) out - copy, front end, model, softmax/argmax, copy back, one
+ * stream synchronisation.  Same workspace as honk_model_forward_pcm_host. */
+HONK_API int honk_model_label_pcm_host(const honk_model* m, const honk_frontend* fe, const void* h_pcm, int dtype,
+                              int64_t n_clips, int64_t n_samples, int64_t clip_stride, int32_t* h_labels,
+                              float* h_probs, void* d_workspace, int64_t workspace_bytes, void* stream);
 HONK_API int64_t honk_model_workspace_bytes_pcm_host(const honk_model* m, const honk_frontend* fe, int64_t n_clips,
                                             int64_t n_samples, int dtype);
 

@@ -73,3 +73,11 @@ def test_api_surface_matches_reference_names():
         shapes = synth.state_dict_shapes(ct.value, cfg)
         assert list(sd.keys()) == list(shapes.keys())
         assert all(tuple(sd[k].shape) == tuple(shapes[k]) for k in sd)
+
+
+def test_every_package_module_imports():
+    import importlib
+    pkg = os.path.join(ROOT, "honk_b200")
+    for fn in sorted(os.listdir(pkg)):
+        if fn.endswith(".py") and fn != "build.py":
+            importlib.import_module("honk_b200." + fn[:-3] if fn != "__init__.py" else "honk_b200")

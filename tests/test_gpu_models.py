@@ -250,3 +250,23 @@ def test_pooled_stacked_groups(name, n, G, K, monkeypatch):
     # the same clip gives the same logits wherever it sits in a group and whichever team ran it
     if n > 64 * 3:
         assert np.abs(y[0] - y[192]).max() <= 1e-4 * np.abs(ref).max()
+
+
+@pytest.mark.parametrize("name,n", [("res26", 1), ("res26", 5), ("res26", 74), ("res26", 75), ("res8", 2), ("res8", 148),
+                                    ("res8", 149), ("res8-narrow", 9), ("res15", 1), ("res15", 37), ("res15", 38)])
+def test_request_sized_batches_latency_mode(name, n):
+    # small batches switch the persistent kernel to one group per team (K = 1) and, for the pooled models, to teams
+    # of four CTAs per stacked group; sizes on both sides of each switch-over, against the FP32 path
+    import honk_b200 as hb
+    cfg = dict(hb.find_config(name))
+    cfg["n_labels"] = 12
+    base = synth.make_clips(max(16, min(n, 64)), start=8100)
+    pre = hb.AudioPreprocessor()
+    mf64 = pre.compute_mfccs_batch(torch.from_numpy(base).cuda())
+    sd = synth.make_state_dict(name, cfg, seed=12, calib_mfcc=mf64[:16].cpu().numpy())
+    mf = mf64.repeat(n // len(base) + 1, 1, 1)[:n].contiguous()
+    mf[1::2] = mf[1::2].flip(2) * 0.7
+    m32, m16 = build(name, cfg, sd, 1), build(name, cfg, sd, 0)
+    ref, y = m32(mf).cpu().numpy(), m16(mf).cpu().numpy()
+    assert m16.native_path == "tcgen05-f16"
+    assert np.abs(y - ref).max() / np.abs(ref).max() <= TOL["tcgen05-f16"], (name, n)

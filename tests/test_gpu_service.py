@@ -58,8 +58,32 @@ def test_listen_windows_and_model_type():
         for kw in (top[0], "not-a-label"):
             host = svc._listen_host(long, 16000, thr, kw, "command_tagging")
             assert svc.listen(long, min_keyword_prob=thr, keyword=kw, method="command_tagging") == host
-    assert svc.listen(long[:31998]) == {} and svc.listen(long[:32000]) == svc._listen_host(long[:32000], 16000, 0.85, "x", "all_label")
+    one, one_host = svc.listen(long[:32000]), svc._listen_host(long[:32000], 16000, 0.85, "x", "all_label")
+    assert svc.listen(long[:31998]) == {} and set(one) == set(one_host) and len(one) == 1
+    assert all(abs(one[k] - one_host[k]) < 1e-5 for k in one)      # (the global-mean sums meet by atomics: ~1e-7 run to run)
     assert svc.listen(long[:100], method="command_tagging") == dict(contains_command=False)
     assert svc.listen(long[:32001]).keys() == svc.listen(long[:32000]).keys()
     with pytest.raises(RuntimeError):
         TorchLabelService(tsd, no_cuda=True, labels=LABELS, model_type=hb.ConfigType.RES8_NARROW)
+
+
+@pytest.mark.parametrize("n", [1, 3, 700])
+def test_label_batch_single_call_matches_two_step(n):
+    # honk_model_label_pcm_host (one native call: copy, front end, model, softmax/argmax, copy back) == forward_pcm +
+    # label_from_logits on device buffers; n = 700 takes the chunked two-stream path
+    import honk_b200 as hb
+    from honk_b200 import ops
+    from honk_b200.service import TorchLabelService
+    cfg = dict(hb.find_config("res8-narrow"))
+    sd = synth.make_state_dict("res8-narrow", cfg, seed=8)
+    tsd = {k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()}
+    svc = TorchLabelService(tsd, labels=LABELS, model_type=hb.ConfigType.RES8_NARROW)
+    base = synth.make_clips(50, start=1200)
+    clips = [base[i % 50][: 16000 - (i % 7) * 900].tobytes() for i in range(n)]      # some short: zero-padded
+    got = svc.label_batch(clips)
+    logits = svc.model.forward_pcm(svc._pcm_tensor(clips), svc.audio_processor)
+    idx, prob = ops.label_from_logits(logits)
+    idx, prob = idx.cpu().numpy(), prob.cpu().numpy()
+    assert [g[0] for g in got] == [LABELS[int(i)] for i in idx]
+    assert np.allclose([g[1] for g in got], prob, atol=1e-5)
+    assert svc.label_batch([]) == []

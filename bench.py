@@ -37,10 +37,19 @@ def parse_args():
     ap.add_argument("--impl", default="honk_b200", choices=["honk_b200", "reference"])
     ap.add_argument("--model", default="res15")
     ap.add_argument("--clips-per-gpu", type=int, default=8192)
+    ap.add_argument("--global-clips", type=int, default=0,
+                    help="strong scaling: this many clips in total, split evenly over the ranks (BASELINE configs[2]: "
+                         "--model res8 --global-clips 16384); overrides --clips-per-gpu")
     ap.add_argument("--precision", type=int, default=0, help="0 = tcgen05 f16 operands, 1 = all-FP32 CUDA cores")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
-    return ap.parse_args()
+    args = ap.parse_args()
+    args.scaling = "weak"
+    if args.global_clips > 0:
+        world = int(os.environ.get("WORLD_SIZE", "1"))
+        args.clips_per_gpu = max(1, args.global_clips // world)
+        args.scaling = "strong"
+    return args
 
 
 def measured_peaks():
@@ -421,7 +430,7 @@ def main():
                   "share_of_step": t_ms / (ms * args.steps)}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": "f64 front end; f16 operands / f32 accumulate CNN" if args.precision == 0 else "f64 front end; f32 CNN",
             "data": "synthetic", "config": workload_config(args, world),
             "path": model.native_path, "gpu_launches": launches, "clocks": clocks,

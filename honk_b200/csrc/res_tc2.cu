@@ -1151,6 +1151,29 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
     a.dbg = s_dbg;
     if (const char* e = getenv("HONK_TC2_MODE")) a.mode = atoi(e);
   }
+  // Experiment switch (HONK_TC2_L2PERSIST=1): mark the rotating activation buffers as persisting L2 lines for this launch.
+  static const bool l2persist = [] { const char* e = getenv("HONK_TC2_L2PERSIST"); return e && atoi(e); }();
+  if (l2persist) {
+    static bool limit_set = false;
+    if (!limit_set) {
+      int dev = 0, max_persist = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, dev);
+      cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, static_cast<size_t>(max_persist));
+      fprintf(stderr, "tc2: persisting L2 limit %d MB\n", max_persist >> 20);
+      limit_set = true;
+    }
+    int dev = 0, max_win = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&max_win, cudaDevAttrMaxAccessPolicyWindowSize, dev);
+    cudaStreamAttrValue av{};
+    av.accessPolicyWindow.base_ptr = act;
+    av.accessPolicyWindow.num_bytes = std::min<size_t>(static_cast<size_t>(2ll * n_slots * p->slot_stride), static_cast<size_t>(max_win));
+    av.accessPolicyWindow.hitRatio = 1.0f;
+    av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    HONK_CUDA(cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &av));
+  }
   {
     ProfSpan span("res_conv", s);
     const dim3 grid(teams * md.G);
@@ -1175,6 +1198,11 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
             "mma total %.0f acc-empty-wait %.0f stage-full-wait %.0f weight-wait %.0f | epilogue total %.0f acc-full-wait %.0f | "
             "lookahead hits %.0f of %.0f tasks\n",
             nb, static_cast<long long>(n_clips), m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[8], m[7], m[11], m[12]);
+  }
+  if (l2persist) {
+    cudaStreamAttrValue av{};
+    av.accessPolicyWindow.num_bytes = 0;
+    HONK_CUDA(cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &av));
   }
   {
     ProfSpan span("res_tail", s);

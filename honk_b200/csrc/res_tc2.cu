@@ -751,6 +751,161 @@ __global__ void __launch_bounds__(NCG * 64) tc2_conv0_pool_kernel(const float* _
   }
 }
 
+// D(16x8, f32) += A(16x16, f16, row) * B(16x8, f16, col): the warp-level tensor-core MMA (legacy mma.sync path; conv0 is
+// 0.2 % of a model's work and its M = positions x N = 48 x K = 28 shape is far too small for a tcgen05 pipeline of its own)
+__device__ __forceinline__ void mma16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                         uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// Pooled models, default pre-pass: conv0 + ReLU + AvgPool as an implicit GEMM on the tensor cores.  M = 16 pooled cells
+// (one conv position of each per MMA), N = 8 channels per tile, K = 32 = 16 pairs:
+//   pair m = 0..8  : A = (x_hi, x_lo) of tap m        B = (w_hi, w_hi) of tap m
+//   pair m = 9..13 : A = (x_hi of taps 2(m-9), 2(m-9)+1)   B = (w_lo of the same two taps)      (tap 9 does not exist: 0)
+// i.e. x*w_hi + x_hi*w_lo with x = x_hi + x_lo, w = w_hi + w_lo split into f16 halves and FP32 accumulation (~2^-21
+// relative, like conv0 of the un-pooled models).  The shared-memory image holds one (hi, lo) pair per pixel, so a pair of
+// the first kind is one 32-bit load.  ReLU and the pool sum are applied to the accumulator fragment per conv position.
+template <int NCG>
+__global__ void __launch_bounds__(256) tc2_conv0_pool_mma_kernel(const float* __restrict__ mfcc, const uint32_t* __restrict__ wb,
+                                                                 unsigned char* __restrict__ y0, int n_clips, int H0, int W0, int ph,
+                                                                 int pw, int Hc, int Wc, int S, int plane_rows, long long slot_stride) {
+  extern __shared__ uint32_t xh[];                       // [S][(H0+2)][(W0+2)] zero-bordered images, (hi | lo << 16) per pixel
+  const int group = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int Wp = W0 + 2, img = (H0 + 2) * Wp;
+  const int n_here = static_cast<int>(min(static_cast<long long>(S), n_clips - static_cast<long long>(group) * S));
+  auto split = [](float f) -> uint32_t {
+    f = fminf(fmaxf(f, -60000.f), 60000.f);              // stays finite in f16
+    const __half hi = __float2half_rn(f);
+    const __half lo = __float2half_rn(f - __half2float(hi));
+    return static_cast<uint32_t>(__half_as_ushort(hi)) | (static_cast<uint32_t>(__half_as_ushort(lo)) << 16);
+  };
+  const float* src = mfcc + static_cast<long long>(group) * S * H0 * W0;     // the group's clips are contiguous
+  if ((W0 & 3) == 0 && ((static_cast<long long>(S) * H0 * W0) & 3) == 0) {
+    // interior: 16-byte loads, four in flight per thread (the border and absent clips are zeroed below)
+    const float4* src4 = reinterpret_cast<const float4*>(src);
+    const int n4 = n_here * H0 * W0 / 4, hw = H0 * W0;
+    for (int i0 = tid; i0 < n4; i0 += 4 * 256) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (i0 + u * 256 < n4) v[u] = __ldg(src4 + i0 + u * 256);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int e = (i0 + u * 256) * 4;
+        if (e < n4 * 4) {
+          const int sc = e / hw, rem = e - sc * hw, y = rem / W0, x = rem - y * W0;
+          uint32_t* d = xh + sc * img + (y + 1) * Wp + x + 1;
+          d[0] = split(v[u].x);
+          d[1] = split(v[u].y);
+          d[2] = split(v[u].z);
+          d[3] = split(v[u].w);
+        }
+      }
+    }
+    for (int i = tid; i < S * img; i += 256) {
+      const int sc = i / img, r = i - sc * img;
+      const int y = r / Wp, x = r - y * Wp;
+      if (sc >= n_here || y == 0 || y == H0 + 1 || x == 0 || x == W0 + 1) xh[i] = 0u;
+    }
+  } else {
+    for (int i = tid; i < S * img; i += 256) {
+      const int sc = i / img, r = i - sc * img;
+      const int y = r / Wp - 1, x = r % Wp - 1;
+      xh[i] = (sc < n_here && y >= 0 && y < H0 && x >= 0 && x < W0) ? split(__ldg(src + (static_cast<long long>(sc) * H0 + y) * W0 + x)) : 0u;
+    }
+  }
+  const int Hp1 = Hc + 1, Hk = S * Hp1 - 1;
+  uint4* dst = reinterpret_cast<uint4*>(y0 + static_cast<long long>(group) * slot_stride);
+  // every unit that is not a real position of a present clip is zero: padding rows, separators, missing clips, tail
+  const int n_units16 = static_cast<int>(slot_stride / 16), n_plane_units = Wc * NCG * plane_rows;
+  for (int i = tid; i < n_units16; i += 256) {
+    bool real = false;
+    if (i < n_plane_units) {
+      const int hk = i % plane_rows - T2_PAD;
+      if (hk >= 0 && hk < Hk) {
+        const int sc = hk / Hp1;
+        real = (hk - sc * Hp1) < Hc && sc < n_here;
+      }
+    }
+    if (!real) dst[i] = make_uint4(0, 0, 0, 0);
+  }
+  // this thread's four K pairs (q = lane % 4): m = q, q + 4 (one pixel each) and q + 8, q + 12 (generic: two pixels + masks)
+  const int q = lane & 3, r0 = lane >> 2;
+  const int off0 = (q / 3) * Wp + q % 3, off1 = ((q + 4) / 3) * Wp + (q + 4) % 3;
+  int off2a, off2b, off3a, off3b;
+  uint32_t sel2, mask2b, z2, sel3, mask3b, z3;
+  {
+    auto tap_off = [&](int t) { return (t / 3) * Wp + t % 3; };
+    const int m2 = q + 8, m3 = q + 12;
+    if (m2 == 8) { off2a = off2b = tap_off(8); sel2 = 0x3210u; mask2b = 0xFFFFFFFFu; }
+    else { off2a = tap_off(2 * (m2 - 9)); off2b = tap_off(2 * (m2 - 9) + 1); sel2 = 0x5410u; mask2b = 0xFFFFFFFFu; }
+    z2 = 0xFFFFFFFFu;
+    if (m3 == 12) { off3a = tap_off(6); off3b = tap_off(7); sel3 = 0x5410u; mask3b = 0xFFFFFFFFu; z3 = 0xFFFFFFFFu; }
+    else if (m3 == 13) { off3a = off3b = tap_off(8); sel3 = 0x5410u; mask3b = 0u; z3 = 0xFFFFFFFFu; }
+    else { off3a = off3b = 0; sel3 = 0x3210u; mask3b = 0u; z3 = 0u; }
+  }
+  uint32_t bw[NCG][4];
+#pragma unroll
+  for (int cg = 0; cg < NCG; ++cg) {
+    const uint32_t* wr = wb + (cg * 8 + r0) * 16;        // B fragment: n = lane / 4
+    bw[cg][0] = __ldg(wr + q);
+    bw[cg][1] = __ldg(wr + q + 4);
+    bw[cg][2] = __ldg(wr + q + 8);
+    bw[cg][3] = __ldg(wr + q + 12);
+  }
+  __syncthreads();
+  const float inv = 1.f / static_cast<float>(ph * pw);
+  const int n_cells = Wc * Hc, units_per_clip = (n_cells + 15) >> 4;
+  for (int u = warp; u < n_here * units_per_clip; u += 8) {
+    const int sc = u / units_per_clip, c_base = (u - sc * units_per_clip) << 4;
+    const int ca = c_base + r0, cb = ca + 8;
+    const bool va = ca < n_cells, vb = cb < n_cells;
+    const int wa = va ? ca / Hc : 0, ha = va ? ca - wa * Hc : 0;
+    const int wbq = vb ? cb / Hc : 0, hb = vb ? cb - wbq * Hc : 0;
+    const uint32_t* pa = xh + sc * img + (ha * ph) * Wp + wa * pw;       // top-left pixel of the cell's first conv position
+    const uint32_t* pb = xh + sc * img + (hb * ph) * Wp + wbq * pw;
+    float acc[NCG][4];
+#pragma unroll
+    for (int cg = 0; cg < NCG; ++cg)
+#pragma unroll
+      for (int k = 0; k < 4; ++k) acc[cg][k] = 0.f;
+    for (int py = 0; py < ph; ++py)
+      for (int px = 0; px < pw; ++px) {
+        const uint32_t* xa = pa + py * Wp + px;
+        const uint32_t* xb = pb + py * Wp + px;
+        const uint32_t a00 = xa[off0], a01 = xb[off0], a10 = xa[off1], a11 = xb[off1];
+        const uint32_t a20 = __byte_perm(xa[off2a], xa[off2b] & mask2b, sel2) & z2;
+        const uint32_t a21 = __byte_perm(xb[off2a], xb[off2b] & mask2b, sel2) & z2;
+        const uint32_t a30 = __byte_perm(xa[off3a], xa[off3b] & mask3b, sel3) & z3;
+        const uint32_t a31 = __byte_perm(xb[off3a], xb[off3b] & mask3b, sel3) & z3;
+        float c[NCG][4];                                  // NCG independent accumulator chains per K step
+#pragma unroll
+        for (int cg = 0; cg < NCG; ++cg) {
+          c[cg][0] = c[cg][1] = c[cg][2] = c[cg][3] = 0.f;
+          mma16816(c[cg], a00, a01, a10, a11, bw[cg][0], bw[cg][1]);
+        }
+#pragma unroll
+        for (int cg = 0; cg < NCG; ++cg) mma16816(c[cg], a20, a21, a30, a31, bw[cg][2], bw[cg][3]);
+#pragma unroll
+        for (int cg = 0; cg < NCG; ++cg)
+#pragma unroll
+          for (int k = 0; k < 4; ++k) acc[cg][k] += fmaxf(c[cg][k], 0.f);
+      }
+    // rows r0 / r0 + 8 of the tile = cells ca / cb; this lane holds channels 2q, 2q + 1 of every channel group
+    unsigned char* oa = reinterpret_cast<unsigned char*>(dst) + ((static_cast<long long>(wa) * NCG) * plane_rows + T2_PAD + sc * Hp1 + ha) * 16 + q * 4;
+    unsigned char* ob = reinterpret_cast<unsigned char*>(dst) + ((static_cast<long long>(wbq) * NCG) * plane_rows + T2_PAD + sc * Hp1 + hb) * 16 + q * 4;
+#pragma unroll
+    for (int cg = 0; cg < NCG; ++cg) {
+      uint32_t o0 = pack_h2(acc[cg][0] * inv, acc[cg][1] * inv), o1 = pack_h2(acc[cg][2] * inv, acc[cg][3] * inv);
+      if (cg == NCG - 1 && q == 3) o0 = o1 = 0x3C003C00u;      // the two constant-one channels
+      if (va) *reinterpret_cast<uint32_t*>(oa + static_cast<long long>(cg) * plane_rows * 16) = o0;
+      if (vb) *reinterpret_cast<uint32_t*>(ob + static_cast<long long>(cg) * plane_rows * 16) = o1;
+    }
+  }
+}
+
 // logits = W'(pool / HW) + b' with the last BatchNorm folded into W', b'
 __global__ void tc2_tail_kernel(const float* __restrict__ pool, const float* __restrict__ wout,
                                 const float* __restrict__ bout, float* __restrict__ logits, int n_clips, int N, int L,
@@ -776,7 +931,9 @@ struct ResTc2Plan {
   int G = T2_G;                   // CTAs per team
   int S = 1, Hc = 101;            // pooled models: S clips of Hc rows stacked along time per kernel "clip" (H = S*(Hc+1)-1)
   int pool_h = 0, pool_w = 0, H0 = 101, W0 = 40;
-  float* d_w0 = nullptr;          // pooled models: conv0 weights [9][NB] float (conv0 + pool run in tc2_conv0_pool_kernel)
+  float* d_w0 = nullptr;          // pooled models: conv0 weights [9][NB] float (FP32 variant of the conv0 + pool pre-pass)
+  uint32_t* d_w0b = nullptr;      // pooled models: conv0 weights as mma.sync B pairs [NB][16] (tc2_conv0_pool_mma_kernel)
+  bool conv0_f32 = false;         // HONK_TC2_CONV0_F32=1: FP32 CUDA-core pre-pass instead of the tensor-core one
   int K = 2;                      // clips per team in flight: 37 teams x 2 x 2 buffers x 449 KB = 66 MB of L2 (K = 3: 100 MB starts
                                   // evicting dirty activations to HBM, and the extra DRAM power costs SM clock under the power cap)
   std::vector<T2Layer> layers;    // [0] = conv0, [1..n_layers] = the C->C layers
@@ -936,6 +1093,22 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
     for (int co = 0; co < C; ++co)
       for (int tap = 0; tap < 9; ++tap) w0[tap * N + co] = w.data[co * 9 + tap];
     HONK_TRY(up(p.get(), w0, &p->d_w0));
+    // the same weights as K pairs of the mma.sync formulation (see tc2_conv0_pool_mma_kernel)
+    std::vector<uint32_t> wb(static_cast<size_t>(N) * 16, 0u);
+    for (int co = 0; co < C; ++co) {
+      unsigned short hi[10] = {0}, lo[10] = {0};
+      for (int tap = 0; tap < 9; ++tap) {
+        const float v = w.data[co * 9 + tap];
+        const __half h = __float2half(v);
+        const __half l = __float2half(v - __half2float(h));
+        hi[tap] = __half_as_ushort(h);
+        lo[tap] = __half_as_ushort(l);
+      }
+      for (int mm = 0; mm < 9; ++mm) wb[co * 16 + mm] = static_cast<uint32_t>(hi[mm]) | (static_cast<uint32_t>(hi[mm]) << 16);
+      for (int mm = 9; mm < 14; ++mm) wb[co * 16 + mm] = static_cast<uint32_t>(lo[2 * (mm - 9)]) | (static_cast<uint32_t>(lo[2 * (mm - 9) + 1]) << 16);
+    }
+    HONK_TRY(up(p.get(), wb, &p->d_w0b));
+    if (const char* e = getenv("HONK_TC2_CONV0_F32")) p->conv0_f32 = atoi(e) != 0;
   } else {
     // conv0 (bias-free, model.py:107): B tile kh = [K half][n = blk*NB + co][8]; input channels 0..2 = (x_hi, x_lo, x_hi)
     // meet (w_hi, w_hi, w_lo); everything else (the whole second K half included) is zero.
@@ -1027,6 +1200,8 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
   if (pooled) {
     const int sm0 = S * (p->H0 + 2) * (p->W0 + 2) * static_cast<int>(sizeof(float));
     if (sm0 + 1024 > max_smem) return HONK_OK;
+    HONK_TRY(set_smem(tc2_conv0_pool_mma_kernel<6>, sm0));
+    HONK_TRY(set_smem(tc2_conv0_pool_mma_kernel<4>, sm0));
     HONK_TRY(set_smem(tc2_conv0_pool_kernel<6, 4, 3>, sm0));
     HONK_TRY(set_smem(tc2_conv0_pool_kernel<4, 4, 3>, sm0));
     HONK_TRY(set_smem(tc2_conv0_pool_kernel<6, 2, 2>, sm0));
@@ -1103,7 +1278,14 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
   tc2_conv0_pool_kernel<NCG_, PH_, PW_><<<grid, NCG_ * 64, smem, s>>>(d_mfcc, p->d_w0, x0, static_cast<int>(n_clips), p->H0, p->W0, \
                                                                       p->pool_h, p->pool_w, p->Hc, p->W, p->S, p->plane_rows, p->slot_stride)
     const int pk = (p->pool_h == 4 && p->pool_w == 3) ? 1 : ((p->pool_h == 2 && p->pool_w == 2) ? 2 : 0);
-    if (p->ncg == 6) {
+    if (!p->conv0_f32) {
+      if (p->ncg == 6)
+        tc2_conv0_pool_mma_kernel<6><<<grid, 256, smem, s>>>(d_mfcc, p->d_w0b, x0, static_cast<int>(n_clips), p->H0, p->W0, p->pool_h,
+                                                             p->pool_w, p->Hc, p->W, p->S, p->plane_rows, p->slot_stride);
+      else
+        tc2_conv0_pool_mma_kernel<4><<<grid, 256, smem, s>>>(d_mfcc, p->d_w0b, x0, static_cast<int>(n_clips), p->H0, p->W0, p->pool_h,
+                                                             p->pool_w, p->Hc, p->W, p->S, p->plane_rows, p->slot_stride);
+    } else if (p->ncg == 6) {
       if (pk == 1) T2_C0(6, 4, 3); else if (pk == 2) T2_C0(6, 2, 2); else T2_C0(6, 0, 0);
     } else {
       if (pk == 1) T2_C0(4, 4, 3); else if (pk == 2) T2_C0(4, 2, 2); else T2_C0(4, 0, 0);

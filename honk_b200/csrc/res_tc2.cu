@@ -221,7 +221,11 @@ template <int NCG, bool DBG>
 __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_constant__ T2Params p) {
   constexpr int NB = NCG * 8;            // padded channels = N block
   constexpr int NKC = NCG / 2;           // K chunks of 16 channels
-  constexpr int NSLOT = 512 / NB;        // TMEM ring of output-column accumulators
+  constexpr int NPHYS = 512 / NB;        // accumulator slots in TMEM
+  constexpr int NSLOT = NPHYS - 2;       // LOGICAL ring of output-column accumulators.  A task writes three consecutive slots
+                                         // starting at physical slot (g - 1) % NSLOT <= NSLOT - 1, so it never straddles the end
+                                         // of TMEM (no MMA split in two): physical slots NSLOT, NSLOT + 1 are second homes of
+                                         // logical slots 0, 1, and the epilogue adds the two homes of those outputs.
   constexpr int NMMA = 3 * NKC;          // MMAs per input column
   constexpr int NSPLIT = NMMA / 2 + 1;   // MMAs issued before the look-ahead probe of the next task
 
@@ -378,9 +382,9 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
               const bool lo_in = jc > j0, c_in = (jc >= j0) && (jc <= jend), hi_in = jc < jend;
               const int first_blk = lo_in ? 0 : (c_in ? 1 : 2), last_blk = hi_in ? 2 : (c_in ? 1 : 0);
               const int n = last_blk - first_blk + 1;
-              const uint32_t sf = static_cast<uint32_t>(gc - 1 + first_blk) % NSLOT;
-              const bool wrap = sf + n > NSLOT;
-              const int n1 = wrap ? static_cast<int>(NSLOT - sf) : n;
+              const uint32_t sf = static_cast<uint32_t>(gc - 1) % NSLOT + first_blk;     // physical slot, <= NSLOT + 1
+              constexpr bool wrap = false;
+              const int n1 = n;
               // first-touched outputs need their ring slot handed back (read and zeroed) by the epilogue:
               // block 2, and at t == 0 block 1 too
               if (!pre && !(DBG && p.mode == 1)) {
@@ -552,6 +556,17 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
                 tmem_ld_wait();
 #pragma unroll
                 for (int c = 0; c < NB / 16; ++c) tmem_zero16(taddr + c * 16);   // the slot goes back cleared (completes below)
+                if (sl < 2) {                                  // logical slots 0, 1 have a second home past the ring's end
+                  uint32_t v2[NB];
+                  const uint32_t taddr2 = taddr + NSLOT * NB;
+#pragma unroll
+                  for (int c = 0; c < NB / 16; ++c) tmem_ld16(taddr2 + c * 16, *reinterpret_cast<uint32_t(*)[16]>(&v2[c * 16]));
+                  tmem_ld_wait();
+#pragma unroll
+                  for (int c = 0; c < NB / 16; ++c) tmem_zero16(taddr2 + c * 16);
+#pragma unroll
+                  for (int c = 0; c < NB; ++c) v[c] = __float_as_uint(__uint_as_float(v[c]) + __uint_as_float(v2[c]));
+                }
               }
               if (DBG && p.mode == 2) {
               } else if (!last) {

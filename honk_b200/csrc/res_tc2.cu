@@ -553,9 +553,6 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
               } else {
 #pragma unroll
                 for (int c = 0; c < NB / 16; ++c) tmem_ld16(taddr + c * 16, *reinterpret_cast<uint32_t(*)[16]>(&v[c * 16]));
-                tmem_ld_wait();
-#pragma unroll
-                for (int c = 0; c < NB / 16; ++c) tmem_zero16(taddr + c * 16);   // the slot goes back cleared (completes below)
                 if (sl < 2) {                                  // logical slots 0, 1 have a second home past the ring's end
                   uint32_t v2[NB];
                   const uint32_t taddr2 = taddr + NSLOT * NB;
@@ -566,7 +563,17 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
                   for (int c = 0; c < NB / 16; ++c) tmem_zero16(taddr2 + c * 16);
 #pragma unroll
                   for (int c = 0; c < NB; ++c) v[c] = __float_as_uint(__uint_as_float(v[c]) + __uint_as_float(v2[c]));
+                } else {
+                  tmem_ld_wait();
                 }
+#pragma unroll
+                for (int c = 0; c < NB / 16; ++c) tmem_zero16(taddr + c * 16);   // the slot goes back cleared
+                // hand the slot back as soon as the zeros have landed: the values are in registers, the MMA warp need not
+                // wait for this column's arithmetic and stores
+                tmem_st_wait();
+                fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(a_acc_empty + 8 * sl);
               }
               if (DBG && p.mode == 2) {
               } else if (!last) {
@@ -592,10 +599,10 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
                   }
                 }
               }
-              tmem_st_wait();
-              fence_before();
-              __syncwarp();
-              if (lane == 0) mbar_arrive(a_acc_empty + 8 * sl);
+              if (DBG && p.mode == 3) {
+                __syncwarp();
+                if (lane == 0) mbar_arrive(a_acc_empty + 8 * sl);
+              }
             }
           }
           if (last) {

@@ -447,23 +447,37 @@ extern "C" int honk_listen(const honk_model* m, const honk_frontend* fe, const v
 // ------------------------------------------------------------------------------------------
 namespace {
 
-struct HostPipe {                       // copy stream + events of one call, released on every exit path
-  cudaStream_t copy = nullptr;
-  std::vector<cudaEvent_t> copied;
-  cudaEvent_t start = nullptr;
+struct HostPipe {                       // copy stream + events of the host pipeline; one per calling thread and device, kept
+  cudaStream_t copy = nullptr;          // across calls (creating and destroying them costs ~0.1 ms per call) and released
+  std::vector<cudaEvent_t> copied;      // when the thread exits.  A call synchronises both streams before it returns, so
+  cudaEvent_t start = nullptr;          // the next call of the same thread can reuse them.
+  int device = -1;
   int init(size_t n_chunks) {
-    HONK_CUDA(cudaStreamCreateWithFlags(&copy, cudaStreamNonBlocking));
-    copied.assign(n_chunks, nullptr);
-    for (size_t k = 0; k < n_chunks; ++k) HONK_CUDA(cudaEventCreateWithFlags(&copied[k], cudaEventDisableTiming));
-    HONK_CUDA(cudaEventCreateWithFlags(&start, cudaEventDisableTiming));
+    int dev = 0;
+    HONK_CUDA(cudaGetDevice(&dev));
+    if (dev != device) {
+      release();
+      device = dev;
+    }
+    if (!copy) HONK_CUDA(cudaStreamCreateWithFlags(&copy, cudaStreamNonBlocking));
+    if (!start) HONK_CUDA(cudaEventCreateWithFlags(&start, cudaEventDisableTiming));
+    while (copied.size() < n_chunks) {
+      cudaEvent_t e = nullptr;
+      HONK_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+      copied.push_back(e);
+    }
     return HONK_OK;
   }
-  ~HostPipe() {
+  void release() {
     for (cudaEvent_t e : copied)
       if (e) cudaEventDestroy(e);
+    copied.clear();
     if (start) cudaEventDestroy(start);
     if (copy) cudaStreamDestroy(copy);
+    start = nullptr;
+    copy = nullptr;
   }
+  ~HostPipe() { release(); }
 };
 
 int pcm_elem_bytes(int dtype) { return dtype == HONK_PCM_I16 ? 2 : (dtype == HONK_PCM_F32 ? 4 : 8); }
@@ -508,14 +522,18 @@ std::vector<int64_t> host_chunk_plan(const honk_model* m, int64_t n_clips, int64
   }
   int64_t first = 4;
   if (const char* e = getenv("HONK_HOST_FIRST_WAVES")) first = std::max(1, std::min(1 << 20, atoi(e)));
-  const int64_t cap = std::max(wave, (n_clips / 2 + wave - 1) / wave * wave);
+  int64_t growth = 3;
+  if (const char* e = getenv("HONK_HOST_GROWTH")) growth = std::max(2, std::min(64, atoi(e)));
+  int64_t cap_pct = 50;
+  if (const char* e = getenv("HONK_HOST_CAP_PCT")) cap_pct = std::max(10, std::min(100, atoi(e)));
+  const int64_t cap = std::max(wave, (n_clips * cap_pct / 100 + wave - 1) / wave * wave);
   int64_t next = first * wave, left = n_clips;
   while (left > 0) {
     int64_t c = std::min(std::min(next, cap), left);
     if (left - c < first * wave) c = left;                 // no sliver at the end
     plan.push_back(c);
     left -= c;
-    next *= 3;
+    next *= growth;
   }
   return plan;
 }
@@ -579,7 +597,7 @@ int forward_pcm_host_impl(const honk_model* m, const honk_frontend* fe, const vo
     HONK_TRY(honk_model_forward_pcm(m, fe, base, dtype, n_clips, n_samples, n_samples, d_logits, inner, inner_bytes, s));
     return finish();
   }
-  HostPipe hp;
+  static thread_local HostPipe hp;
   HONK_TRY(hp.init(plan.size()));
   // the scratch may have been handed out in the order of `s`: the copy stream must not run ahead of that
   HONK_CUDA(cudaEventRecord(hp.start, s));

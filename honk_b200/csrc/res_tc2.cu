@@ -164,6 +164,21 @@ __device__ __forceinline__ void tmem_zero16(uint32_t taddr) {
       "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1,%1};" ::"r"(taddr), "r"(0u)
       : "memory");
 }
+__device__ __forceinline__ void tmem_zero8(uint32_t taddr) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1};" ::"r"(taddr), "r"(0u) : "memory");
+}
+// HB = 16 or 24 accumulator columns of this thread's TMEM lane
+template <int HB>
+__device__ __forceinline__ void tmem_ld_cols(uint32_t taddr, uint32_t (&v)[HB]) {
+  static_assert(HB == 16 || HB == 24, "half a slot is 16 or 24 columns");
+  tmem_ld16(taddr, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));
+  if (HB == 24) tmem_ld8(taddr + 16, *reinterpret_cast<uint32_t(*)[8]>(&v[16]));
+}
+template <int HB>
+__device__ __forceinline__ void tmem_zero_cols(uint32_t taddr) {
+  tmem_zero16(taddr);
+  if (HB == 24) tmem_zero8(taddr + 16);
+}
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 #define T2_TIMED(acc, stmt) do { if (DBG) { const long long t__ = clock64(); stmt; acc += clock64() - t__; } else { stmt; } } while (0)
@@ -256,7 +271,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
     }
     for (int k = 0; k < NSLOT; ++k) {
       mbar_init(a_acc_full + 8 * k, 1);
-      mbar_init(a_acc_empty + 8 * k, 4);
+      mbar_init(a_acc_empty + 8 * k, 8);
     }
     for (int k = 0; k < 2; ++k) {
       mbar_init(a_wfull + 8 * k, 1);
@@ -492,7 +507,11 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
     // The two groups of 4 warps take alternate output columns (all NB channels each).  Stored activations
     // are the raw x_L = relu(conv) [+ x_{L-2}]; BatchNorm lives in the next layer's weights (scale) and in
     // its two constant-one input channels (mean shift, exact at the zero-padded borders).
+    // Both groups of 4 warps work on EVERY output column, each on half of its channels (HC channel groups = HB accumulator
+    // columns): a column is drained in about half the time of a whole-column pass, which is what the 8-slot ring needs.
+    constexpr int HC = NCG / 2, HB = NB / 2;
     const int ew = warp - 2, quad = warp & 3, half = ew >> 2;
+    const int cg0 = half * HC;
     const int h = quad * 32 + lane;
     const int sub = h / p.Hp1;                              // clip of a stacked group this row belongs to
     const bool valid = h < p.H && (h - sub * p.Hp1) < p.Hp1 - 1;
@@ -507,7 +526,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
         const int d = ly.d, flags = ly.flags;
         const bool add_res = flags & 1, last = flags & 2;
         const int nseg = ly.n_seg[rank];
-        const long long cstep = 2ll * d * p.col_bytes;        // this group's next column of a segment
+        const long long cstep = static_cast<long long>(d) * p.col_bytes;   // next column of a segment
         for (int ab = 0; ab < nab; ++ab) {
           const int clip = K * pair + ab, slot = K * team + ab;
           unsigned char* Qs = p.Q + static_cast<long long>(slot) * p.slot_stride + (T2_PAD + h) * 16;
@@ -515,59 +534,54 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
           unsigned char* outb = (L & 1) ? Ps : Qs;            // conv0 -> Q; odd: Q -> P; even: P (+Q residual) -> Q in place
           const unsigned char* resb = (flags & 16) ? p.y0 + static_cast<long long>(clip) * p.slot_stride + (T2_PAD + h) * 16 : Qs;
           const bool ld_res = add_res && valid && !(DBG && p.mode == 2);
-          float psum[NB];
+          float psum[HB];
           if (last) {
 #pragma unroll
-            for (int k = 0; k < NB; ++k) psum[k] = 0.f;
+            for (int k = 0; k < HB; ++k) psum[k] = 0.f;
           }
           for (int s = 0; s < nseg; ++s) {
             const T2Seg& sg = ly.seg[rank][s];
             const int j0 = sg.j0, jlim = sg.j0 + sg.n_out;
-            const int o0 = j0 + ((g ^ static_cast<uint32_t>(half)) & 1);   // first column of this group
-            uint32_t gi = g + (o0 - j0);
+            uint32_t gi = g;
             g += sg.n_out;
-            long long off = static_cast<long long>(sg.r + o0 * d) * p.col_bytes;
-            uint4 rv[NCG];                                     // residual, prefetched one column ahead
+            long long off = static_cast<long long>(sg.r + j0 * d) * p.col_bytes + static_cast<long long>(cg0) * plane_bytes;
+            uint4 rv[HC];                                      // residual, prefetched one column ahead
 #pragma unroll
-            for (int c = 0; c < NCG; ++c) rv[c] = make_uint4(0, 0, 0, 0);
-            if (ld_res && o0 < jlim) {
+            for (int c = 0; c < HC; ++c) rv[c] = make_uint4(0, 0, 0, 0);
+            if (ld_res) {
 #pragma unroll
-              for (int c = 0; c < NCG; ++c) rv[c] = ldcg16(resb + off + c * plane_bytes);
+              for (int c = 0; c < HC; ++c) rv[c] = ldcg16(resb + off + c * plane_bytes);
             }
-            for (int o = o0; o < jlim; o += 2, gi += 2, off += cstep) {
+            for (int o = j0; o < jlim; ++o, ++gi, off += cstep) {
               const uint32_t sl = gi % NSLOT;
-              uint4 rc[NCG];
+              uint4 rc[HC];
 #pragma unroll
-              for (int c = 0; c < NCG; ++c) rc[c] = rv[c];
-              if (ld_res && o + 2 < jlim) {
+              for (int c = 0; c < HC; ++c) rc[c] = rv[c];
+              if (ld_res && o + 1 < jlim) {
 #pragma unroll
-                for (int c = 0; c < NCG; ++c) rv[c] = ldcg16(resb + off + cstep + c * plane_bytes);
+                for (int c = 0; c < HC; ++c) rv[c] = ldcg16(resb + off + cstep + c * plane_bytes);
               }
               T2_TIMED(t_wait, mbar_wait(a_acc_full + 8 * sl, (gi / NSLOT) & 1));
               fence_after();
-              uint32_t v[NB];
-              const uint32_t taddr = tmem + (static_cast<uint32_t>(quad * 32) << 16) + sl * NB;
+              uint32_t v[HB];
+              const uint32_t taddr = tmem + (static_cast<uint32_t>(quad * 32) << 16) + sl * NB + half * HB;
               if (DBG && p.mode == 3) {
 #pragma unroll
-                for (int c = 0; c < NB; ++c) v[c] = 0;
+                for (int c = 0; c < HB; ++c) v[c] = 0;
               } else {
-#pragma unroll
-                for (int c = 0; c < NB / 16; ++c) tmem_ld16(taddr + c * 16, *reinterpret_cast<uint32_t(*)[16]>(&v[c * 16]));
+                tmem_ld_cols<HB>(taddr, v);
                 if (sl < 2) {                                  // logical slots 0, 1 have a second home past the ring's end
-                  uint32_t v2[NB];
+                  uint32_t v2[HB];
                   const uint32_t taddr2 = taddr + NSLOT * NB;
-#pragma unroll
-                  for (int c = 0; c < NB / 16; ++c) tmem_ld16(taddr2 + c * 16, *reinterpret_cast<uint32_t(*)[16]>(&v2[c * 16]));
+                  tmem_ld_cols<HB>(taddr2, v2);
                   tmem_ld_wait();
+                  tmem_zero_cols<HB>(taddr2);
 #pragma unroll
-                  for (int c = 0; c < NB / 16; ++c) tmem_zero16(taddr2 + c * 16);
-#pragma unroll
-                  for (int c = 0; c < NB; ++c) v[c] = __float_as_uint(__uint_as_float(v[c]) + __uint_as_float(v2[c]));
+                  for (int c = 0; c < HB; ++c) v[c] = __float_as_uint(__uint_as_float(v[c]) + __uint_as_float(v2[c]));
                 } else {
                   tmem_ld_wait();
                 }
-#pragma unroll
-                for (int c = 0; c < NB / 16; ++c) tmem_zero16(taddr + c * 16);   // the slot goes back cleared
+                tmem_zero_cols<HB>(taddr);                     // the slot goes back cleared
                 // hand the slot back as soon as the zeros have landed: the values are in registers, the MMA warp need not
                 // wait for this column's arithmetic and stores
                 tmem_st_wait();
@@ -578,18 +592,18 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
               if (DBG && p.mode == 2) {
               } else if (!last) {
 #pragma unroll
-                for (int c = 0; c < NCG; ++c) {
+                for (int c = 0; c < HC; ++c) {
                   uint32_t w4[4];
                   const uint32_t* rr = reinterpret_cast<const uint32_t*>(&rc[c]);
 #pragma unroll
                   for (int k = 0; k < 4; ++k)
                     w4[k] = relu_add_h2(pack_h2(__uint_as_float(v[c * 8 + 2 * k]), __uint_as_float(v[c * 8 + 2 * k + 1])), rr[k]);
-                  if (c == NCG - 1) w4[3] = 0x3C003C00u;       // the two constant-one channels
+                  if (c == HC - 1 && half == 1) w4[3] = 0x3C003C00u;   // the two constant-one channels (last channel group)
                   if (valid) stcg16(outb + off + c * plane_bytes, make_uint4(w4[0], w4[1], w4[2], w4[3]));
                 }
               } else if (valid) {
 #pragma unroll
-                for (int c = 0; c < NCG; ++c) {
+                for (int c = 0; c < HC; ++c) {
                   const __half2* rh = reinterpret_cast<const __half2*>(&rc[c]);
 #pragma unroll
                   for (int k = 0; k < 4; ++k) {
@@ -610,11 +624,11 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
             const int s_lo = __shfl_sync(0xffffffffu, sub, 0), s_hi = min(__shfl_sync(0xffffffffu, sub, 31), p.S - 1);
             for (int sc = s_lo; sc <= s_hi; ++sc) {
 #pragma unroll
-              for (int k = 0; k < NB; ++k) {
+              for (int k = 0; k < HB; ++k) {
                 float sum = (sub == sc) ? psum[k] : 0.f;          // invalid rows never accumulated
 #pragma unroll
                 for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-                if (lane == 0) atomicAdd(p.pool + (static_cast<long long>(clip) * p.S + sc) * NB + k, sum);
+                if (lane == 0) atomicAdd(p.pool + (static_cast<long long>(clip) * p.S + sc) * NB + half * HB + k, sum);
               }
             }
           }

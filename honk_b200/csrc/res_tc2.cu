@@ -53,7 +53,10 @@ using namespace umma;
 
 constexpr int T2_G = 4;           // CTAs per team
 constexpr int T2_NSTAGE = 8;      // A-operand stages (one input column each)
-constexpr int T2_THREADS = 352;   // warp 0 producer, 1 MMA, 2-9 epilogue, 10 flag signaller
+// warp 0 producer, 1 MMA, then NG groups of 4 epilogue warps (NG = 3 for 6 channel groups, 2 for 4: 16 accumulator columns
+// per group either way), then the flag signaller
+constexpr int t2_groups(int ncg) { return ncg % 3 == 0 ? 3 : 2; }
+constexpr int t2_threads(int ncg) { return (3 + 4 * t2_groups(ncg)) * 32; }
 constexpr int T2_PAD = 16;        // zero rows above every channel plane (>= max dilation)
 constexpr int T2_MAXSEG = 8;
 constexpr int T2_MAXL = 24;       // C->C layers (res26)
@@ -233,7 +236,8 @@ __device__ __forceinline__ uint32_t probe_issue4_commit(uint32_t pa, uint32_t pa
 }
 
 template <int NCG, bool DBG>
-__global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_constant__ T2Params p) {
+__global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __grid_constant__ T2Params p) {
+  constexpr int NG = t2_groups(NCG), T2_THREADS = t2_threads(NCG), SIG_WARP = 2 + 4 * NG;
   constexpr int NB = NCG * 8;            // padded channels = N block
   constexpr int NKC = NCG / 2;           // K chunks of 16 channels
   constexpr int NPHYS = 512 / NB;        // accumulator slots in TMEM
@@ -271,13 +275,13 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
     }
     for (int k = 0; k < NSLOT; ++k) {
       mbar_init(a_acc_full + 8 * k, 1);
-      mbar_init(a_acc_empty + 8 * k, 8);
+      mbar_init(a_acc_empty + 8 * k, 4 * NG);
     }
     for (int k = 0; k < 2; ++k) {
       mbar_init(a_wfull + 8 * k, 1);
       mbar_init(a_wfree + 8 * k, 1);
     }
-    for (int k = 0; k < 4; ++k) mbar_init(a_done + 8 * k, 8);
+    for (int k = 0; k < 4; ++k) mbar_init(a_done + 8 * k, 4 * NG);
     mbar_init(smem_u32(&bar_dbg), 1);
     fence_mbar_init();
   }
@@ -502,15 +506,16 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
       long long* o = p.dbg + blockIdx.x * T2_NDBG;
       o[3] = clock64() - t_start; o[4] = t_acc; o[5] = t_full; o[6] = t_w; o[11] = n_hit; o[12] = n_task;
     }
-  } else if (warp < 10 && !(DBG && p.mode == 1)) {
+  } else if (warp < SIG_WARP && !(DBG && p.mode == 1)) {
     // ======================================= epilogue =======================================
     // The two groups of 4 warps take alternate output columns (all NB channels each).  Stored activations
     // are the raw x_L = relu(conv) [+ x_{L-2}]; BatchNorm lives in the next layer's weights (scale) and in
     // its two constant-one input channels (mean shift, exact at the zero-padded borders).
-    // Both groups of 4 warps work on EVERY output column, each on half of its channels (HC channel groups = HB accumulator
-    // columns): a column is drained in about half the time of a whole-column pass, which is what the 8-slot ring needs.
-    constexpr int HC = NCG / 2, HB = NB / 2;
-    const int ew = warp - 2, quad = warp & 3, half = ew >> 2;
+    // All NG groups of 4 warps work on EVERY output column, each on its share of the channels (HC channel groups = HB
+    // accumulator columns): a column is drained in 1/NG of the time of a whole-column pass, which is what the 8-slot ring
+    // needs.
+    constexpr int HC = NCG / NG, HB = HC * 8;
+    const int ew = warp - 2, quad = warp & 3, half = ew >> 2;   // half = this warp's group
     const int cg0 = half * HC;
     const int h = quad * 32 + lane;
     const int sub = h / p.Hp1;                              // clip of a stacked group this row belongs to
@@ -598,7 +603,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
 #pragma unroll
                   for (int k = 0; k < 4; ++k)
                     w4[k] = relu_add_h2(pack_h2(__uint_as_float(v[c * 8 + 2 * k]), __uint_as_float(v[c * 8 + 2 * k + 1])), rr[k]);
-                  if (c == HC - 1 && half == 1) w4[3] = 0x3C003C00u;   // the two constant-one channels (last channel group)
+                  if (c == HC - 1 && half == NG - 1) w4[3] = 0x3C003C00u;   // the two constant-one channels (last channel group)
                   if (valid) stcg16(outb + off + c * plane_bytes, make_uint4(w4[0], w4[1], w4[2], w4[3]));
                 }
               } else if (valid) {
@@ -639,7 +644,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) tc2_res_kernel(const __grid_con
       }
     }
     if (DBG && etid == 0) { long long* o = p.dbg + blockIdx.x * T2_NDBG; o[7] = t_wait; o[8] = clock64() - t_start_e; }
-  } else if (warp == 10 && !(DBG && p.mode == 1)) {
+  } else if (warp == SIG_WARP && !(DBG && p.mode == 1)) {
     // ======================================= flag signaller =================================
     // Publishes "all stores of this CTA for (clip, layer) are visible" to the team: waits until the eight
     // epilogue warps have arrived, then a gpu-scope fence (cumulative over the stores observed through the
@@ -1396,11 +1401,11 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
     ProfSpan span("res_conv", s);
     const dim3 grid(teams * md.G);
     if (p->ncg == 6) {
-      if (dbg) tc2_res_kernel<6, true><<<grid, T2_THREADS, p->smem_bytes, s>>>(a);
-      else tc2_res_kernel<6, false><<<grid, T2_THREADS, p->smem_bytes, s>>>(a);
+      if (dbg) tc2_res_kernel<6, true><<<grid, t2_threads(6), p->smem_bytes, s>>>(a);
+      else tc2_res_kernel<6, false><<<grid, t2_threads(6), p->smem_bytes, s>>>(a);
     } else {
-      if (dbg) tc2_res_kernel<4, true><<<grid, T2_THREADS, p->smem_bytes, s>>>(a);
-      else tc2_res_kernel<4, false><<<grid, T2_THREADS, p->smem_bytes, s>>>(a);
+      if (dbg) tc2_res_kernel<4, true><<<grid, t2_threads(4), p->smem_bytes, s>>>(a);
+      else tc2_res_kernel<4, false><<<grid, t2_threads(4), p->smem_bytes, s>>>(a);
     }
     HONK_LAUNCH_CHECK();
   }

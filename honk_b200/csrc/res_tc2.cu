@@ -33,9 +33,12 @@
 // through all layers in lockstep (A.L, B.L, A.L+1, ...), so the team-wide "layer L of clip A
 // done" flag (a release counter in global memory) is hidden behind the other clips' work.  Each
 // CTA owns whole chains (or chain segments with one halo input column per cut).  Roles: warp 0 =
-// bulk-copy (TMA) producer, warp 1 = MMA issuer, warps 2-9 = epilogue (TMEM -> ReLU + residual ->
-// f16 -> L2; two groups of 4 warps take alternate columns), warp 10 = flag signaller.
+// bulk-copy (TMA) producer, warp 1 = MMA issuer, then NG groups of 4 epilogue warps (TMEM -> ReLU + residual ->
+// f16 -> L2; every group drains every output column, 16 accumulator columns = 2 channel groups each, so a
+// slot of the 8-slot logical TMEM ring goes back in 1/NG of a whole-column pass), last warp = flag signaller.
 // Working set: 37 teams x 2 clips x 2 buffers x 449 KB = 66 MB, L2-resident.
+// Pooled models (res8, res26) run on the same kernel from layer 1 with S clips stacked along the time axis
+// per 128-row tile (see res_tc2_plan_create).
 #include "res_tc.cuh"
 #include "umma.cuh"
 

@@ -98,18 +98,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1)
 // PAIR: cluster of 2, leader issues cta_group::2 MMAs (B tiles hold N/2 rows per CTA).  copies: thread 64 of every CTA
 // keeps a ring of four 12 KB bulk copies from an L2-resident buffer in flight while the MMAs run.
 template <bool PAIR>
-__global__ void __launch_bounds__(128, 1) rate2_probe(long long* out, const unsigned char* __restrict__ gsrc, int N, int iters, int copies) {
+__global__ void __launch_bounds__(128, 1) rate2_probe(long long* out, const unsigned char* __restrict__ gsrc, int N, int iters, int copies,
+                                                      int shift_rows = 16, int plane_rows = 160) {
   extern __shared__ __align__(1024) unsigned char smem[];
   __shared__ __align__(8) uint64_t bar, cbar[4];
   __shared__ uint32_t tmem_base_s;
   __shared__ volatile int stop;
   const uint32_t rank = PAIR ? cluster_ctarank() : 0;
   const int NB = PAIR ? N / 2 : N;
-  constexpr int PLANE = 160 * 16;                       // A: 6 planes (3 K chunks x 2 halves) of 160 rows
+  const int PLANE = plane_rows * 16;                    // A: 6 planes (3 K chunks x 2 halves) of plane_rows rows (room: 6 x 2560 B)
   unsigned char* sA = smem;                             // 6 * 2560 = 15360
-  unsigned char* sB = smem + 6 * PLANE;                 // 9 tiles * 2 * NB * 16
+  unsigned char* sB = smem + 6 * 2560;                  // 9 tiles * 2 * NB * 16
   unsigned char* sC = sB + 9 * 2 * NB * 16;             // copy ring: 4 x 12288
-  const int words = (6 * PLANE + 9 * 2 * NB * 16) / 4;
+  const int words = (6 * 2560 + 9 * 2 * NB * 16) / 4;
   for (int i = threadIdx.x; i < words; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
   fence_async_smem();
   const int warp = threadIdx.x >> 5;
@@ -148,7 +149,7 @@ __global__ void __launch_bounds__(128, 1) rate2_probe(long long* out, const unsi
     for (int r = 0; r < iters; ++r) {
       for (int i = 0; i < 9; ++i) {
         const int kh = i / 3, kc = i - kh * 3;
-        const uint64_t ad = make_desc(smem_u32(sA) + kc * 2 * PLANE + kh * 16 * 16, PLANE, 128);
+        const uint64_t ad = make_desc(smem_u32(sA) + kc * 2 * PLANE + kh * shift_rows * 16, PLANE, 128);
         const uint64_t bd = make_desc(smem_u32(sB) + i * 2 * NB * 16, NB * 16, 128);
         if (PAIR) mma2_f16_ss(tmem, ad, bd, idesc, 1); else mma_f16_ss(tmem, ad, bd, idesc, 1);
       }
@@ -166,6 +167,51 @@ __global__ void __launch_bounds__(128, 1) rate2_probe(long long* out, const unsi
   __syncthreads();
   if (PAIR) cluster_sync();
   if (warp == 0) { if (PAIR) tmem_dealloc2(tmem, 256); else tmem_dealloc(tmem, 256); }
+}
+
+// (3) kernel-like issue pattern: per task 9 MMAs into a rotating accumulator slot (48-column steps over 8 slots) followed by
+// `ncommit` tcgen05.commit to rotating mbarriers nobody waits on.  Does the per-task bookkeeping cost tensor time?
+__global__ void __launch_bounds__(128, 1) task_probe(long long* out, int N, int iters, int ncommit, int rotate) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  __shared__ __align__(8) uint64_t bar, cb[16];
+  __shared__ uint32_t tmem_base_s;
+  constexpr int PLANE = 160 * 16;
+  unsigned char* sA = smem;
+  unsigned char* sB = smem + 6 * PLANE;
+  const int words = (6 * PLANE + 9 * 2 * 144 * 16) / 4;
+  for (int i = threadIdx.x; i < words; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0u;
+  fence_async_smem();
+  const int warp = threadIdx.x >> 5;
+  if (warp == 0) tmem_alloc(smem_u32(&tmem_base_s), 512);
+  if (threadIdx.x == 32) {
+    mbar_init(smem_u32(&bar), 1);
+    for (int k = 0; k < 16; ++k) mbar_init(smem_u32(&cb[k]), 1);
+    fence_mbar_init();
+  }
+  fence_before();
+  __syncthreads();
+  fence_after();
+  const uint32_t tmem = tmem_base_s;
+  if (threadIdx.x == 0) {
+    const uint32_t idesc = make_idesc(128, N, 0);
+    const long long t0 = clock64();
+    for (int r = 0; r < iters; ++r) {
+      const uint32_t d = tmem + (rotate ? (r & 7) * 48 : 0);
+      for (int i = 0; i < 9; ++i) {
+        const int kh = i / 3, kc = i - kh * 3;
+        const uint64_t ad = make_desc(smem_u32(sA) + kc * 2 * PLANE + kh * 16, PLANE, 128);
+        const uint64_t bd = make_desc(smem_u32(sB) + i * 2 * 144 * 16, 144 * 16, 128);
+        mma_f16_ss(d, ad, bd, idesc, 1);
+      }
+      for (int c = 0; c < ncommit; ++c) commit(smem_u32(&cb[(r * 2 + c) & 15]));
+    }
+    commit(smem_u32(&bar));
+    mbar_wait(smem_u32(&bar), 0);
+    out[0] = clock64() - t0;
+  }
+  fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
 }
 
 int main() {
@@ -241,11 +287,39 @@ int main() {
     at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    CK(cudaLaunchKernelEx(&cfg, rate2_probe<true>, dout, (const unsigned char*)dsrc, N, iters, copies));
+    CK(cudaLaunchKernelEx(&cfg, rate2_probe<true>, dout, (const unsigned char*)dsrc, N, iters, copies, 16, 160));
     CK(cudaDeviceSynchronize());
     CK(cudaMemcpy(h, dout, 24, cudaMemcpyDeviceToHost));
     printf("rate pair   M=256 N=144 copies=%d: %.1f clk/MMA, %.1f clk/task (two columns), %.2f / %.2f 12KB-copies per task in CTA 0 / 1\n",
            copies, double(h[0]) / (9.0 * iters), double(h[0]) / iters, double(h[1]) / iters, double(h[2]) / iters);
+  }
+  {
+    const int smem3 = 6 * 2560 + 9 * 2 * 144 * 16 + 1024;
+    CK(cudaFuncSetAttribute(task_probe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem3));
+    for (int Nn : {144, 96, 48})
+      for (int nc : {0, 1, 2, 3})
+        for (int rot : {0, 1}) {
+          if (Nn != 144 && (nc == 3 || rot == 0)) continue;
+          long long h[1];
+          CK(cudaMemset(dout, 0, 64));
+          task_probe<<<1, 128, smem3>>>(dout, Nn, 2000, nc, rot);
+          CK(cudaDeviceSynchronize());
+          CK(cudaMemcpy(h, dout, 8, cudaMemcpyDeviceToHost));
+          printf("task_probe N=%3d commits/task=%d rotating-slot=%d: %.1f clk/task (9 MMAs)\n", Nn, nc, rot, double(h[0]) / 2000);
+        }
+  }
+  // A-operand alignment: time taps are start-address offsets of kh * d rows (16 B each) and the K halves sit plane_rows * 16 B apart
+  for (int plane_rows : {160, 117}) {
+    for (int shift : {16, 8, 4, 2, 1}) {
+      if (plane_rows * 16 * 5 + (2 * shift + 128) * 16 > 6 * 2560) continue;
+      long long h[3];
+      CK(cudaMemset(dout, 0, 64));
+      rate2_probe<false><<<1, 128, smem1>>>(dout, dsrc, N, iters, 0, shift, plane_rows);
+      CK(cudaDeviceSynchronize());
+      CK(cudaMemcpy(h, dout, 24, cudaMemcpyDeviceToHost));
+      printf("rate single N=144, A taps shifted by %2d rows, K halves %4d B apart: %.1f clk/MMA\n", shift, plane_rows * 16,
+             double(h[0]) / (9.0 * iters));
+    }
   }
   return 0;
 }

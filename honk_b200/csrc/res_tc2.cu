@@ -61,6 +61,7 @@ constexpr int T2_NSTAGE = 8;      // A-operand stages (one input column each)
 constexpr int t2_groups(int ncg) { return ncg % 3 == 0 ? 3 : 2; }
 constexpr int t2_threads(int ncg) { return (3 + 4 * t2_groups(ncg)) * 32; }
 constexpr int T2_PAD = 16;        // zero rows above every channel plane (>= max dilation)
+constexpr int T2_NTB = 32;        // "task done" barriers (ring): ONE tcgen05.commit per task serves the producer and the epilogue
 constexpr int T2_MAXSEG = 8;
 constexpr int T2_MAXL = 24;       // C->C layers (res26)
 constexpr int T2_NDBG = 16;       // debug counters per CTA
@@ -252,8 +253,14 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
   constexpr int NSPLIT = NMMA / 2 + 1;   // MMAs issued before the look-ahead probe of the next task
 
   extern __shared__ __align__(1024) unsigned char smem[];
-  __shared__ __align__(8) uint64_t bar_full[T2_NSTAGE], bar_empty[T2_NSTAGE];
-  __shared__ __align__(8) uint64_t bar_acc_full[NSLOT], bar_acc_empty[NSLOT];
+  // A tcgen05.commit costs the issuing thread ~97 clk and an MMA ~54 clk (scripts/umma2_probe.cu): with the two or three
+  // commits per task of a per-stage "empty" and a per-slot "accumulator full" barrier the issue stream (~700 clk) was
+  // longer than the 648 clk the 9 MMAs take.  Hence one barrier per TASK, task t -> bar_task[t % T2_NTB]: the producer
+  // waits for task it - T2_NSTAGE before refilling its stage, the epilogue for the task that contributes last to a column.
+  // A waiter is never a whole ring behind: the MMA warp runs at most T2_NSTAGE tasks ahead of the producer's loads and,
+  // through the accumulator ring, fewer than ~10 tasks ahead of the epilogue.
+  __shared__ __align__(8) uint64_t bar_full[T2_NSTAGE], bar_task[T2_NTB];
+  __shared__ __align__(8) uint64_t bar_acc_empty[NSLOT];
   __shared__ __align__(8) uint64_t bar_wfull[2], bar_wfree[2];
   __shared__ __align__(8) uint64_t bar_done[4];        // epilogue -> signaller: this CTA's stores of one (clip, layer) are issued
   __shared__ __align__(8) uint64_t bar_dbg;            // debug mode 1: pipe drain
@@ -261,8 +268,8 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
 
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);      // provably warp-uniform: keeps role code on the uniform datapath
-  const uint32_t a_full = keep(smem_u32(&bar_full[0])), a_empty = keep(smem_u32(&bar_empty[0]));
-  const uint32_t a_acc_full = keep(smem_u32(&bar_acc_full[0])), a_acc_empty = keep(smem_u32(&bar_acc_empty[0]));
+  const uint32_t a_full = keep(smem_u32(&bar_full[0])), a_task = keep(smem_u32(&bar_task[0]));
+  const uint32_t a_acc_empty = keep(smem_u32(&bar_acc_empty[0]));
   const uint32_t a_wfull = keep(smem_u32(&bar_wfull[0])), a_wfree = keep(smem_u32(&bar_wfree[0]));
   const uint32_t a_done = keep(smem_u32(&bar_done[0]));
   const int G = p.G, L0 = p.L0;
@@ -272,14 +279,9 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
 
   if (warp == 1) tmem_alloc(smem_u32(&tmem_base_s), 512);
   if (tid == 0) {
-    for (int s = 0; s < T2_NSTAGE; ++s) {
-      mbar_init(a_full + 8 * s, 1);
-      mbar_init(a_empty + 8 * s, 1);
-    }
-    for (int k = 0; k < NSLOT; ++k) {
-      mbar_init(a_acc_full + 8 * k, 1);
-      mbar_init(a_acc_empty + 8 * k, 4 * NG);
-    }
+    for (int s = 0; s < T2_NSTAGE; ++s) mbar_init(a_full + 8 * s, 1);
+    for (int k = 0; k < T2_NTB; ++k) mbar_init(a_task + 8 * k, 1);
+    for (int k = 0; k < NSLOT; ++k) mbar_init(a_acc_empty + 8 * k, 4 * NG);
     for (int k = 0; k < 2; ++k) {
       mbar_init(a_wfull + 8 * k, 1);
       mbar_init(a_wfree + 8 * k, 1);
@@ -348,7 +350,10 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
               const int r = sg.r, jin0 = sg.jin0, n_in = sg.n_in;
               for (int t = 0; t < n_in; ++t, ++it) {
                 const int st = it % T2_NSTAGE;
-                T2_TIMED(t_empty, mbar_wait(a_empty + 8 * st, ((it / T2_NSTAGE) & 1) ^ 1));
+                if (it >= T2_NSTAGE) {                     // the task that last read this stage is done
+                  const uint32_t tp = it - T2_NSTAGE;
+                  T2_TIMED(t_empty, mbar_wait(a_task + 8 * (tp % T2_NTB), (tp / T2_NTB) & 1));
+                }
                 const uint32_t full = a_full + 8 * st;
                 mbar_expect_tx(full, bytes);
                 bulk_load(smem_u32(stages + st * p.stage_stride), in + (r + (jin0 + t) * d) * colb, bytes, full);
@@ -378,7 +383,7 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
     const uint32_t a_st0 = a_lbo | (smem_u32(stages) >> 4);
     const uint32_t pr2 = 2 * p.plane_rows;
     constexpr uint32_t IDESC0 = make_idesc(128, 0, 0), IDESC_BLK = static_cast<uint32_t>(NB >> 3) << 17;
-    uint32_t st = 0, stpar = 0, q = 0;
+    uint32_t st = 0, stpar = 0, q = 0, tk = 0;  // tk = running task index (the producer's `it`, the epilogue's `tk0 + ...`)
     uint32_t a_st = a_st0;                      // low descriptor word of stage st
     int gseg = 2 * NSLOT;                       // ring index of the segment's first output (offset keeps halo indices >= 0)
     long long t_acc = 0, t_full = 0, t_w = 0, n_task = 0, n_hit = 0;
@@ -459,9 +464,8 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
                   bd[i] = b_hi | static_cast<uint64_t>(b_f + ii * 6 * NB);
                 }
                 const uint32_t ok = probe_issue4_commit(
-                    pa, pap, pb, pbp, d1, id1, ad[0], ad[1], ad[2], ad[3], bd[0], bd[1], bd[2], bd[3], a_empty + 8 * st,
-                    lo_in ? a_acc_full + 8 * (static_cast<uint32_t>(gc - 1) % NSLOT) : 0u,
-                    (t == n_in - 1 && c_in) ? a_acc_full + 8 * (static_cast<uint32_t>(gc) % NSLOT) : 0u);
+                    pa, pap, pb, pbp, d1, id1, ad[0], ad[1], ad[2], ad[3], bd[0], bd[1], bd[2], bd[3], a_task + 8 * (tk % T2_NTB),
+                    0u, 0u);
                 __syncwarp();
                 pre = ok && has_next;
                 if (DBG && has_next) { n_task += 1; n_hit += pre; }
@@ -484,12 +488,11 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
                   if (!wrap) issue_mmas<NSPLIT, NMMA, NKC, NB, false>(a_hi, a_st, pr2, d, b_hi, b_f, d1, id1, tmem, id2, b2);
                   else issue_mmas<NSPLIT, NMMA, NKC, NB, true>(a_hi, a_st, pr2, d, b_hi, b_f, d1, id1, tmem, id2, b2);
                 }
-                commit(a_empty + 8 * st);
-                if (lo_in) commit(a_acc_full + 8 * (static_cast<uint32_t>(gc - 1) % NSLOT));
-                if (t == n_in - 1 && c_in) commit(a_acc_full + 8 * (static_cast<uint32_t>(gc) % NSLOT));
+                commit(a_task + 8 * (tk % T2_NTB));
               }
               __syncwarp();
               }
+              ++tk;
               a_st += stage16;
               if (++st == T2_NSTAGE) { st = 0; stpar ^= 1; a_st = a_st0; }
             }
@@ -524,7 +527,7 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
     const int sub = h / p.Hp1;                              // clip of a stacked group this row belongs to
     const bool valid = h < p.H && (h - sub * p.Hp1) < p.Hp1 - 1;
     const int etid = ew * 32 + lane;
-    uint32_t g = 0, ev = 0;
+    uint32_t g = 0, ev = 0, tk0 = 0;            // tk0 = tasks before the current segment (same order as the MMA warp)
     long long t_wait = 0;
     const long long t_start_e = clock64();
     for (int pair = team; pair < n_pairs; pair += n_teams) {
@@ -552,6 +555,9 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
             const int j0 = sg.j0, jlim = sg.j0 + sg.n_out;
             uint32_t gi = g;
             g += sg.n_out;
+            const uint32_t tks = tk0;                          // task index of this segment's first input column
+            tk0 += sg.n_in;
+            const int jin0 = sg.jin0, jin_last = sg.jin0 + sg.n_in - 1;
             long long off = static_cast<long long>(sg.r + j0 * d) * p.col_bytes + static_cast<long long>(cg0) * plane_bytes;
             uint4 rv[HC];                                      // residual, prefetched one column ahead
 #pragma unroll
@@ -569,7 +575,9 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
 #pragma unroll
                 for (int c = 0; c < HC; ++c) rv[c] = ldcg16(resb + off + cstep + c * plane_bytes);
               }
-              T2_TIMED(t_wait, mbar_wait(a_acc_full + 8 * sl, (gi / NSLOT) & 1));
+              // column o is complete when the task of input column min(o + 1, last input of the segment) is
+              const uint32_t tkc = tks + static_cast<uint32_t>(min(o + 1, jin_last) - jin0);
+              T2_TIMED(t_wait, mbar_wait(a_task + 8 * (tkc % T2_NTB), (tkc / T2_NTB) & 1));
               fence_after();
               uint32_t v[HB];
               const uint32_t taddr = tmem + (static_cast<uint32_t>(quad * 32) << 16) + sl * NB + half * HB;

@@ -214,6 +214,48 @@ __global__ void __launch_bounds__(128, 1) task_probe(long long* out, int N, int 
   if (warp == 0) tmem_dealloc(tmem, 512);
 }
 
+// (4) is the ~54 clk issue cost of a tcgen05.mma per issuing THREAD or per SM?  `nthr` threads (lane 0 of warps 0..nthr-1)
+// each issue iters x 9 MMAs of width N into their own accumulator columns.
+__global__ void __launch_bounds__(128, 1) dual_probe(long long* out, int N, int iters, int nthr) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  __shared__ __align__(8) uint64_t bar[4];
+  __shared__ uint32_t tmem_base_s;
+  constexpr int PLANE = 160 * 16;
+  unsigned char* sA = smem;
+  unsigned char* sB = smem + 6 * PLANE;
+  const int words = (6 * PLANE + 9 * 2 * 144 * 16) / 4;
+  for (int i = threadIdx.x; i < words; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0u;
+  fence_async_smem();
+  const int warp = threadIdx.x >> 5;
+  if (warp == 0) tmem_alloc(smem_u32(&tmem_base_s), 512);
+  if (threadIdx.x == 32) {
+    for (int k = 0; k < 4; ++k) mbar_init(smem_u32(&bar[k]), 1);
+    fence_mbar_init();
+  }
+  fence_before();
+  __syncthreads();
+  fence_after();
+  const uint32_t tmem = tmem_base_s;
+  const long long t0 = clock64();
+  if ((threadIdx.x & 31) == 0 && warp < nthr) {
+    const uint32_t idesc = make_idesc(128, N, 0);
+    const uint32_t d = tmem + warp * 128;
+    for (int r = 0; r < iters; ++r)
+      for (int i = 0; i < 9; ++i) {
+        const int kh = i / 3, kc = i - kh * 3;
+        const uint64_t ad = make_desc(smem_u32(sA) + kc * 2 * PLANE + kh * 16, PLANE, 128);
+        const uint64_t bd = make_desc(smem_u32(sB) + i * 2 * 144 * 16, 144 * 16, 128);
+        mma_f16_ss(d, ad, bd, idesc, 1);
+      }
+    commit(smem_u32(&bar[warp]));
+    mbar_wait(smem_u32(&bar[warp]), 0);
+    out[warp] = clock64() - t0;
+  }
+  fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
 int main() {
   // ---- correctness ----
   for (int N : {144, 96, 48}) {
@@ -307,6 +349,22 @@ int main() {
           CK(cudaMemcpy(h, dout, 8, cudaMemcpyDeviceToHost));
           printf("task_probe N=%3d commits/task=%d rotating-slot=%d: %.1f clk/task (9 MMAs)\n", Nn, nc, rot, double(h[0]) / 2000);
         }
+  }
+  {
+    const int smem3 = 6 * 2560 + 9 * 2 * 144 * 16 + 1024;
+    CK(cudaFuncSetAttribute(dual_probe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem3));
+    for (int Nn : {48, 64, 96})
+      for (int nthr : {1, 2, 3}) {
+        long long h[4] = {0, 0, 0, 0};
+        CK(cudaMemset(dout, 0, 64));
+        dual_probe<<<1, 128, smem3>>>(dout, Nn, 1800 / nthr, nthr);
+        CK(cudaDeviceSynchronize());
+        CK(cudaMemcpy(h, dout, 32, cudaMemcpyDeviceToHost));
+        long long mx = 0;
+        for (int k = 0; k < nthr; ++k) mx = h[k] > mx ? h[k] : mx;
+        printf("dual_probe N=%3d, %d issuing thread(s), %d MMAs in total: %.1f clk/MMA\n", Nn, nthr, 9 * (1800 / nthr) * nthr,
+               double(mx) / (9.0 * (1800 / nthr) * nthr));
+      }
   }
   // A-operand alignment: time taps are start-address offsets of kh * d rows (16 B each) and the K halves sit plane_rows * 16 B apart
   for (int plane_rows : {160, 117}) {

@@ -53,7 +53,7 @@ constexpr int CT_NPOS = CT_HO2 * CT_WO2;        // 416 positions -> 26624 featur
 constexpr int CT_NTILE = 5;                     // M = 128 tiles over the 13*41 = 533 flat rows
 constexpr int CT_NSLAB = CT_KH2 * CT_KW2;       // weight slabs (one tap each: 4 channel chunks x 2 KB)
 constexpr int CT_NS2 = 6;                       // slabs in flight
-constexpr int CT_THREADS = 320;
+constexpr int CT_THREADS = 352;                 // warp 0 producer, 1 and 10 MMA issuers, 2-9 epilogue
 constexpr int CT_X8_ROWS = CT_WO1 * CT_H;       // 3232 units per clip
 constexpr int CT_X8_BYTES = CT_X8_ROWS * 16;    // 51712
 constexpr int CT_X8_ALLOC = (CT_X8_ROWS + 48) * 16;                   // over-read of the last column's tile
@@ -128,19 +128,19 @@ __global__ void __launch_bounds__(CT_THREADS, 1) cnn_tc_kernel(const __grid_cons
   if (warp == 1) tmem_alloc(smem_u32(&tmem_base_s), 512);
   if (tid == 0) {
     mbar_init(a_xfull, 1);
-    mbar_init(a_xfree, 1);
+    mbar_init(a_xfree, 2);                      // both MMA issuers
     mbar_init(a_w1, 1);
     for (int s = 0; s < CT_NS2; ++s) {
       mbar_init(a_wfull + 8 * s, 1);
-      mbar_init(a_wempty + 8 * s, 1);
+      mbar_init(a_wempty + 8 * s, 2);
     }
     for (int k = 0; k < 3; ++k) {
       mbar_init(a_c1full + 8 * k, 1);
       mbar_init(a_c1empty + 8 * k, 4);
     }
     mbar_init(a_y1ready, 8);
-    mbar_init(a_y1free, 1);
-    mbar_init(a_c2full, 1);
+    mbar_init(a_y1free, 2);
+    mbar_init(a_c2full, 2);
     mbar_init(a_c2empty, 8);
     fence_mbar_init();
   }
@@ -173,8 +173,13 @@ __global__ void __launch_bounds__(CT_THREADS, 1) cnn_tc_kernel(const __grid_cons
         }
       }
     }
-  } else if (warp == 1) {
-    // ======================================= MMA issuer =====================================
+  } else if (warp == 1 || warp == 10) {
+    // ======================================= MMA issuers ====================================
+    // A tcgen05.mma costs its issuing thread ~54 clk (scripts/umma2_probe.cu: dual_probe), more than the 48 clk an N = 64
+    // MMA takes to execute, so one issuing thread cannot keep the pipe full; two threads can.  Issuer q takes the conv1
+    // output columns of parity q and, in conv2, its own accumulator tiles (0-2 / 3-4): no accumulator is shared.
+    const int q = warp == 1 ? 0 : 1;
+    const int t_lo = q == 0 ? 0 : 3, t_hi = q == 0 ? 3 : CT_NTILE;
     constexpr uint32_t IDESC = make_idesc(128, CT_C, 0);
     // conv1: A K halves one row (16 B) apart, 8-row groups contiguous; B tile [2][64][8]
     const uint64_t a1_hi = make_desc(0, 16, 128) & 0xFFFFFFFF00000000ull;
@@ -192,6 +197,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) cnn_tc_kernel(const __grid_cons
       mbar_wait(a_xfull, k & 1);
       fence_after();
       for (int w = 0; w < CT_WO1; ++w, ++cw) {
+        if ((w & 1) != q) continue;
         const uint32_t buf = cw % 3;
         mbar_wait(a_c1empty + 8 * buf, ((cw / 3) & 1) ^ 1);
         fence_after();
@@ -218,8 +224,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) cnn_tc_kernel(const __grid_cons
           const int kh = s / CT_KW2, kw = s - kh * CT_KW2;
           const uint32_t a_tap = a2_lo0 + kh + kw * CT_HP;
           const uint32_t b_lo = b2_lo0 + st * (CT_SLAB_BYTES / 16);
-#pragma unroll
-          for (int t = 0; t < CT_NTILE; ++t) {
+          for (int t = t_lo; t < t_hi; ++t) {
 #pragma unroll
             for (int kc = 0; kc < 4; ++kc)
               mma_f16_ss(tmem + t * CT_C, a2_hi | static_cast<uint64_t>(a_tap + t * 128 + 2 * kc * CT_R2),

@@ -176,8 +176,10 @@ __global__ void __launch_bounds__(CT_THREADS, 1) cnn_tc_kernel(const __grid_cons
   } else if (warp == 1 || warp == 10) {
     // ======================================= MMA issuers ====================================
     // A tcgen05.mma costs its issuing thread ~54 clk (scripts/umma2_probe.cu: dual_probe), more than the 48 clk an N = 64
-    // MMA takes to execute, so one issuing thread cannot keep the pipe full; two threads can.  Issuer q takes the conv1
-    // output columns of parity q and, in conv2, its own accumulator tiles (0-2 / 3-4): no accumulator is shared.
+    // MMA takes to execute, so one issuing thread cannot keep the pipe full; two threads can.  No accumulator is shared:
+    // in conv1 issuer 1 takes the columns that land in accumulator buffer 2 and issuer 0 those of buffers 0 and 1 (every
+    // buffer's full / empty barriers then see the uses of ONE in-order issuer, which the parity waits rely on); in conv2
+    // issuer 0 owns tiles 0-2 and issuer 1 tiles 3-4.
     const int q = warp == 1 ? 0 : 1;
     const int t_lo = q == 0 ? 0 : 3, t_hi = q == 0 ? 3 : CT_NTILE;
     constexpr uint32_t IDESC = make_idesc(128, CT_C, 0);
@@ -197,8 +199,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) cnn_tc_kernel(const __grid_cons
       mbar_wait(a_xfull, k & 1);
       fence_after();
       for (int w = 0; w < CT_WO1; ++w, ++cw) {
-        if ((w & 1) != q) continue;
         const uint32_t buf = cw % 3;
+        if ((buf == 2) != (q == 1)) continue;      // issuer 1 owns accumulator buffer 2, issuer 0 buffers 0 and 1
         mbar_wait(a_c1empty + 8 * buf, ((cw / 3) & 1) ^ 1);
         fence_after();
         if (elect_one()) {

@@ -514,7 +514,7 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
     }
   } else if (warp < SIG_WARP && !(DBG && p.mode == 1)) {
     // ======================================= epilogue =======================================
-    // The two groups of 4 warps take alternate output columns (all NB channels each).  Stored activations
+    // Every group of 4 warps drains its share of the channels of every output column.  Stored activations
     // are the raw x_L = relu(conv) [+ x_{L-2}]; BatchNorm lives in the next layer's weights (scale) and in
     // its two constant-one input channels (mean shift, exact at the zero-padded borders).
     // All NG groups of 4 warps work on EVERY output column, each on its share of the channels (HC channel groups = HB

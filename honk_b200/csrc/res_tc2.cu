@@ -191,17 +191,16 @@ __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.
 #define T2_TIMED(acc, stmt) do { if (DBG) { const long long t__ = clock64(); stmt; acc += clock64() - t__; } else { stmt; } } while (0)
 
 // MMAs [I0, I1) of one task: index i = kh * NK + kc reads the A rows shifted by kh*d and the 16-channel chunk kc, against B
-// tile i.  WRAP: the task's N blocks straddle the end of the TMEM ring and every MMA is issued in two parts.
-template <int I0, int I1, int NK, int NB, bool WRAP>
+// tile i.  (A task's accumulator slots never straddle the end of TMEM: see NPHYS / NSLOT in the kernel.)
+template <int I0, int I1, int NK, int NB>
 __device__ __forceinline__ void issue_mmas(uint64_t a_hi, uint32_t a_lo, uint32_t pr2, uint32_t d, uint64_t b_hi, uint32_t b_f,
-                                           uint32_t d1, uint32_t id1, uint32_t d2, uint32_t id2, uint32_t b2) {
+                                           uint32_t d1, uint32_t id1) {
 #pragma unroll
   for (int i = I0; i < I1; ++i) {
     const int kh = i / NK, kc = i - kh * NK;
     const uint64_t ad = a_hi | static_cast<uint64_t>(a_lo + kc * pr2 + kh * d);
     const uint64_t bd = b_hi | static_cast<uint64_t>(b_f + i * 6 * NB);
     mma_f16_ss(d1, ad, bd, id1, 1);
-    if (WRAP) mma_f16_ss(d2, ad, bd + static_cast<uint64_t>(b2), id2, 1);
   }
 }
 
@@ -410,8 +409,6 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
               const int first_blk = lo_in ? 0 : (c_in ? 1 : 2), last_blk = hi_in ? 2 : (c_in ? 1 : 0);
               const int n = last_blk - first_blk + 1;
               const uint32_t sf = static_cast<uint32_t>(gc - 1) % NSLOT + first_blk;     // physical slot, <= NSLOT + 1
-              constexpr bool wrap = false;
-              const int n1 = n;
               // first-touched outputs need their ring slot handed back (read and zeroed) by the epilogue:
               // block 2, and at t == 0 block 1 too
               if (!pre && !(DBG && p.mode == 1)) {
@@ -431,22 +428,19 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
               fence_after();
               const uint32_t b_f = b_lo0 + first_blk * NB;
               const uint32_t d1 = tmem + sf * NB;
-              const uint32_t id1 = IDESC0 + n1 * IDESC_BLK, id2 = IDESC0 + (n - n1) * IDESC_BLK;
-              const uint32_t b2 = n1 * NB;
+              const uint32_t id1 = IDESC0 + n * IDESC_BLK;
               if (elect_one()) {
                 if (conv0) {
-                  if (!wrap) issue_mmas<0, 3, 1, NB, false>(a_hi, a_st, pr2, d, b_hi, b_f, d1, id1, tmem, id2, b2);
-                  else issue_mmas<0, 3, 1, NB, true>(a_hi, a_st, pr2, d, b_hi, b_f, d1, id1, tmem, id2, b2);
+                  issue_mmas<0, 3, 1, NB>(a_hi, a_st, pr2, d, b_hi, b_f, d1, id1);
                 } else {
-                  if (!wrap) issue_mmas<0, NSPLIT, NKC, NB, false>(a_hi, a_st, pr2, d, b_hi, b_f, d1, id1, tmem, id2, b2);
-                  else issue_mmas<0, NSPLIT, NKC, NB, true>(a_hi, a_st, pr2, d, b_hi, b_f, d1, id1, tmem, id2, b2);
+                  issue_mmas<0, NSPLIT, NKC, NB>(a_hi, a_st, pr2, d, b_hi, b_f, d1, id1);
                 }
               }
               __syncwarp();
               // Look one task ahead while the queued MMAs drain: probe (never block on) the barriers the next
               // task of this segment needs, so that its issue can start without a serialized poll.
               pre = false;
-              if (NMMA - NSPLIT == 4 && !conv0 && !wrap && !(DBG && p.mode == 1)) {
+              if (NMMA - NSPLIT == 4 && !conv0 && !(DBG && p.mode == 1)) {
                 // fast path (every regular task of res15): probes, second-half MMAs and commits in one sequence
                 const bool has_next = t + 1 < n_in;
                 const uint32_t st1 = (st + 1 == T2_NSTAGE) ? 0 : st + 1;
@@ -485,8 +479,7 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
               }
               if (elect_one()) {
                 if (!conv0) {
-                  if (!wrap) issue_mmas<NSPLIT, NMMA, NKC, NB, false>(a_hi, a_st, pr2, d, b_hi, b_f, d1, id1, tmem, id2, b2);
-                  else issue_mmas<NSPLIT, NMMA, NKC, NB, true>(a_hi, a_st, pr2, d, b_hi, b_f, d1, id1, tmem, id2, b2);
+                  issue_mmas<NSPLIT, NMMA, NKC, NB>(a_hi, a_st, pr2, d, b_hi, b_f, d1, id1);
                 }
                 commit(a_task + 8 * (tk % T2_NTB));
               }

@@ -62,6 +62,9 @@ constexpr int t2_groups(int ncg) { return ncg % 3 == 0 ? 3 : 2; }
 constexpr int t2_threads(int ncg) { return (3 + 4 * t2_groups(ncg)) * 32; }
 constexpr int T2_PAD = 16;        // zero rows above every channel plane (>= max dilation)
 constexpr int T2_NTB = 32;        // "task done" barriers (ring): ONE tcgen05.commit per task serves the producer and the epilogue
+#ifndef T2_EARLY_RELEASE
+#define T2_EARLY_RELEASE 1         // epilogue hands a TMEM slot back before (1) or after (0) the column's arithmetic and stores
+#endif
 constexpr int T2_MAXSEG = 8;
 constexpr int T2_MAXL = 24;       // C->C layers (res26)
 constexpr int T2_NDBG = 16;       // debug counters per CTA
@@ -593,10 +596,12 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
                 tmem_zero_cols<HB>(taddr);                     // the slot goes back cleared
                 // hand the slot back as soon as the zeros have landed: the values are in registers, the MMA warp need not
                 // wait for this column's arithmetic and stores
-                tmem_st_wait();
-                fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(a_acc_empty + 8 * sl);
+                if (T2_EARLY_RELEASE) {
+                  tmem_st_wait();
+                  fence_before();
+                  __syncwarp();
+                  if (lane == 0) mbar_arrive(a_acc_empty + 8 * sl);
+                }
               }
               if (DBG && p.mode == 2) {
               } else if (!last) {
@@ -623,6 +628,11 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
                 }
               }
               if (DBG && p.mode == 3) {
+                __syncwarp();
+                if (lane == 0) mbar_arrive(a_acc_empty + 8 * sl);
+              } else if (!T2_EARLY_RELEASE) {                  // the zero stores have had the column's arithmetic to land
+                tmem_st_wait();
+                fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(a_acc_empty + 8 * sl);
               }

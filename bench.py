@@ -24,6 +24,10 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+SPANS = ("frontend", "fe_dft", "fe_post", "res_zero", "res_pack_x0", "res_conv0_pool", "res_conv0", "res_conv", "res_tail", "cnn_pack_x8", "cnn_conv",
+         "cnn_fc", "f32_model")
+FRONTEND_KERNEL = "fe2_mfcc_kernel (persistent, FP64 DMMA dense DFT + mel + log + DCT)"
+FE_DTYPE = "f64"
 METRIC = "clips_per_s_mfcc_cnn"
 UNIT = "clips/s"
 N_UNIQUE = 2048          # distinct synthetic clips generated per rank, tiled to the batch
@@ -147,15 +151,27 @@ def make_weights(name, cfg, calib_mfcc):
 # ----------------------------------------------------------------------------------------------
 # CPU path of the reference (oracle port): per-clip MFCC like collate_fn + torch CPU forward
 # ----------------------------------------------------------------------------------------------
+def cpu_model_name():
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.lower().startswith("model name"):
+                    return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    import platform
+    return platform.processor() or "unknown"
+
+
 class CpuPath:
     """The reference's CPU implementation of the path, restated in oracle/ (kind "port": the
     reference's librosa 0.6 dependency is not installable and /root/reference does not exist on
     the GPU box).  MFCC one clip at a time like SpeechDataset.collate_fn (model.py:253-265) -
-    spread over a thread pool - then the model forward in float32, batch 64, all torch threads."""
+    spread over a PROCESS pool, one worker per core (the per-clip loop holds the GIL) -
+    then the model forward in float32, batch 64, all torch threads."""
 
     def __init__(self, name, cfg, sd):
         import torch
-        from concurrent.futures import ThreadPoolExecutor
         from oracle import honk_oracle as orc
         self.orc, self.torch = orc, torch
         self.name, self.cfg, self.sd = name, cfg, sd
@@ -165,16 +181,13 @@ class CpuPath:
         except Exception:
             pass
         torch.set_num_threads(self.cores)
-        self.pre = orc.AudioPreprocessorOracle()
-        self.pool = ThreadPoolExecutor(max_workers=self.cores)
-
-    def _mfcc(self, clip):
-        return self.pre.compute_mfccs(self.orc.pcm16_to_float(clip)).reshape(-1, 40)
+        self.pool = orc.MfccPool(self.cores)
+        self.cpu_model = cpu_model_name()
 
     def run(self, pcm):
         import numpy as np
         torch = self.torch
-        mf = np.stack(list(self.pool.map(self._mfcc, pcm)))
+        mf = self.pool.compute(pcm)
         outs = []
         with torch.no_grad():
             for i in range(0, len(mf), 64):
@@ -185,6 +198,9 @@ class CpuPath:
         t0 = time.perf_counter()
         out = self.run(pcm)
         return time.perf_counter() - t0, out
+
+    def close(self):
+        self.pool.close()
 
 
 def cpu_sample_size(cpu, pcm, target_s, lo=64, hi=4096):
@@ -220,14 +236,15 @@ def run_reference(args):
         cpu.run(sample)
     dt = (time.perf_counter() - t0) / max(1, args.steps)
     value = n / dt
-    sample_desc = "%d clips per step (bounded sample of the %d-clip/GPU workload), MFCC per clip + %s fp32 forward batch 64" % (
-        n, args.clips_per_gpu, name)
+    sample_desc = "%d clips per step (bounded sample of the %d-clip/GPU workload), float64 MFCC per clip over a %d-process pool + %s fp32 forward batch 64, torch %d threads" % (
+        n, args.clips_per_gpu, cpu.cores, name, cpu.cores)
+    cpu.close()
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64 front end / f32 CNN", "data": "synthetic",
         "config": workload_config(args, args.gpus),
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cpu.cores, "kind": "port", "sample": sample_desc},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cpu.cores, "cpu_model": cpu.cpu_model, "kind": "port", "sample": sample_desc},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -303,9 +320,13 @@ def main():
     model.precision = args.precision
     model.cuda().eval()
 
+    gatherer = parallel.LogitGatherer(B * world, cfg["n_labels"], dev) if world > 1 else None
+
     def step_device():
+        # front end + CNN on this rank's shard; the all_gather of the logits runs on a side stream into a preallocated
+        # [B * world, L] buffer and is consumed one step later, so it never re-synchronises the ranks mid-loop
         logits = model.forward_pcm(pcm, pre)
-        return parallel.gather_logits(logits, B * world) if world > 1 else logits
+        return gatherer.submit(logits) if gatherer is not None else logits
 
     host_out = torch.empty((B, cfg["n_labels"]), dtype=torch.float32).pin_memory()
 
@@ -322,6 +343,8 @@ def main():
     with torch.no_grad():
         for _ in range(max(args.warmup, 0)):
             out = step_device()
+        if gatherer is not None:
+            gatherer.flush()
         barrier()
         # ---------------- timed region (device-resident inputs) ----------------
         N.profile_reset()
@@ -334,6 +357,8 @@ def main():
         e0.record()
         for _ in range(args.steps):
             out = step_device()
+        if gatherer is not None:
+            out = gatherer.flush()                 # the last step's gather completes inside the timed region
         e1.record()
         barrier()
         launches = N.launch_count() - launches0
@@ -341,7 +366,7 @@ def main():
         N.profile_enable(False)
         ms = e0.elapsed_time(e1) / max(1, args.steps)
         spans = {}
-        for sp in ("frontend", "res_pack_x0", "res_conv0_pool", "res_conv0", "res_conv", "res_tail", "cnn_pack_x8", "cnn_conv", "cnn_fc", "f32_model"):
+        for sp in SPANS:
             t, n = N.profile_get(sp)
             if n:
                 spans[sp] = (t, n)
@@ -360,10 +385,21 @@ def main():
         e2e_wall = (time.perf_counter() - t0) / max(1, args.steps) * 1e3
         e2e_ms = max(f0.elapsed_time(f1) / max(1, args.steps), e2e_wall)
 
+    conv_span = next((k for k in ("res_conv", "cnn_conv", "f32_model") if k in spans), None)
+    per_rank = None
+    ms_local = ms
     if world > 1:
-        t = torch.tensor([ms, e2e_ms], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, e2e_ms = float(t[0]), float(t[1])
+        # per-rank breakdown: whose step sets the max, and is it the conv kernel (power-cap spread) or something else?
+        mine = torch.tensor([ms, e2e_ms, spans.get(conv_span, (0.0, 0))[0] / max(1, args.steps), spans.get("frontend", (0.0, 0))[0] / max(1, args.steps),
+                             (clocks.get("sm_mhz") or 0.0), gatherer.seconds_in_submit * 1e3 / max(1, args.steps + args.warmup)],
+                            device=dev, dtype=torch.float64)
+        allr = torch.empty((world, mine.numel()), device=dev, dtype=torch.float64)
+        dist.all_gather_into_tensor(allr, mine)
+        allr = allr.cpu().numpy()
+        per_rank = {"ms_per_step": [round(float(v), 4) for v in allr[:, 0]], "e2e_ms_per_step": [round(float(v), 4) for v in allr[:, 1]],
+                    (conv_span or "conv") + "_ms": [round(float(v), 4) for v in allr[:, 2]], "frontend_ms": [round(float(v), 4) for v in allr[:, 3]],
+                    "sm_mhz_median": [float(v) for v in allr[:, 4]], "gather_submit_host_ms": [round(float(v), 4) for v in allr[:, 5]]}
+        ms, e2e_ms = float(allr[:, 0].max()), float(allr[:, 1].max())
         lt = torch.tensor([launches], device=dev, dtype=torch.int64)
         dist.all_reduce(lt)
         launches = int(lt[0])
@@ -377,9 +413,21 @@ def main():
         peaks = measured_peaks()
         total_clips = B * world
         value = total_clips / (ms * 1e-3)
-        # ---- roofline of the dominant kernel (rank 0's spans) ----
+        step_ms_local = ms_local * args.steps           # rank 0's own timed region: shares are of THIS rank's step
+
+        def tensor_roof(kernel, flops, t_ms, n_launch, traffic_key=None):
+            achieved = flops / (t_ms * 1e-3) / 1e12
+            tr = recorded_traffic(traffic_key, B) if traffic_key else None
+            return {"bound": "tensor", "kernel": kernel, "achieved": achieved, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
+                    "frac": achieved / peaks["tf_sustained"], "frac_burst": achieved / peaks["tf_burst"],
+                    "peak_source": peaks["source"] + " bf16 sustained (frac) / burst (frac_burst), MEASURED_PEAKS.json",
+                    "traffic": tr, "traffic_source": "profiles/traffic.json: ncu --set full capture of this kernel on this workload, scaled by clips per launch; NOT measured in this run" if tr else None,
+                    "avg_launch_ms": t_ms / n_launch, "launches_per_step": n_launch / args.steps, "flops_per_launch": flops / n_launch,
+                    "share_of_step": t_ms / step_ms_local}
+
+        # ---- roofline candidates (rank 0's spans); the reported one is the kernel with the largest share of the step ----
         n_layers = cfg.get("n_layers", 0)
-        roof = None
+        cands = []
         if "res_conv" in spans and name.startswith("res"):
             C = cfg["n_feature_maps"]
             H, W = 101, 40
@@ -387,69 +435,59 @@ def main():
                 H, W = H // cfg["res_pool"][0], W // cfg["res_pool"][1]
             flops_layer_clip = 2 * 9 * C * C * H * W                     # unpadded 2*MAC of one C->C 3x3 layer
             t_ms, n_spans = spans["res_conv"]
-            clips_done = B * args.steps
             persistent = "res_conv0" not in spans          # one launch runs conv0 + all C->C layers (res_tc2.cu)
-            n_launch = n_spans if persistent else n_spans * n_layers
-            avg_launch_ms = t_ms / n_launch
-            achieved = flops_layer_clip * n_layers * clips_done / (t_ms * 1e-3) / 1e12
-            roof = {"bound": "tensor",
-                    "kernel": (("tc2_res_kernel (persistent: %d 3x3 C->C layers on %d-clip time-stacked tiles, tcgen05 ring-accumulate)"
-                                % (n_layers, 113 // (H + 1)) if "res_pool" in cfg else
-                                "tc2_res_kernel (persistent: conv0 + %d dilated 3x3 C->C layers, tcgen05 ring-accumulate)" % n_layers))
-                              if persistent else "tc_conv_kernel (dilated 3x3 C->C implicit GEMM, tcgen05)",
-                    "achieved": achieved, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
-                    "frac": achieved / peaks["tf_sustained"], "peak_source": peaks["source"] + " bf16 sustained",
-                    "traffic": (recorded_traffic("tc2_res_kernel" if name == "res15" else "tc2_res_kernel:" + name, B)
-                                if persistent else None),
-                    "avg_launch_ms": avg_launch_ms, "launches_per_step": n_launch / args.steps,
-                    "flops_per_launch": flops_layer_clip * n_layers * clips_done / n_launch,
-                    "share_of_step": t_ms / (ms * args.steps)}
+            kname = (("tc2_res_kernel (persistent: %d 3x3 C->C layers on %d-clip time-stacked tiles, tcgen05 ring-accumulate)"
+                      % (n_layers, 113 // (H + 1)) if "res_pool" in cfg else
+                      "tc2_res_kernel (persistent: conv0 + %d dilated 3x3 C->C layers, tcgen05 ring-accumulate)" % n_layers)
+                     if persistent else "tc_conv_kernel (dilated 3x3 C->C implicit GEMM, tcgen05)")
+            cands.append(tensor_roof(kname, flops_layer_clip * n_layers * B * args.steps, t_ms, n_spans if persistent else n_spans * n_layers,
+                                     ("tc2_res_kernel" if name == "res15" else "tc2_res_kernel:" + name) if persistent else None))
         elif "cnn_conv" in spans:
             t_ms, n_spans = spans["cnn_conv"]
-            fl = orc.conv_flops_per_clip(name, cfg)                # conv1 + conv2 + Linear, unpadded 2*MAC
-            achieved = fl * B * args.steps / (t_ms * 1e-3) / 1e12
-            roof = {"bound": "tensor", "kernel": "cnn_tc_kernel (persistent: conv1 + maxpool + conv2 per clip, tcgen05 implicit GEMM)",
-                    "achieved": achieved, "peak": peaks["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / peaks["tf_sustained"],
-                    "peak_source": peaks["source"] + " bf16 sustained", "traffic": None, "avg_launch_ms": t_ms / n_spans,
-                    "launches_per_step": n_spans / args.steps, "share_of_step": t_ms / (ms * args.steps)}
+            cands.append(tensor_roof("cnn_tc_kernel (persistent: conv1 + maxpool + conv2 [+ lin/dnn] per clip, tcgen05 implicit GEMM)",
+                                     orc.conv_flops_per_clip(name, cfg) * B * args.steps, t_ms, n_spans))
         elif "f32_model" in spans:
             t_ms, n_spans = spans["f32_model"]
-            fl = orc.conv_flops_per_clip(name, cfg)
-            achieved = fl * B * args.steps / (t_ms * 1e-3) / 1e12
-            roof = {"bound": "tensor", "kernel": "conv_gemm_f32_kernel (CUDA-core FP32 path)", "achieved": achieved,
-                    "peak": peaks["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / peaks["tf_sustained"],
-                    "peak_source": peaks["source"] + " bf16 sustained", "traffic": None,
-                    "share_of_step": t_ms / (ms * args.steps)}
+            cands.append(tensor_roof("conv_gemm_f32_kernel (CUDA-core FP32 path)", orc.conv_flops_per_clip(name, cfg) * B * args.steps, t_ms, n_spans))
         fe = None
         if "frontend" in spans:
             t_ms, n_spans = spans["frontend"]
-            bytes_clip = 32000 + 101 * 40 * 4
+            bytes_clip = 32000 + 101 * 40 * 4                              # int16 PCM in + float32 MFCC out
             gbs = bytes_clip * B * args.steps / (t_ms * 1e-3) / 1e9
-            fe = {"kernel": "fe_mfcc_kernel", "bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                  "frac": gbs / peaks["hbm_gbs"], "clips_per_s": B * args.steps / (t_ms * 1e-3),
-                  "share_of_step": t_ms / (ms * args.steps)}
+            fe = {"bound": "hbm", "kernel": FRONTEND_KERNEL, "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                  "frac": gbs / peaks["hbm_gbs"], "peak_source": peaks["source"] + " copy bandwidth, MEASURED_PEAKS.json",
+                  "traffic": None, "clips_per_s": B * args.steps / (t_ms * 1e-3), "avg_launch_ms": t_ms / n_spans,
+                  "bytes_per_launch": bytes_clip * B * args.steps / n_spans, "share_of_step": t_ms / step_ms_local,
+                  "note": "algorithmic HBM bytes (48 160 B/clip) over the front end's span; the kernels are arithmetic-bound by "
+                          "construction (dense DFT), see DESIGN.md section 4"}
+            cands.append(fe)
+        roof = max(cands, key=lambda r: r["share_of_step"]) if cands else None
+        others = [r for r in cands if r is not roof]
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": args.scaling,
-            "vs_baseline": None, "dtype": "f64 front end; f16 operands / f32 accumulate CNN" if args.precision == 0 else "f64 front end; f32 CNN",
+            "vs_baseline": None, "dtype": FE_DTYPE + " front end; f16 operands / f32 accumulate CNN" if args.precision == 0 else FE_DTYPE + " front end; f32 CNN",
             "data": "synthetic", "config": workload_config(args, world),
             "path": model.native_path, "gpu_launches": launches, "clocks": clocks,
             "e2e": {"value": total_clips / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(pcm_host.numel() * 2), "d2h_bytes_per_step": int(host_logits.numel() * 4)},
-            "roofline": roof, "frontend_roofline": fe,
+            "roofline": roof, "other_kernels": others,
             "spans_ms_per_step": {k: v[0] / args.steps for k, v in spans.items()},
             "algorithmic_flops_per_clip": orc.conv_flops_per_clip(name, cfg),
         }
+        if per_rank is not None:
+            line["per_rank"] = per_rank
         if world == 1 and not args.no_cpu_baseline:
             pcm_np = pcm_host.numpy()[:N_UNIQUE]
             cpu = CpuPath(name, cfg, sd)
             n, _ = cpu_sample_size(cpu, pcm_np, args.cpu_seconds, hi=N_UNIQUE)
             dt, ref = cpu.timed(pcm_np[:n])
+            cpu.close()
             got = host_logits[:n].numpy()
             agree = float((got.argmax(1) == ref.argmax(1)).mean())
-            line["cpu_baseline"] = {"value": n / dt, "unit": UNIT, "cores": cpu.cores, "kind": "port",
-                                    "sample": "%d clips of the same batch: per-clip float64 MFCC (thread pool) + %s fp32 forward, batch 64, torch %d threads"
-                                              % (n, name, cpu.cores),
+            line["cpu_baseline"] = {"value": n / dt, "unit": UNIT, "cores": cpu.cores, "cpu_model": cpu.cpu_model, "kind": "port",
+                                    "sample": "%d clips of the same batch: per-clip float64 MFCC over a %d-process pool + %s fp32 forward, batch 64, torch %d threads"
+                                              % (n, cpu.cores, name, cpu.cores),
                                     "top1_agreement_vs_gpu": agree,
                                     "max_logit_err_rel": float(np.abs(got - ref).max() / np.abs(ref).max())}
         print(json.dumps(line), flush=True)

@@ -80,7 +80,7 @@ def lib():
         L.honk_model_destroy.argtypes = [vp]
         L.honk_model_workspace_bytes.argtypes = [vp, i64]
         L.honk_model_workspace_bytes.restype = i64
-        L.honk_model_forward.argtypes = [vp, vp, i64, vp, vp, i64, vp]
+        L.honk_model_forward.argtypes = [vp, vp, i64, i32, i32, vp, vp, i64, vp]
         L.honk_model_forward_pcm.argtypes = [vp, vp, vp, C.c_int, i64, i64, i64, vp, vp, i64, vp]
         L.honk_model_workspace_bytes_pcm.argtypes = [vp, vp, i64, i64]
         L.honk_model_workspace_bytes_pcm.restype = i64
@@ -101,7 +101,7 @@ def lib():
         L.honk_profile_enable.argtypes = [C.c_int]
         L.honk_profile_get.argtypes = [C.c_char_p, C.POINTER(C.c_double), C.POINTER(i64)]
         L.honk_model_path.restype = C.c_char_p
-        if L.honk_abi_version() != 1:
+        if L.honk_abi_version() != 2:
             raise RuntimeError("honk_b200: ABI version mismatch")
         _lib = L
     return _lib

@@ -155,21 +155,25 @@ __global__ void label_kernel(const float* __restrict__ logits, long long n, int 
   const float* z = logits + clip * L;
   float best = -INFINITY;
   int arg = 0x7fffffff;
+  bool nan = false;
   for (int i = lane; i < L; i += 32) {
     const float v = z[i];
-    if (v > best) { best = v; arg = i; }
+    nan |= (v != v);
+    if (v > best || arg == 0x7fffffff) { best = v; arg = i; }       // a row of -inf still names its first entry
   }
   for (int o = 16; o; o >>= 1) {
     const float ob = __shfl_xor_sync(0xffffffffu, best, o);
     const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
     if (ob > best || (ob == best && oa < arg)) { best = ob; arg = oa; }
   }
+  nan = __any_sync(0xffffffffu, nan);
   float sum = 0.f;
   for (int i = lane; i < L; i += 32) sum += expf(z[i] - best);
   for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
   if (lane == 0) {
-    if (labels) labels[clip] = arg;
-    if (probs) probs[clip] = 1.f / sum;
+    // one NaN logit makes every softmax entry NaN: np.argmax then names entry 0 and max() is NaN (service.py:103-104)
+    if (labels) labels[clip] = nan ? 0 : arg;
+    if (probs) probs[clip] = nan ? __int_as_float(0x7fc00000) : 1.f / sum;
   }
 }
 
@@ -187,16 +191,19 @@ __global__ void __launch_bounds__(256) eval_metrics_kernel(const float* __restri
   if (clip < n) {
     const float* z = logits + clip * L;
     float best = -INFINITY;
-    int arg = 0x7fffffff;
+    int arg = 0x7fffffff, first_nan = 0x7fffffff;
     for (int i = lane; i < L; i += 32) {
       const float v = z[i];
-      if (v > best) { best = v; arg = i; }
+      if (v != v && first_nan == 0x7fffffff) first_nan = i;
+      if (v > best || arg == 0x7fffffff) { best = v; arg = i; }
     }
     for (int o = 16; o; o >>= 1) {
       const float ob = __shfl_xor_sync(0xffffffffu, best, o);
       const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
       if (ob > best || (ob == best && oa < arg)) { best = ob; arg = oa; }      // first maximum, like torch.max
+      first_nan = min(first_nan, __shfl_xor_sync(0xffffffffu, first_nan, o));
     }
+    if (first_nan != 0x7fffffff) { arg = first_nan; best = __int_as_float(0x7fc00000); }   // torch.max propagates NaN: its index wins
     double sum = 0.0;
     for (int i = lane; i < L; i += 32) sum += exp(static_cast<double>(z[i]) - static_cast<double>(best));
     for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
@@ -204,7 +211,9 @@ __global__ void __launch_bounds__(256) eval_metrics_kernel(const float* __restri
     if (lane == 0) {
       if (pred) pred[clip] = arg;
       ok = (static_cast<long long>(arg) == y);
-      if (y >= 0 && y < L) loss = log(sum) + static_cast<double>(best) - static_cast<double>(z[y]);   // logsumexp(z) - z[y]
+      // logsumexp(z) - z[y]; a target outside [0, L) is an error in torch (device assert): it poisons the sum with NaN here
+      // instead of being skipped silently, and honk_b200.train.evaluate raises on it
+      loss = (y >= 0 && y < L) ? log(sum) + static_cast<double>(best) - static_cast<double>(z[y]) : __longlong_as_double(0x7ff8000000000000LL);
     }
   }
   if (lane == 0) { s_loss[wib] = loss; s_ok[wib] = ok; }

@@ -308,10 +308,13 @@ extern "C" int64_t honk_model_workspace_bytes(const honk_model* m, int64_t n_cli
   return m->tc ? res_tc_workspace_bytes(m, n_clips) : f32_workspace(m, n_clips);
 }
 
-extern "C" int honk_model_forward(const honk_model* m, const float* d_mfcc, int64_t n_clips, float* d_logits,
-                                  void* d_workspace, int64_t workspace_bytes, void* stream) {
+extern "C" int honk_model_forward(const honk_model* m, const float* d_mfcc, int64_t n_clips, int32_t height, int32_t width,
+                                  float* d_logits, void* d_workspace, int64_t workspace_bytes, void* stream) {
   HONK_CHECK(m, HONK_ERR_INVALID, "honk_model_forward: null model");
   HONK_CHECK(n_clips >= 0, HONK_ERR_INVALID, "negative n_clips");
+  HONK_CHECK(height == m->H0 && width == m->W0, HONK_ERR_INVALID,
+             "honk_model_forward: input clips are %d x %d but the model expects %d x %d (frames x coefficients)", height, width,
+             m->H0, m->W0);
   if (n_clips == 0) return HONK_OK;
   HONK_CHECK(d_mfcc && d_logits, HONK_ERR_INVALID, "honk_model_forward: null buffer");
   HONK_CHECK(d_workspace && workspace_bytes >= honk_model_workspace_bytes(m, n_clips), HONK_ERR_WORKSPACE,
@@ -357,7 +360,7 @@ extern "C" int honk_model_forward_pcm(const honk_model* m, const honk_frontend* 
   const int64_t mf = align_up(n_clips * static_cast<int64_t>(m->H0) * m->W0 * 4, 256);
   float* mfcc = static_cast<float*>(d_workspace);
   HONK_TRY(honk_frontend_mfcc(fe, d_pcm, dtype, n_clips, n_samples, clip_stride, mfcc, stream));
-  return honk_model_forward(m, mfcc, n_clips, d_logits, static_cast<char*>(d_workspace) + mf,
+  return honk_model_forward(m, mfcc, n_clips, m->H0, m->W0, d_logits, static_cast<char*>(d_workspace) + mf,
                             workspace_bytes - mf, stream);
 }
 
@@ -597,8 +600,25 @@ int forward_pcm_host_impl(const honk_model* m, const honk_frontend* fe, const vo
     HONK_TRY(honk_model_forward_pcm(m, fe, base, dtype, n_clips, n_samples, n_samples, d_logits, inner, inner_bytes, s));
     return finish();
   }
+  // everything that can be refused is checked before the first copy is queued
+  HONK_CHECK(honk_frontend_num_frames(fe, n_samples) == m->H0 && fe_n_dct(fe) == m->W0, HONK_ERR_INVALID,
+             "front end yields %lld x %d but the model expects %d x %d", static_cast<long long>(honk_frontend_num_frames(fe, n_samples)),
+             fe_n_dct(fe), m->H0, m->W0);
   static thread_local HostPipe hp;
   HONK_TRY(hp.init(plan.size()));
+  // From here on copies into the caller's workspace are in flight on the copy stream: a failure below must not return
+  // while they run (the caller may free or reuse the workspace and the pinned buffers), and the thread's events must be
+  // quiescent for its next call.  The guard drains both streams on every early return.
+  struct Drain {
+    cudaStream_t a, b;
+    bool armed = true;
+    ~Drain() {
+      if (armed) {
+        cudaStreamSynchronize(a);
+        cudaStreamSynchronize(b);
+      }
+    }
+  } drain{hp.copy, s};
   // the scratch may have been handed out in the order of `s`: the copy stream must not run ahead of that
   HONK_CUDA(cudaEventRecord(hp.start, s));
   HONK_CUDA(cudaStreamWaitEvent(hp.copy, hp.start, 0));
@@ -626,6 +646,7 @@ int forward_pcm_host_impl(const honk_model* m, const honk_frontend* fe, const vo
   }
   HONK_TRY(finish());
   HONK_CUDA(cudaStreamSynchronize(hp.copy));
+  drain.armed = false;                                       // both streams are already idle
   return HONK_OK;
 }
 }  // namespace

@@ -525,6 +525,7 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
     const int etid = ew * 32 + lane;
     uint32_t g = 0, ev = 0, tk0 = 0;            // tk0 = tasks before the current segment (same order as the MMA warp)
     long long t_wait = 0;
+    [[maybe_unused]] unsigned long long n_sat = 0;   // DBG: accumulator values beyond the f16 range (stored saturated)
     const long long t_start_e = clock64();
     for (int pair = team; pair < n_pairs; pair += n_teams) {
       const int nab = min(K, p.n_clips - K * pair);
@@ -603,6 +604,10 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
                   if (lane == 0) mbar_arrive(a_acc_empty + 8 * sl);
                 }
               }
+              if (DBG && valid) {                                // f16 storage saturates silently (pack_h2): count what would
+#pragma unroll
+                for (int c = 0; c < HB; ++c) n_sat += fabsf(__uint_as_float(v[c])) > 65504.f;
+              }
               if (DBG && p.mode == 2) {
               } else if (!last) {
 #pragma unroll
@@ -658,6 +663,7 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
       }
     }
     if (DBG && etid == 0) { long long* o = p.dbg + blockIdx.x * T2_NDBG; o[7] = t_wait; o[8] = clock64() - t_start_e; }
+    if (DBG && n_sat) atomicAdd(reinterpret_cast<unsigned long long*>(p.dbg + blockIdx.x * T2_NDBG + 13), n_sat);
   } else if (warp == SIG_WARP && !(DBG && p.mode == 1)) {
     // ======================================= flag signaller =================================
     // Publishes "all stores of this CTA for (clip, layer) are visible" to the team: waits until the eight
@@ -961,6 +967,28 @@ __global__ void __launch_bounds__(256) tc2_conv0_pool_mma_kernel(const float* __
   }
 }
 
+// Zeroes exactly the 16-byte units of the activation arena that no layer ever stores and that must read as zero: the
+// T2_PAD rows above every channel plane (time padding), the S - 1 separator rows of a stacked group, and each slot's tail.
+__global__ void __launch_bounds__(256) tc2_zero_pads_kernel(unsigned char* __restrict__ act, long long slot_stride, int n_slots2,
+                                                            int planes_per_slot, int plane_rows, int S, int Hc, int tail_units) {
+  const int per_plane = T2_PAD + S - 1;
+  const long long per_slot = static_cast<long long>(planes_per_slot) * per_plane + tail_units;
+  const long long total = per_slot * n_slots2;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long slot = i / per_slot, r = i - slot * per_slot;
+    long long unit;
+    if (r < static_cast<long long>(planes_per_slot) * per_plane) {
+      const long long pl = r / per_plane;
+      const int k = static_cast<int>(r - pl * per_plane);
+      const int row = k < T2_PAD ? k : T2_PAD + (k - T2_PAD) * (Hc + 1) + Hc;
+      unit = pl * plane_rows + row;
+    } else {
+      unit = static_cast<long long>(planes_per_slot) * plane_rows + (r - static_cast<long long>(planes_per_slot) * per_plane);
+    }
+    *reinterpret_cast<uint4*>(act + slot * slot_stride + unit * 16) = make_uint4(0, 0, 0, 0);
+  }
+}
+
 // logits = W'(pool / HW) + b' with the last BatchNorm folded into W', b'
 __global__ void tc2_tail_kernel(const float* __restrict__ pool, const float* __restrict__ wout,
                                 const float* __restrict__ bout, float* __restrict__ logits, int n_clips, int N, int L,
@@ -983,6 +1011,7 @@ struct ResTc2Plan {
   int plane_rows = 117, col_bytes = 0, stage_stride = 0, wbytes = 0, smem_bytes = 0;
   long long slot_stride = 0, x0_clip_stride = 0;
   int max_teams = 37;
+  int max_resident = 148;         // co-resident CTAs of tc2_res_kernel on this device (occupancy x SMs)
   int G = T2_G;                   // CTAs per team
   int S = 1, Hc = 101;            // pooled models: S clips of Hc rows stacked along time per kernel "clip" (H = S*(Hc+1)-1)
   int pool_h = 0, pool_w = 0, H0 = 101, W0 = 40;
@@ -1264,13 +1293,19 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
     HONK_TRY(set_smem(tc2_conv0_pool_kernel<6, 0, 0>, sm0));
     HONK_TRY(set_smem(tc2_conv0_pool_kernel<4, 0, 0>, sm0));
   }
+  int per_sm = 0;
   if (ncg == 6) {
     HONK_TRY(set_smem(tc2_res_kernel<6, false>, p->smem_bytes));
     HONK_TRY(set_smem(tc2_res_kernel<6, true>, p->smem_bytes));
+    HONK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tc2_res_kernel<6, false>, t2_threads(6), p->smem_bytes));
   } else {
     HONK_TRY(set_smem(tc2_res_kernel<4, false>, p->smem_bytes));
     HONK_TRY(set_smem(tc2_res_kernel<4, true>, p->smem_bytes));
+    HONK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, tc2_res_kernel<4, false>, t2_threads(4), p->smem_bytes));
   }
+  p->max_resident = per_sm * m->n_sms;                 // CTAs that can be co-resident: the persistent grid never exceeds it
+  if (p->max_resident < G) return HONK_OK;
+  p->max_teams = std::min(p->max_teams, p->max_resident / G);
   *out = p.release();
   return HONK_OK;
 }
@@ -1323,8 +1358,19 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
   const int64_t zero_bytes = ar.off;
   unsigned char* x0 = pooled ? ar.take<unsigned char>(n_groups * p->slot_stride) : ar.take<unsigned char>(n_clips * p->x0_clip_stride);
   HONK_CHECK(ar.ok(), HONK_ERR_WORKSPACE, "internal: tcgen05 workspace overrun");
-  // zero rows between planes must be zero; pool sums and layer counters start at zero
-  HONK_CUDA(cudaMemsetAsync(act, 0, static_cast<size_t>(zero_bytes), s));
+  {
+    // What must start as zero: the T2_PAD rows above every channel plane (the convolutions' time padding), the separator rows
+    // of stacked groups (never stored), the tail pad of every slot, the pool sums and the layer counters.  Real rows are
+    // written by a layer before any later layer reads them, so the arena itself (66 MB for res15) is not cleared.
+    ProfSpan span("res_zero", s);
+    const long long planes_per_slot = static_cast<long long>(p->W) * p->ncg;
+    const int tail_units = static_cast<int>((p->slot_stride - planes_per_slot * p->plane_rows * 16) / 16);
+    const long long units = 2ll * n_slots * (planes_per_slot * (T2_PAD + p->S - 1) + tail_units);
+    tc2_zero_pads_kernel<<<static_cast<unsigned>(std::min<long long>((units + 255) / 256, 16 * p->n_sms)), 256, 0, s>>>(
+        act, p->slot_stride, 2 * n_slots, static_cast<int>(planes_per_slot), p->plane_rows, p->S, p->Hc, tail_units);
+    HONK_LAUNCH_CHECK();
+    HONK_CUDA(cudaMemsetAsync(pool, 0, static_cast<size_t>(zero_bytes - (reinterpret_cast<unsigned char*>(pool) - act)), s));
+  }
   if (pooled) {
     ProfSpan span("res_conv0_pool", s);
     const size_t smem = static_cast<size_t>(p->S) * (p->H0 + 2) * (p->W0 + 2) * sizeof(float);
@@ -1413,14 +1459,26 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
   }
   {
     ProfSpan span("res_conv", s);
-    const dim3 grid(teams * md.G);
-    if (p->ncg == 6) {
-      if (dbg) tc2_res_kernel<6, true><<<grid, t2_threads(6), p->smem_bytes, s>>>(a);
-      else tc2_res_kernel<6, false><<<grid, t2_threads(6), p->smem_bytes, s>>>(a);
-    } else {
-      if (dbg) tc2_res_kernel<4, true><<<grid, t2_threads(4), p->smem_bytes, s>>>(a);
-      else tc2_res_kernel<4, false><<<grid, t2_threads(4), p->smem_bytes, s>>>(a);
-    }
+    // The CTAs of a team spin on each other's layer counters, so the whole grid must be resident at once.  A cooperative
+    // launch makes the driver schedule all CTAs together or not at all - also when another stream (a second serving
+    // thread, the NCCL gather) holds SMs - instead of relying on an otherwise idle GPU; a grid that cannot be co-resident
+    // is refused with an error rather than left to spin into the kernel's poll limit.
+    HONK_CHECK(teams * md.G <= p->max_resident, HONK_ERR_UNSUPPORTED, "tc2_res_kernel: %d CTAs cannot be co-resident (limit %d)",
+               teams * md.G, p->max_resident);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(teams * md.G);
+    cfg.blockDim = dim3(t2_threads(p->ncg));
+    cfg.dynamicSmemBytes = p->smem_bytes;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeCooperative;
+    at[0].val.cooperative = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    cudaError_t le;
+    if (p->ncg == 6) le = dbg ? cudaLaunchKernelEx(&cfg, tc2_res_kernel<6, true>, a) : cudaLaunchKernelEx(&cfg, tc2_res_kernel<6, false>, a);
+    else le = dbg ? cudaLaunchKernelEx(&cfg, tc2_res_kernel<4, true>, a) : cudaLaunchKernelEx(&cfg, tc2_res_kernel<4, false>, a);
+    HONK_CHECK(le == cudaSuccess, HONK_ERR_CUDA, "tc2_res_kernel cooperative launch failed: %s", cudaGetErrorString(le));
     HONK_LAUNCH_CHECK();
   }
   if (dbg) {
@@ -1433,8 +1491,8 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
       for (int k = 0; k < T2_NDBG; ++k) m[k] += static_cast<double>(h[b * T2_NDBG + k]) / nb;
     fprintf(stderr, "tc2 dbg (mean cycles/CTA, %d CTAs, %lld clips): producer total %.0f flag-wait %.0f stage-empty-wait %.0f | "
             "mma total %.0f acc-empty-wait %.0f stage-full-wait %.0f weight-wait %.0f | epilogue total %.0f acc-full-wait %.0f | "
-            "lookahead hits %.0f of %.0f tasks\n",
-            nb, static_cast<long long>(n_clips), m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[8], m[7], m[11], m[12]);
+            "lookahead hits %.0f of %.0f tasks | f16 saturations %.0f\n",
+            nb, static_cast<long long>(n_clips), m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[8], m[7], m[11], m[12], m[13] * nb);
   }
   if (l2persist) {
     cudaStreamAttrValue av{};

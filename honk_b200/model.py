@@ -10,6 +10,7 @@ compute the logits.  Inference only (eval mode); there is no CPU fallback.
 from __future__ import annotations
 
 import ctypes as C
+import threading
 from enum import Enum
 
 import numpy as np
@@ -105,6 +106,7 @@ class SerializableModule(nn.Module):
         super().__init__()
         self._native = None           # honk_model* as int
         self._native_key = None       # (device index, parameter versions) the handle was built from
+        self._native_lock = threading.Lock()   # label() is entered from CherryPy's thread pool (server.py:144-146)
         self.precision = 0            # 0: tcgen05 f16 operands where available; 1: all-FP32 CUDA cores
 
     def save(self, filename):
@@ -118,6 +120,7 @@ class SerializableModule(nn.Module):
         raise NotImplementedError
 
     def _release(self):
+        """Destroys the handle.  Callers hold ``_native_lock`` (or are the finaliser)."""
         if getattr(self, "_native", None):
             try:
                 N.lib().honk_model_destroy(self._native)
@@ -126,6 +129,19 @@ class SerializableModule(nn.Module):
         self._native = None
         self._native_key = None
 
+    def __getstate__(self):                      # locks do not pickle / deepcopy; the handle belongs to this object
+        d = self.__dict__.copy()
+        d["_native"], d["_native_key"], d["_native_lock"] = None, None, None
+        return d
+
+    def __setstate__(self, d):
+        super().__setstate__(d)
+        self._native_lock = threading.Lock()
+
+    def warm(self):
+        """Builds the native handle now (weights validated, BN folded, repacked) instead of inside the first request."""
+        return self._ensure_native(self._device())
+
     def __del__(self):
         try:
             self._release()
@@ -133,14 +149,23 @@ class SerializableModule(nn.Module):
             pass
 
     def _state_key(self, device):
-        vers = tuple(t._version for t in self.state_dict(keep_vars=True).values())
-        ptrs = tuple(t.data_ptr() for t in self.state_dict(keep_vars=True).values())
-        return (device.index, self.precision, vers, ptrs)
+        ts = list(self.state_dict(keep_vars=True).values())          # one pass: (version, storage) of every entry
+        return (device.index, self.precision, tuple(t._version for t in ts), tuple(t.data_ptr() for t in ts))
 
     def _ensure_native(self, device):
+        """The native handle for the current weights, built on first use and rebuilt when a parameter changed.
+        Serialised by a lock: two first requests from a thread pool must not both build (and one leak) a handle, nor
+        may one destroy the handle the other is about to use.  A handle that is in use by a concurrent forward is only
+        replaced when the weights really changed, which inference callers do not do mid-request."""
         key = self._state_key(device)
         if self._native is not None and key == self._native_key:
             return self._native
+        with self._native_lock:
+            if self._native is not None and key == self._native_key:
+                return self._native
+            return self._build_native(device, key)
+
+    def _build_native(self, device, key):
         self._release()
         cfg = self._native_config()
         cfg.precision = int(self.precision)
@@ -179,6 +204,11 @@ class SerializableModule(nn.Module):
         dev = self._device()
         if not x.is_cuda:
             raise RuntimeError("honk_b200: model input must be a CUDA tensor")
+        if x.dim() != 3 or tuple(x.shape[1:]) != (self.height, self.width):
+            # the reference raises a size mismatch for the cnn-* models (model.py:195-205); the kernels here are built
+            # for the configured height x width for every family, so any other shape is refused instead of read
+            raise ValueError("honk_b200: model input must be [n_clips, %d, %d] (frames x coefficients), got %s"
+                             % (self.height, self.width, tuple(x.shape)))
         return ops.model_forward(x, self._ensure_native(dev), self.n_labels)
 
     def forward_pcm(self, pcm, audio_processor):

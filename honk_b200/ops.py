@@ -44,6 +44,8 @@ def _(pcm, frontend, n_frames, n_dct):
 @torch.library.custom_op("honk_b200::model_forward", mutates_args=(), device_types="cuda")
 def model_forward(mfcc: torch.Tensor, model: int, n_labels: int) -> torch.Tensor:
     N.require_cuda(mfcc, "model input")
+    if mfcc.dim() != 3:
+        raise ValueError("honk_b200: model input must be [n_clips, frames, coefficients], got %s" % (tuple(mfcc.shape),))
     x = mfcc.to(torch.float32).contiguous()          # inputs may arrive Fortran-ordered (manage_audio.py:41)
     B = x.shape[0]
     out = torch.empty((B, n_labels), dtype=torch.float32, device=x.device)
@@ -51,7 +53,8 @@ def model_forward(mfcc: torch.Tensor, model: int, n_labels: int) -> torch.Tensor
     ws_bytes = int(L.honk_model_workspace_bytes(model, B))
     ws = torch.empty((max(ws_bytes, 1),), dtype=torch.uint8, device=x.device)
     with torch.cuda.device(x.device):
-        N.check(L.honk_model_forward(model, x.data_ptr(), B, out.data_ptr(), ws.data_ptr(), ws_bytes,
+        # the clip shape travels across the C ABI: a wrong shape is HONK_ERR_INVALID (ValueError), never an out-of-bounds read
+        N.check(L.honk_model_forward(model, x.data_ptr(), B, x.shape[1], x.shape[2], out.data_ptr(), ws.data_ptr(), ws_bytes,
                                      N.stream_ptr(x.device)))
     return out
 

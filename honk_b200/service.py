@@ -4,7 +4,8 @@
 MFCC -> model -> softmax -> argmax) but the whole chain, including softmax/argmax, runs on
 the GPU through one fused C-ABI call; ``label_batch`` is the batched extension used for the
 sliding windows of the ``/listen`` endpoint (server.py:99-112).  Thread-safe: the model
-handle is immutable and every call allocates its own workspace on the caller's stream.
+handle is immutable, it is built in ``reload()`` (not inside the first request), every thread keeps its own pinned
+staging buffer and device workspace, and every call runs on the calling thread's current stream.
 """
 from __future__ import annotations
 
@@ -78,6 +79,7 @@ class TorchLabelService(LabelService):
         else:
             self.model.load(self.model_filename)
         self.model.eval()
+        self.model.warm()            # build the native handle here, not inside the first (possibly concurrent) request
 
     def _pcm_rows(self, clips):
         """Request bodies -> int16 rows.  Request-sized batches are assembled in a page-locked buffer kept per thread

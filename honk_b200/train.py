@@ -18,7 +18,13 @@ def eval_metrics(scores, labels):
     """``(accuracy, mean CrossEntropyLoss)`` of one batch as Python floats (train.py:41-46, 66-83)."""
     _, correct, loss_sum = ops.eval_metrics(scores, labels)
     n = max(int(labels.shape[0]), 1)
-    return float(correct.item()) / n, float(loss_sum.item()) / n
+    loss = float(loss_sum.item()) / n
+    if loss != loss:                 # the kernel poisons the sum for a target outside [0, n_labels) (or a NaN score)
+        lab = labels.detach().cpu()
+        if lab.numel() and (int(lab.min()) < 0 or int(lab.max()) >= scores.shape[1]):
+            raise IndexError("Target %d is out of bounds for %d labels" % (int(lab.max() if lab.max() >= scores.shape[1] else lab.min()),
+                                                                          scores.shape[1]))
+    return float(correct.item()) / n, loss
 
 
 def print_eval(name, scores, labels, loss=None, end="\n"):

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define HONK_B200_ABI_VERSION 1
+#define HONK_B200_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define HONK_API __attribute__((visibility("default")))
@@ -141,9 +141,12 @@ HONK_API int honk_model_destroy(honk_model* m);
 HONK_API int64_t honk_model_workspace_bytes(const honk_model* m, int64_t n_clips);
 
 /* d_mfcc float32 [n_clips, height, width] -> d_logits float32 [n_clips, n_labels]
- * (pre-softmax, like forward(); model.py:104-121, 186-205). */
-HONK_API int honk_model_forward(const honk_model* m, const float* d_mfcc, int64_t n_clips, float* d_logits,
-                       void* d_workspace, int64_t workspace_bytes, void* stream);
+ * (pre-softmax, like forward(); model.py:104-121, 186-205).  `height` x `width` is the shape of one
+ * clip of d_mfcc as the caller holds it; it must equal the model's input (101 x 40 by default) or the
+ * call fails with HONK_ERR_INVALID - the reference raises a size mismatch for a wrong shape
+ * (model.py:195-205), it never reads past the tensor. */
+HONK_API int honk_model_forward(const honk_model* m, const float* d_mfcc, int64_t n_clips, int32_t height, int32_t width,
+                       float* d_logits, void* d_workspace, int64_t workspace_bytes, void* stream);
 
 /* Fused path: PCM -> front end -> CNN without materialising MFCCs for the caller.
  * Same semantics as honk_frontend_mfcc followed by honk_model_forward. */

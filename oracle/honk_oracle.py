@@ -177,6 +177,50 @@ class AudioPreprocessorOracle:
         return np.stack([self.compute_mfccs(c).reshape(-1, self.dct_filters.shape[0]) for c in clips])
 
 
+_POOL_PRE = None
+
+
+def _pool_mfcc(clip):
+    """Worker of ``MfccPool``: one int16 clip -> float32 ``[n_frames, n_dct]`` exactly as ``collate_fn`` calls it."""
+    global _POOL_PRE
+    if _POOL_PRE is None:
+        _POOL_PRE = AudioPreprocessorOracle()
+    return _POOL_PRE.compute_mfccs(pcm16_to_float(clip)).reshape(-1, _POOL_PRE.dct_filters.shape[0])
+
+
+class MfccPool:
+    """Per-clip ``compute_mfccs`` (manage_audio.py:30-42, called one clip at a time like model.py:253-265) spread over a
+    PROCESS pool: the per-clip loop holds the GIL (101 small matmuls + np.split), so threads do not scale it
+    (SURVEY.md 8d asks for the all-cores number).  Workers are forked (they only run numpy / scipy, never CUDA, so a
+    live CUDA context in the parent is not touched); ``HONK_ORACLE_MP=spawn`` selects spawned workers instead."""
+
+    def __init__(self, workers=None):
+        import multiprocessing as mp
+        import os
+        if workers is None:
+            try:
+                workers = len(os.sched_getaffinity(0))
+            except AttributeError:
+                workers = os.cpu_count() or 1
+        self.workers = max(1, int(workers))
+        self._pool = mp.get_context(os.environ.get("HONK_ORACLE_MP", "fork")).Pool(self.workers)
+
+    def compute(self, clips):
+        clips = [np.ascontiguousarray(c) for c in clips]
+        chunk = max(1, min(64, len(clips) // (4 * self.workers) or 1))
+        return np.stack(self._pool.map(_pool_mfcc, clips, chunksize=chunk))
+
+    def close(self):
+        self._pool.close()
+        self._pool.join()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+
 def pcm16_to_float(pcm):
     """``np.frombuffer(wav, int16) / 32768.`` (service.py:98) -> float64."""
     return np.asarray(pcm, dtype=np.int16) / 32768.0

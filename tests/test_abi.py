@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol(built_lib):
     lib = ctypes.CDLL(built_lib)
     for s in declared_symbols():
         assert hasattr(lib, s), "missing export " + s
-    assert lib.honk_abi_version() == 1
+    assert lib.honk_abi_version() == 2
 
 
 def test_python_binding_covers_header(built_lib):

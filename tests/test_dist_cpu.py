@@ -3,11 +3,12 @@ import os
 import socket
 
 import numpy as np
+import pytest
 import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from honk_b200.parallel import gather_logits, shard_range
+from honk_b200.parallel import LogitGatherer, gather_logits, shard_range
 
 
 def test_shard_range_partitions():
@@ -26,18 +27,27 @@ def _worker(rank, world, port, n_total, q):
     full = torch.arange(n_total * 12, dtype=torch.float32).reshape(n_total, 12)
     lo, hi = shard_range(n_total, rank, world)
     out = gather_logits(full[lo:hi].clone(), n_total)
-    q.put((rank, bool(torch.equal(out, full))))
+    ok = bool(torch.equal(out, full))
+    # the pipelined gatherer: the result of step i is handed out by step i+1's submit (or flush)
+    g = LogitGatherer(n_total, 12, "cpu")
+    assert g.submit(full[lo:hi] * 1.0) is None
+    for step in (2.0, 3.0):
+        prev = g.submit(full[lo:hi] * step)
+        ok = ok and bool(torch.equal(prev, full * (step - 1.0)))
+    ok = ok and bool(torch.equal(g.flush(), full * 3.0)) and g.flush() is None
+    q.put((rank, ok))
     dist.destroy_process_group()
 
 
-def test_gather_logits_gloo_world2():
+@pytest.mark.parametrize("n_total", [37, 64])          # ragged and equal shards
+def test_gather_logits_gloo_world2(n_total):
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
     port = s.getsockname()[1]
     s.close()
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, 37, q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, n_total, q)) for r in range(2)]
     [p.start() for p in procs]
     res = [q.get(timeout=120) for _ in procs]
     [p.join(60) for p in procs]

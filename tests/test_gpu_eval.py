@@ -61,6 +61,18 @@ def test_eval_metrics_vs_reference_golden(golden_dir, capsys):
     _, c, ls = ops.eval_metrics(big, yb)
     assert c.item() == int((big.argmax(1) == yb).sum())
     assert abs(ls.item() / 100003 - torch.nn.functional.cross_entropy(big.double(), yb).item()) < 1e-9
+    # a target outside [0, n_labels) is an error in torch (device assert): not skipped silently here either
+    bad = yb[:64].clone()
+    bad[5] = 12
+    _, _, ls = ops.eval_metrics(big[:64], bad)
+    assert np.isnan(ls.item())
+    with pytest.raises(IndexError):
+        train.eval_metrics(big[:64], bad)
+    # NaN scores: torch.max names the first NaN entry (print_eval's argmax, train.py:42)
+    zn = big[:4].clone()
+    zn[2, 5] = float("nan")
+    pred, _, _ = ops.eval_metrics(zn, yb[:4])
+    assert int(pred[2]) == 5 and int(pred[0]) == int(zn[0].argmax())
 
 
 def test_evaluate_pcm_and_mfcc_loaders():

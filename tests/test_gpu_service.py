@@ -67,6 +67,165 @@ def test_listen_windows_and_model_type():
         TorchLabelService(tsd, no_cuda=True, labels=LABELS, model_type=hb.ConfigType.RES8_NARROW)
 
 
+def _oracle_label_fn(orc, name, sd, cfg, labels):
+    """``TorchLabelService.label`` restated on the CPU (service.py:89-104): int16 / 32768 -> float64 MFCC -> model in
+    float64 -> softmax -> (label, prob)."""
+    pre = orc.AudioPreprocessorOracle()
+
+    def label(wav_bytes):
+        x = np.frombuffer(wav_bytes, dtype=np.int16) / 32768.0
+        mf = pre.compute_mfccs(x).squeeze(2)[None]
+        z = orc.model_forward(name, sd, cfg, mf, torch.float64).numpy()[0]
+        idx, p = orc.softmax_label(z)
+        return labels[idx], p
+    return label
+
+
+@pytest.mark.parametrize("name", ["res8-narrow", "cnn-trad-pool2"])
+def test_listen_matches_oracle_listen(name):
+    # SURVEY 8(f) N1: the device path (honk_listen: windows read in place, listen_reduce_kernel, early exit) against the
+    # reference's loop restated in oracle.listen (server.py:99-112 over service.py:106-110) with an ORACLE label function
+    # (float64 MFCC + float64 model + softmax), not against the product's own host path.
+    import honk_b200 as hb
+    from honk_b200.service import TorchLabelService
+    from oracle import honk_oracle as orc
+    cfg = dict(hb.find_config(name))
+    cfg["n_labels"] = 12
+    clips = [synth.make_clip(900 + i, seed=5) for i in range(4)]
+    long = np.concatenate(clips)[: 16000 * 3 + 4321].tobytes()          # 3.27 s: the tail is shorter than one hop
+    mf = orc.AudioPreprocessorOracle().compute_mfccs_batch([orc.pcm16_to_float(c) for c in clips])
+    sd = synth.make_state_dict(name, cfg, seed=21, calib_mfcc=mf)
+    tsd = {k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()}
+    keep = hb.find_config(name)["n_labels"]
+    svc = TorchLabelService(tsd, labels=LABELS, model_type=hb.ConfigType(name))
+    label_fn = _oracle_label_fn(orc, name, sd, cfg, LABELS)
+    tol = 2e-3                                                           # f16-operand CNN path: probabilities to ~1e-3
+    per = []
+    # 10.25 ms: a hop (164 samples) that is no multiple of 8; 500.03125 ms: an ODD byte step (16001), which the reference's
+    # byte-wise stride() turns into windows at odd byte offsets (host-window path of the drop-in)
+    for ms in (500, 250, 100, 37, 10.25, 500.03125, 1000, 1):
+        if ms == 1:
+            buf = long[: 2 * 16000 + 2 * 16 * 20]                         # 1 ms hop = 16 samples: keep it to 21 windows
+        else:
+            buf = long
+        ref = orc.listen(label_fn, buf, stride_ms=ms)
+        got = svc.listen(buf, stride_ms=ms)
+        assert set(got) == set(ref), (ms, got, ref)
+        assert all(abs(got[k] - ref[k]) <= tol * max(1.0, ref[k]) for k in ref), (ms, got, ref)
+        if ms == 500:
+            per = [label_fn(w) for w in [long[i:i + 32000] for i in range(0, len(long) - 32000 + 1, 16000)]]
+    # command_tagging: thresholds on either side of the winning probabilities, a keyword that wins and one that does not
+    top = max(per, key=lambda lp: lp[1])
+    for thr in (top[1] - 5e-3, top[1] + 5e-3, 0.0):
+        for kw in (top[0], per[-1][0], "not-a-label"):
+            ref = orc.listen(label_fn, long, min_keyword_prob=thr, keyword=kw, method="command_tagging")
+            got = svc.listen(long, min_keyword_prob=thr, keyword=kw, method="command_tagging")
+            assert got == ref, (thr, kw)
+    # degenerate lengths: shorter than one window, exactly one window, one byte more, an odd byte count
+    for n in (100, 31998, 32000, 32001, 48001):
+        for method in ("all_label", "command_tagging"):
+            ref = orc.listen(label_fn, long[:n], method=method, keyword=top[0], min_keyword_prob=0.0)
+            got = svc.listen(long[:n], method=method, keyword=top[0], min_keyword_prob=0.0)
+            if method == "command_tagging":
+                assert got == ref, (n, method)
+            else:
+                assert set(got) == set(ref) and all(abs(got[k] - ref[k]) <= tol for k in ref), (n, got, ref)
+    hb.find_config(name)["n_labels"] = keep
+
+
+def test_concurrent_threads_and_streams():
+    # server.py:144-146: CherryPy calls label() from a thread pool with one shared model.  Four threads, each on its own
+    # CUDA stream, hammer label_batch (request-sized: persistent kernel in latency mode), forward_pcm (device entry) and
+    # label() of the same service; every result must equal the single-threaded one.
+    import threading
+    import honk_b200 as hb
+    from honk_b200.service import TorchLabelService
+    cfg = dict(hb.find_config("res8"))
+    cfg["n_labels"] = 12
+    base = synth.make_clips(96, start=5100)
+    pre0 = hb.AudioPreprocessor()
+    mf = pre0.compute_mfccs_batch(torch.from_numpy(base[:16]).cuda()).cpu().numpy()
+    sd = synth.make_state_dict("res8", cfg, seed=31, calib_mfcc=mf)
+    tsd = {k: torch.from_numpy(np.asarray(v)) for k, v in sd.items()}
+    svc = TorchLabelService(tsd, labels=LABELS, model_type=hb.ConfigType.RES8)
+    reqs = [c.tobytes() for c in base]
+    want_small = svc.label_batch(reqs[:5])
+    want_big = svc.model.forward_pcm(torch.from_numpy(base).cuda(), svc.audio_processor).cpu().numpy()
+    want_one = [svc.label(r) for r in reqs[:3]]
+    errors = []
+
+    def worker(k):
+        try:
+            st = torch.cuda.Stream()
+            with torch.cuda.stream(st):
+                x = torch.from_numpy(base).cuda()
+                for it in range(12):
+                    got = svc.label_batch(reqs[:5])
+                    assert [g[0] for g in got] == [w[0] for w in want_small]
+                    assert np.allclose([g[1] for g in got], [w[1] for w in want_small], atol=1e-5)
+                    y = svc.model.forward_pcm(x, svc.audio_processor)
+                    st.synchronize()
+                    assert np.allclose(y.cpu().numpy(), want_big, rtol=0, atol=1e-4 * np.abs(want_big).max())
+                    lab = svc.label(reqs[(k + it) % 3])
+                    assert lab[0] == want_one[(k + it) % 3][0] and abs(lab[1] - want_one[(k + it) % 3][1]) < 1e-5
+        except BaseException as e:      # noqa: BLE001 - reported to the main thread
+            errors.append((k, repr(e)))
+
+    threads = [threading.Thread(target=worker, args=(k,)) for k in range(4)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(300)
+    assert not errors, errors
+    # a model whose handle was never built: the first requests arrive concurrently (ADVICE r1: _ensure_native race)
+    m = hb.find_model("res8-narrow")(dict(hb.find_config("res8-narrow")))
+    m.cuda().eval()
+    x = pre0.compute_mfccs_batch(torch.from_numpy(base[:4]).cuda())
+    outs, handles = [None] * 6, [None] * 6
+
+    def first(k):
+        with torch.cuda.stream(torch.cuda.Stream()):
+            outs[k] = m(x).cpu().numpy()
+            handles[k] = m._native
+    ts = [threading.Thread(target=first, args=(k,)) for k in range(6)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join(120)
+    assert len(set(handles)) == 1 and handles[0] is not None
+    assert all(np.array_equal(o, outs[0]) for o in outs)
+
+
+def test_label_nan_and_shape_errors():
+    # one NaN logit makes every softmax entry NaN: np.argmax names entry 0, max() is NaN (service.py:103-104); the drop-in
+    # returns that instead of an out-of-range index.  Wrong input shapes are refused, never read out of bounds.
+    import honk_b200 as hb
+    from honk_b200 import ops
+    z = torch.randn(5, 12, device="cuda")
+    z[1, 7] = float("nan")
+    z[3, :] = float("nan")
+    idx, p = ops.label_from_logits(z)
+    idx, p = idx.cpu().numpy(), p.cpu().numpy()
+    assert idx[1] == 0 and idx[3] == 0 and np.isnan(p[1]) and np.isnan(p[3])
+    sm = torch.softmax(z.double(), 1).cpu().numpy()
+    for r in (0, 2, 4):
+        assert idx[r] == sm[r].argmax() and abs(p[r] - sm[r].max()) < 1e-6
+    zi = torch.full((2, 4), float("-inf"), device="cuda")
+    zi[1, 2] = 0.0
+    idx, p = ops.label_from_logits(zi)
+    assert int(idx[1]) == 2 and 0 <= int(idx[0]) < 4
+    m = hb.find_model("res8-narrow")(dict(hb.find_config("res8-narrow"))).cuda().eval()
+    good = torch.zeros(3, 101, 40, device="cuda")
+    assert m(good).shape == (3, 12)
+    for bad in (torch.zeros(101, 40, device="cuda"), torch.zeros(3, 40, 101, device="cuda"), torch.zeros(3, 99, 40, device="cuda"),
+                torch.zeros(3, 101, 20, device="cuda"), torch.zeros(3, 1, 101, 40, device="cuda")):
+        with pytest.raises(ValueError):
+            m(bad)
+    with pytest.raises(ValueError):
+        ops.model_forward(torch.zeros(3, 50, 40, device="cuda"), m.warm(), 12)       # the C ABI itself checks the clip shape
+    assert m(good).shape == (3, 12)                                                   # the context survived
+
+
 @pytest.mark.parametrize("n", [1, 3, 700])
 def test_label_batch_single_call_matches_two_step(n):
     # honk_model_label_pcm_host (one native call: copy, front end, model, softmax/argmax, copy back) == forward_pcm +

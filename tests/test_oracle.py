@@ -84,6 +84,60 @@ def test_stft_against_direct_dft():
         np.testing.assert_allclose(P[:, t], np.abs(X) ** 2, rtol=2e-6, atol=1e-12)
 
 
+def test_whole_chain_against_independent_implementation():
+    # Front-end parity is UNPINNED by the reference (librosa 0.6.x is neither vendored nor installable, and the reference
+    # holds no golden MFCCs).  This is a whole-chain WITNESS, not a pin: transformers.audio_utils is an independent numpy
+    # implementation written to match librosa (reflect-padded centred STFT, periodic Hann, power spectrum, Slaney mel
+    # filters with area norm); log where > 0 and scipy's orthonormal DCT-II complete manage_audio.py:30-42.  Its spectrum
+    # stays float64 where librosa 0.6 rounds to complex64, hence the 2e-5 bound (measured 3.9e-6).
+    tr = pytest.importorskip("transformers.audio_utils")
+    fftpack = pytest.importorskip("scipy.fftpack")
+    mel = tr.mel_filter_bank(241, 40, 20.0, 4000.0, 16000, norm="slaney", mel_scale="slaney")
+    assert np.abs(mel.T - orc.mel_filterbank()).max() <= 1e-15
+    win = tr.window_function(480, "hann", periodic=True)
+    pre = orc.AudioPreprocessorOracle()
+    special = synth.special_clips()
+    clips = [special[k] for k in ("square_fullscale", "impulse", "short_padded", "one_lsb")] + list(synth.make_clips(64, start=20000, seed=7))
+    worst = 0.0
+    for pcm in clips:
+        y = orc.pcm16_to_float(pcm)
+        S = tr.spectrogram(y, win, frame_length=480, hop_length=160, fft_length=480, power=2.0, center=True,
+                           pad_mode="reflect", mel_filters=mel, mel_floor=1e-300)
+        assert S.shape == (40, 101)
+        S[S <= 1e-300] = 0.0                  # undo the witness's mel floor: exact zeros stay zero (manage_audio.py:39)
+        pos = S > 0
+        S[pos] = np.log(S[pos])
+        # bands that only hold rounding noise of an exactly-zero spectrum differ by construction (float64 vs complex64)
+        live = S > S.max(axis=0, keepdims=True) - 30.0
+        got = pre.compute_mfccs(y)[:, :, 0]
+        if live.all():
+            worst = max(worst, float(np.abs(fftpack.dct(S, type=2, norm="ortho", axis=0).T - got).max()))
+        else:
+            lm_got = (got.astype(np.float64) @ orc.dct_filters(40, 40)).T
+            worst = max(worst, float(np.abs(lm_got - S)[live].max()))
+    assert worst <= 2e-5, worst
+    assert np.all(pre.compute_mfccs(orc.pcm16_to_float(special["zeros"])) == 0)
+
+
+def test_listen_oracle_follows_reference_loop():
+    # oracle.listen restates ListenEndpoint.POST (server.py:99-112) over stride() (service.py:106-110): byte strides,
+    # window = 2 * 16000 bytes, per-label sums of the winning probability, early exit for command_tagging
+    calls = []
+
+    def label_fn(b):
+        calls.append(len(b))
+        k = len(calls)
+        return ("command" if k == 3 else "other", 0.9 if k == 3 else 0.5)
+    wav = bytes(2 * 16000 * 3)
+    out = orc.listen(label_fn, wav, stride_ms=500)
+    assert len(calls) == 5 and set(calls) == {32000} and out == {"other": 2.0, "command": 0.9}
+    calls.clear()
+    assert orc.listen(label_fn, wav, stride_ms=500, method="command_tagging") == dict(contains_command=True) and len(calls) == 3
+    calls.clear()
+    assert orc.listen(label_fn, wav, stride_ms=500, min_keyword_prob=0.95, method="command_tagging") == dict(contains_command=False)
+    assert orc.listen(label_fn, wav[:31999]) == {}
+
+
 def test_sine_known_answer():
     # a bin-centred sinusoid of amplitude A gives |X_b| = A*N/4 under a periodic Hann window
     A, b = 0.5, 30

@@ -26,8 +26,8 @@ if ROOT not in sys.path:
 
 SPANS = ("frontend", "fe_dft", "fe_post", "res_zero", "res_pack_x0", "res_conv0_pool", "res_conv0", "res_conv", "res_tail", "cnn_pack_x8", "cnn_conv",
          "cnn_fc", "f32_model")
-FRONTEND_KERNEL = "fe2_mfcc_kernel (persistent, FP64 DMMA dense DFT + mel + log + DCT)"
-FE_DTYPE = "f64"
+FRONTEND_KERNEL = "fe3_dft_kernel + fe3_post_kernel (DFT as exact int8-limb tcgen05 MMAs with int32 accumulators, cta_group::2; then FP64 mel + log + DCT)"
+FE_DTYPE = "exact int8-limb DFT (s32 accumulate) + f64 mel/log/DCT"
 METRIC = "clips_per_s_mfcc_cnn"
 UNIT = "clips/s"
 N_UNIQUE = 2048          # distinct synthetic clips generated per rank, tiled to the batch

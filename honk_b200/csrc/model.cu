@@ -342,7 +342,8 @@ extern "C" int64_t honk_model_workspace_bytes_pcm(const honk_model* m, const hon
                                                   int64_t n_samples) {
   if (!m || !fe || n_clips <= 0) return 0;
   const int64_t mf = align_up(n_clips * honk_frontend_num_frames(fe, n_samples) * m->W0 * 4, 256);
-  return mf + honk_model_workspace_bytes(m, n_clips);
+  // the front end's scratch is dead once the MFCCs exist: it shares the model's workspace region
+  return mf + std::max(honk_model_workspace_bytes(m, n_clips), honk_frontend_workspace_bytes(fe, n_clips, n_samples, HONK_PCM_I16));
 }
 
 extern "C" int honk_model_forward_pcm(const honk_model* m, const honk_frontend* fe, const void* d_pcm, int dtype,
@@ -359,7 +360,8 @@ extern "C" int honk_model_forward_pcm(const honk_model* m, const honk_frontend* 
              HONK_ERR_WORKSPACE, "workspace too small");
   const int64_t mf = align_up(n_clips * static_cast<int64_t>(m->H0) * m->W0 * 4, 256);
   float* mfcc = static_cast<float*>(d_workspace);
-  HONK_TRY(honk_frontend_mfcc(fe, d_pcm, dtype, n_clips, n_samples, clip_stride, mfcc, stream));
+  HONK_TRY(honk_frontend_mfcc(fe, d_pcm, dtype, n_clips, n_samples, clip_stride, mfcc, static_cast<char*>(d_workspace) + mf,
+                              workspace_bytes - mf, stream));
   return honk_model_forward(m, mfcc, n_clips, m->H0, m->W0, d_logits, static_cast<char*>(d_workspace) + mf,
                             workspace_bytes - mf, stream);
 }

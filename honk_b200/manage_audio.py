@@ -52,6 +52,11 @@ class AudioPreprocessor(object):
     def handle(self):
         return self._handle
 
+    @property
+    def native_path(self):
+        """How int16 PCM is transformed: "tcgen05-i8-limbs" (exact integer DFT on the tensor cores), "fp64-dmma" or "fp64-dfma"."""
+        return N.lib().honk_frontend_path(self._handle).decode()
+
     def mel_basis(self):
         out = np.empty((self.n_mels, 1 + self.n_fft // 2), dtype=np.float64)
         N.check(N.lib().honk_frontend_get_mel(self._handle, out.ctypes.data))

@@ -29,10 +29,13 @@ def _row_stride(pcm):
 def frontend_mfcc(pcm: torch.Tensor, frontend: int, n_frames: int, n_dct: int) -> torch.Tensor:
     pcm = _prep_pcm(pcm)
     out = torch.empty((pcm.shape[0], n_frames, n_dct), dtype=torch.float32, device=pcm.device)
+    L = N.lib()
+    code = N.pcm_dtype_code(pcm)
+    ws_bytes = int(L.honk_frontend_workspace_bytes(frontend, pcm.shape[0], pcm.shape[1], code))
+    ws = torch.empty((max(ws_bytes, 1),), dtype=torch.uint8, device=pcm.device)
     with torch.cuda.device(pcm.device):
-        N.check(N.lib().honk_frontend_mfcc(frontend, pcm.data_ptr(), N.pcm_dtype_code(pcm), pcm.shape[0],
-                                           pcm.shape[1], _row_stride(pcm), out.data_ptr(),
-                                           N.stream_ptr(pcm.device)))
+        N.check(L.honk_frontend_mfcc(frontend, pcm.data_ptr(), code, pcm.shape[0], pcm.shape[1], _row_stride(pcm),
+                                     out.data_ptr(), ws.data_ptr(), ws_bytes, N.stream_ptr(pcm.device)))
     return out
 
 

@@ -88,7 +88,15 @@ HONK_API int honk_frontend_get_mel(const honk_frontend* fe, double* h_out);
  * d_mfcc: float32 [n_clips, n_frames, n_dct_filters] (time-major, the layout
  * collate_fn's reshape(1,-1,40) and service.py's squeeze(2) give the model). */
 HONK_API int honk_frontend_mfcc(const honk_frontend* fe, const void* d_pcm, int dtype, int64_t n_clips,
-                       int64_t n_samples, int64_t clip_stride, float* d_mfcc, void* stream);
+                       int64_t n_samples, int64_t clip_stride, float* d_mfcc, void* d_workspace,
+                       int64_t workspace_bytes, void* stream);
+/* DEVICE scratch honk_frontend_mfcc needs for this call (256-byte aligned; 0 for the paths that need none).
+ * int16 PCM with the default geometry goes through the integer-limb tensor-core DFT, which stages the float32
+ * power spectrum (480 B per frame, at most 4096 clips at a time) between its two kernels. */
+HONK_API int64_t honk_frontend_workspace_bytes(const honk_frontend* fe, int64_t n_clips, int64_t n_samples, int dtype);
+/* Name of the path int16 PCM takes through this front end: "tcgen05-i8-limbs" (exact integer DFT on the tensor
+ * cores), "fp64-dmma" or "fp64-dfma". */
+HONK_API const char* honk_frontend_path(const honk_frontend* fe);
 
 /* ------------------------------------------------------------------------------------------
  * Models.  Replaces SpeechResModel / SpeechModel construction, load_state_dict and forward

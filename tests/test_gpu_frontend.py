@@ -1,7 +1,8 @@
 """GPU parity of the front end (through the C ABI) against the CPU oracle and golden vectors.
 
-Tolerance: the kernel computes in FP64 like the reference, so the bound is set by the final
-float32 cast and the float32 power: |d MFCC| <= 2e-4 absolute (MFCC magnitudes reach ~150)."""
+Tolerance: the DFT is exact (integer limbs on the tensor cores for int16 PCM) or FP64 (float inputs) and
+mel / log / DCT are FP64 like the reference, so the bound is set by the float32 spectrum / power the reference
+itself uses and the final float32 cast: |d MFCC| <= 2e-4 absolute (MFCC magnitudes reach ~150); measured 8e-6."""
 import os
 
 import numpy as np
@@ -82,7 +83,10 @@ def test_dtypes_agree_and_strided_rows(pre):
     pcm = torch.from_numpy(synth.make_clips(5, start=900)).cuda()
     a = pre.compute_mfccs_batch(pcm)
     b = pre.compute_mfccs_batch(pcm.to(torch.float64) / 32768.0)
-    assert torch.equal(a, b)                                    # int16/32768 is exact in FP64
+    # int16 / 32768 is exact in FP64, so both inputs describe the same signal; int16 takes the integer-limb tensor-core DFT
+    # (exact spectrum, one float32 rounding), float64 the FP64 DFT: they differ by float32 rounding noise of the spectrum
+    assert pre.native_path == "tcgen05-i8-limbs"
+    assert (a - b).abs().max().item() <= 2e-5
     wide = torch.zeros((5, 20000), dtype=torch.int16, device="cuda")
     wide[:, :16000] = pcm
     assert torch.equal(pre.compute_mfccs_batch(wide[:, :16000]), a)   # row stride != n_samples
@@ -121,3 +125,34 @@ def test_errors(pre):
     assert pre.compute_mfccs_batch(torch.zeros(0, 16000, device="cuda")).shape == (0, 101, 40)
     with pytest.raises(NotImplementedError):
         pre.compute_pcen(np.zeros(16000))
+
+
+def test_int16_tensor_core_path_shapes_and_edges(pre, orc):
+    # integer-limb tcgen05 DFT (fe_i8.cu): ragged tile pairs (clip counts around multiples of 128 rows), clips shorter than
+    # one hop group, lengths that are no multiple of 16 or 160 (per-sample builder path), overlapping rows, odd alignment
+    from honk_b200 import AudioPreprocessor
+    cases = [(1, 16000), (2, 16000), (3, 15999), (5, 8000), (7, 1600), (2, 320), (1, 241), (130, 16000), (4, 16016), (3, 12345)]
+    for n, ns in cases:
+        clips = synth.make_clips(n, start=9000 + n)[:, :ns].copy() if ns <= 16000 else np.concatenate(
+            [synth.make_clips(n, start=9000 + n), synth.make_clips(n, start=9100 + n)[:, :ns - 16000]], axis=1)
+        ref = np.stack([orc.AudioPreprocessorOracle().compute_mfccs(orc.pcm16_to_float(c))[:, :, 0] for c in clips])
+        got = pre.compute_mfccs_batch(torch.from_numpy(clips).cuda()).cpu().numpy()
+        assert got.shape == ref.shape, (n, ns)
+        assert np.abs(got - ref).max() <= ATOL, (n, ns, np.abs(got - ref).max())
+    base = torch.from_numpy(np.concatenate(list(synth.make_clips(3, start=40)))).cuda()
+    for hop, off in ((4000, 0), (164, 0), (8000, 1), (1, 3)):          # overlapping rows; buffers that are not 16-byte aligned
+        buf = base[off:]
+        n = min(9, 1 + (buf.numel() - 16000) // hop)
+        win = buf.as_strided((n, 16000), (hop, 1))
+        got = pre.compute_mfccs_batch(win).cpu().numpy()
+        ref = np.stack([orc.AudioPreprocessorOracle().compute_mfccs(orc.pcm16_to_float(w))[:, :, 0] for w in win.cpu().numpy()])
+        assert np.abs(got - ref).max() <= ATOL, (hop, off)
+    # the FP64 DMMA kernel (HONK_FE_I8=0) stays available and agrees
+    os.environ["HONK_FE_I8"] = "0"
+    try:
+        p64 = AudioPreprocessor()
+    finally:
+        os.environ.pop("HONK_FE_I8")
+    assert p64.native_path == "fp64-dmma"
+    x = torch.from_numpy(synth.make_clips(33, start=77)).cuda()
+    assert (p64.compute_mfccs_batch(x) - pre.compute_mfccs_batch(x)).abs().max().item() <= 2e-5

@@ -609,7 +609,7 @@ constexpr int F3P_FR = 16;
 
 template <int KPC, int NM, int ND>
 __global__ void __launch_bounds__(128, 4) fe3_post_kernel(const FeDev t, const float* __restrict__ Pg, long long total_frames, int n_items,
-                                                       float* __restrict__ out) {
+                                                       float* __restrict__ out, unsigned char* __restrict__ x0, int n_frames) {
   extern __shared__ __align__(16) unsigned char f3p_smem[];
   constexpr int LMS = NM + 4;
   double* P = reinterpret_cast<double*>(f3p_smem);                   // [16][KPC] power widened to double
@@ -683,10 +683,35 @@ __global__ void __launch_bounds__(128, 4) fe3_post_kernel(const FeDev t, const f
       }
       const long long g = g0 + 8 * ft + row;
       if (g < total_frames) {
-        float* op = out + g * ND + 2 * kq;
+        if (x0 == nullptr) {
+          float* op = out + g * ND + 2 * kq;
 #pragma unroll
-        for (int c = 0; c < CPW; ++c)
-          if (c < nct) *reinterpret_cast<float2*>(op + 8 * (ct0 + c)) = make_float2(static_cast<float>(o[c][0]), static_cast<float>(o[c][1]));
+          for (int c = 0; c < CPW; ++c)
+            if (c < nct) *reinterpret_cast<float2*>(op + 8 * (ct0 + c)) = make_float2(static_cast<float>(o[c][0]), static_cast<float>(o[c][1]));
+        } else {
+          // conv0's A operand of the persistent res kernel (res_tc2.cu): x0[clip][w][H + 2][8 halves] = (hi, lo, hi, 0...) of the
+          // float32 MFCC, a zero row above and below (conv0's time padding).  Eight consecutive frames of a warp's rows are
+          // 128 contiguous bytes per coefficient.
+          const long long clip = g / n_frames;
+          const int tt = static_cast<int>(g - clip * n_frames);
+          uint4* xb = reinterpret_cast<uint4*>(x0) + clip * ND * (n_frames + 2) + 1 + tt;
+#pragma unroll
+          for (int c = 0; c < CPW; ++c)
+            if (c < nct) {
+#pragma unroll
+              for (int e = 0; e < 2; ++e) {
+                const int w = 8 * (ct0 + c) + 2 * kq + e;
+                const float xv = fminf(fmaxf(static_cast<float>(o[c][e]), -60000.f), 60000.f);      // stays finite in f16
+                const __half hi = __float2half_rn(xv);
+                const __half lo = __float2half_rn(xv - __half2float(hi));
+                const uint32_t uh = __half_as_ushort(hi), ul = __half_as_ushort(lo);
+                uint4* dst = xb + static_cast<long long>(w) * (n_frames + 2);
+                *dst = make_uint4(uh | (ul << 16), uh, 0u, 0u);
+                if (tt == 0) dst[-1] = make_uint4(0, 0, 0, 0);
+                if (tt == n_frames - 1) dst[1] = make_uint4(0, 0, 0, 0);
+              }
+            }
+        }
       }
     }
     __syncthreads();
@@ -788,7 +813,7 @@ int64_t fe3_workspace_bytes(int64_t n_clips, int64_t n_frames) {
 
 // int16 PCM -> float32 MFCC through the power-spectrum scratch `ws` (fe3_workspace_bytes)
 int fe3_mfcc(const Fe3Plan* p, const FeDev& t, const short* d_pcm, int64_t n_clips, int64_t n_samples, int64_t clip_stride, float* d_mfcc,
-             void* ws, cudaStream_t s) {
+             unsigned char* d_x0, void* ws, cudaStream_t s) {
   const int n_frames = static_cast<int>(1 + n_samples / F3_HOP);
   for (int64_t c0 = 0; c0 < n_clips; c0 += 4096) {
     const int64_t nc = std::min<int64_t>(4096, n_clips - c0);
@@ -814,7 +839,8 @@ int fe3_mfcc(const Fe3Plan* p, const FeDev& t, const short* d_pcm, int64_t n_cli
       const long long total_frames = nc * n_frames;
       const int n_items = static_cast<int>((total_frames + F3P_FR - 1) / F3P_FR);
       fe3_post_kernel<F3_PSTRIDE, 40, 40><<<std::min(n_items, p->n_sms * 8), 128, p->post_smem, s>>>(
-          t, static_cast<const float*>(ws), total_frames, n_items, d_mfcc + c0 * n_frames * 40);
+          t, static_cast<const float*>(ws), total_frames, n_items, d_mfcc ? d_mfcc + c0 * n_frames * 40 : nullptr,
+          d_x0 ? d_x0 + c0 * 40 * (n_frames + 2) * 16 : nullptr, n_frames);
       HONK_LAUNCH_CHECK();
     }
   }

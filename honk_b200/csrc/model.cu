@@ -342,8 +342,10 @@ extern "C" int64_t honk_model_workspace_bytes_pcm(const honk_model* m, const hon
                                                   int64_t n_samples) {
   if (!m || !fe || n_clips <= 0) return 0;
   const int64_t mf = align_up(n_clips * honk_frontend_num_frames(fe, n_samples) * m->W0 * 4, 256);
-  // the front end's scratch is dead once the MFCCs exist: it shares the model's workspace region
-  return mf + std::max(honk_model_workspace_bytes(m, n_clips), honk_frontend_workspace_bytes(fe, n_clips, n_samples, HONK_PCM_I16));
+  const int64_t few = honk_frontend_workspace_bytes(fe, n_clips, n_samples, HONK_PCM_I16), mw = honk_model_workspace_bytes(m, n_clips);
+  // two layouts: [MFCC][model scratch, shared with the front end's scratch (dead once the MFCCs exist)], or, when the front
+  // end writes conv0's operand image straight into the model's scratch, [front-end scratch][model scratch]
+  return std::max(mf + std::max(mw, few), few + mw);
 }
 
 extern "C" int honk_model_forward_pcm(const honk_model* m, const honk_frontend* fe, const void* d_pcm, int dtype,
@@ -358,6 +360,17 @@ extern "C" int honk_model_forward_pcm(const honk_model* m, const honk_frontend* 
              fe_n_dct(fe), m->W0);
   HONK_CHECK(d_workspace && workspace_bytes >= honk_model_workspace_bytes_pcm(m, fe, n_clips, n_samples),
              HONK_ERR_WORKSPACE, "workspace too small");
+  if (m->tc2 && fe_can_x0(fe, dtype, n_clips, n_samples) && !getenv("HONK_NO_X0_FUSION")) {
+    // un-pooled res* on the persistent kernel, int16 PCM: the front end's last stage writes conv0's f16 hi/lo operand image
+    // itself - no MFCC tensor, no pack kernel (manage_audio.py:30-42 -> model.py:107-111 without the HBM round trip)
+    const int64_t few = honk_frontend_workspace_bytes(fe, n_clips, n_samples, dtype);
+    char* mws = static_cast<char*>(d_workspace) + few;
+    int H = 0, W = 0;
+    if (unsigned char* x0 = res_tc2_x0_buffer(m->tc2, n_clips, mws, workspace_bytes - few, &H, &W)) {
+      HONK_TRY(fe_forward_x0(fe, d_pcm, dtype, n_clips, n_samples, clip_stride, x0, H, W, d_workspace, few, stream));
+      return res_tc2_forward(m->tc2, nullptr, n_clips, d_logits, mws, workspace_bytes - few, static_cast<cudaStream_t>(stream));
+    }
+  }
   const int64_t mf = align_up(n_clips * static_cast<int64_t>(m->H0) * m->W0 * 4, 256);
   float* mfcc = static_cast<float*>(d_workspace);
   HONK_TRY(honk_frontend_mfcc(fe, d_pcm, dtype, n_clips, n_samples, clip_stride, mfcc, static_cast<char*>(d_workspace) + mf,

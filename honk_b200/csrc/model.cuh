@@ -57,6 +57,12 @@ int64_t res_tc_workspace_bytes(const honk_model* m, int64_t n_clips);
 int res_tc2_plan_create(honk_model* m, ResTc2Plan** out);
 int64_t res_tc2_workspace_bytes(const ResTc2Plan* p, int64_t n_clips);
 int res_tc2_wave_clips(const ResTc2Plan* p);   // clips all teams process at once: batch cuts on this boundary lose nothing
+// Un-pooled models: where conv0's operand image x0[clip][W][H + 2][8 halves] of this batch lives inside `ws` (so that the
+// front end can write it directly); nullptr for pooled models.  d_mfcc == nullptr in res_tc2_forward: x0 is already there.
+unsigned char* res_tc2_x0_buffer(const ResTc2Plan* p, int64_t n_clips, void* ws, int64_t ws_bytes, int* H, int* W);
+int fe_forward_x0(const honk_frontend* fe, const void* d_pcm, int dtype, int64_t n_clips, int64_t n_samples, int64_t clip_stride,
+                  unsigned char* d_x0, int H, int W, void* d_workspace, int64_t workspace_bytes, void* stream);   // frontend.cu
+bool fe_can_x0(const honk_frontend* fe, int dtype, int64_t n_clips, int64_t n_samples);
 int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, float* d_logits, void* ws, int64_t ws_bytes,
                     cudaStream_t s);
 // cnn_tc.cu: tcgen05 conv1 + conv2 for cnn-trad-pool2; *out == nullptr when the geometry differs.

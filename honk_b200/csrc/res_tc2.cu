@@ -1345,6 +1345,22 @@ int64_t res_tc2_workspace_bytes(const ResTc2Plan* p, int64_t n_clips) {
   return align_up(a.off, 256);
 }
 
+unsigned char* res_tc2_x0_buffer(const ResTc2Plan* p, int64_t n_clips, void* ws, int64_t ws_bytes, int* H, int* W) {
+  if (p->pool_h > 0 || !ws) return nullptr;
+  const int64_t n_groups = tc2_groups(p, n_clips);
+  const T2Mode md = tc2_mode(p, n_groups);
+  const int n_slots = md.K * tc2_teams(md, n_groups);
+  Arena ar(ws, ws_bytes);                               // the same sequence of takes as res_tc2_forward
+  ar.take<unsigned char>(2ll * n_slots * p->slot_stride);
+  ar.take<float>(n_groups * p->S * p->NB);
+  ar.take<unsigned int>(n_groups);
+  unsigned char* x0 = ar.take<unsigned char>(n_clips * p->x0_clip_stride);
+  if (!ar.ok()) return nullptr;
+  *H = p->H;
+  *W = p->W;
+  return x0;
+}
+
 int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, float* d_logits, void* ws, int64_t ws_bytes,
                     cudaStream_t s) {
   const bool pooled = p->pool_h > 0;
@@ -1371,6 +1387,7 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
     HONK_LAUNCH_CHECK();
     HONK_CUDA(cudaMemsetAsync(pool, 0, static_cast<size_t>(zero_bytes - (reinterpret_cast<unsigned char*>(pool) - act)), s));
   }
+  HONK_CHECK(d_mfcc || !pooled, HONK_ERR_INVALID, "internal: pooled models take MFCCs");
   if (pooled) {
     ProfSpan span("res_conv0_pool", s);
     const size_t smem = static_cast<size_t>(p->S) * (p->H0 + 2) * (p->W0 + 2) * sizeof(float);
@@ -1393,7 +1410,7 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
     }
 #undef T2_C0
     HONK_LAUNCH_CHECK();
-  } else {
+  } else if (d_mfcc) {                                  // nullptr: the front end wrote x0 itself (fe_forward_x0)
     ProfSpan span("res_pack_x0", s);
     tc2_pack_x0_kernel<<<static_cast<unsigned>(n_clips), 256, p->H * (p->W + 1) * sizeof(float), s>>>(d_mfcc, x0, p->H, p->W);
     HONK_LAUNCH_CHECK();

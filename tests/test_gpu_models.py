@@ -59,7 +59,7 @@ def test_golden_logits(golden_dir, name, precision):
         assert (y.argmax(1) == ref.argmax(1)).all()
 
 
-@pytest.mark.parametrize("name", ["res8-narrow", "res8", "cnn-trad-pool2"])
+@pytest.mark.parametrize("name", ["res8-narrow", "res8", "cnn-trad-pool2", "res15-narrow", "res15"])
 def test_against_oracle_batch64(name):
     # BASELINE config 1 shape: batch 64 synthetic clips through front end + CNN
     import honk_b200 as hb
@@ -77,7 +77,9 @@ def test_against_oracle_batch64(name):
         err = np.abs(y - ref).max() / np.abs(ref).max()
         assert err <= TOL[m.native_path] * 1.5, (name, m.native_path, err)
         y2 = m(pre.compute_mfccs_batch(torch.from_numpy(clips).cuda())).cpu().numpy()
-        assert np.allclose(y, y2, rtol=0, atol=1e-5 * np.abs(ref).max())   # fused PCM entry == two-step entry (atomics reorder sums)
+        # fused PCM entry == two-step entry (atomics reorder sums).  For the un-pooled res* models on the tcgen05 path the
+        # fused entry never materialises MFCCs: the front end writes conv0's operand image itself (fe_forward_x0)
+        assert np.allclose(y, y2, rtol=0, atol=1e-5 * np.abs(ref).max())
 
 
 @pytest.mark.parametrize("name,n", [("res15-narrow", 1500), ("res8-narrow", 70)])

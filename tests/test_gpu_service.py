@@ -126,7 +126,7 @@ def test_listen_matches_oracle_listen(name, precision):
     keep = hb.find_config(name)["n_labels"]
     svc = TorchLabelService(tsd, labels=LABELS, model_type=hb.ConfigType(name))
     svc.model.precision = precision
-    tol, amb = (2e-3, 6e-3) if precision == 0 else (2e-5, 2e-4)
+    tol, amb = (5e-3, 1.5e-2) if precision == 0 else (2e-5, 2e-4)      # f16-operand CNN: probabilities to ~3e-3
     # 10.25 ms: a hop (164 samples) that is no multiple of 8; 500.03125 ms: an ODD byte step (16001), which the reference's
     # byte-wise stride() turns into windows at odd byte offsets (host-window path of the drop-in)
     for ms in (500, 250, 100, 37, 10.25, 500.03125, 1000, 1):

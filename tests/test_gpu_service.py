@@ -225,7 +225,8 @@ def test_concurrent_threads_and_streams():
     for t in ts:
         t.join(120)
     assert len(set(handles)) == 1 and handles[0] is not None
-    assert all(np.array_equal(o, outs[0]) for o in outs)
+    # (the global-mean sums of the tcgen05 path meet by atomics: ~1e-7 relative run to run, not bit-equal)
+    assert all(np.allclose(o, outs[0], rtol=0, atol=1e-5 * np.abs(outs[0]).max()) for o in outs)
 
 
 def test_label_nan_and_shape_errors():

@@ -20,7 +20,7 @@ FAMILY_RES, FAMILY_CNN = 0, 1
 EXPORTS = [
     "honk_abi_version", "honk_last_error", "honk_device_check", "honk_frontend_create",
     "honk_frontend_destroy", "honk_frontend_num_frames", "honk_frontend_get_dct", "honk_frontend_get_mel",
-    "honk_frontend_mfcc", "honk_frontend_workspace_bytes", "honk_frontend_path", "honk_model_create", "honk_model_destroy", "honk_model_workspace_bytes",
+    "honk_frontend_mfcc", "honk_frontend_workspace_bytes", "honk_frontend_path", "honk_frontend_mfcc_noalloc", "honk_model_create", "honk_model_destroy", "honk_model_workspace_bytes",
     "honk_model_forward", "honk_model_forward_pcm", "honk_model_workspace_bytes_pcm",
     "honk_model_forward_pcm_host", "honk_model_label_pcm_host", "honk_model_workspace_bytes_pcm_host",
     "honk_label_from_logits", "honk_eval_metrics", "honk_load_audio", "honk_listen", "honk_listen_num_windows", "honk_listen_workspace_bytes", "honk_launch_count", "honk_model_path", "honk_profile_enable",
@@ -78,6 +78,7 @@ def lib():
         L.honk_frontend_mfcc.argtypes = [vp, vp, C.c_int, i64, i64, i64, vp, vp, i64, vp]
         L.honk_frontend_workspace_bytes.argtypes = [vp, i64, i64, C.c_int]
         L.honk_frontend_workspace_bytes.restype = i64
+        L.honk_frontend_mfcc_noalloc.argtypes = [vp, vp, i64, i64, i64, vp, vp]
         L.honk_frontend_path.argtypes = [vp]
         L.honk_frontend_path.restype = C.c_char_p
         L.honk_model_create.argtypes = [C.POINTER(ModelConfig), C.POINTER(Tensor), i32, C.c_int, C.POINTER(vp)]

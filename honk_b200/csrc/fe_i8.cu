@@ -723,7 +723,14 @@ __global__ void __launch_bounds__(128, 4) fe3_post_kernel(const FeDev t, const f
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
+// Scratch of the allocation-free entry point (honk_frontend_mfcc_noalloc): the float32 power spectrum of at most
+// HONK_NOALLOC_MAX_FRAMES frames (64 one-second clips), 480 B per frame = 3 102 720 B.  Every GPU that loads the library
+// holds this array until the process exits.  In HOST code the name below is only a stand-in for the symbol, not a device
+// address: fe3_plan_create asks cudaGetSymbolAddress for the real address on the front end's device and keeps it in the plan.
+static __device__ __align__(256) float f3_static_P[HONK_NOALLOC_MAX_FRAMES * F3_PSTRIDE];
+
 struct Fe3Plan {
+  float* d_static_P = nullptr;    // device address of f3_static_P on this plan's device (null: the lookup failed)
   unsigned char* d_bslab = nullptr;
   int n_sms = 148;
   int max_pairs = 74;          // co-resident CTA pairs of fe3_dft_kernel
@@ -802,6 +809,13 @@ int fe3_plan_create(const double* win, const FeDev& t, int device, Fe3Plan** out
   }
   p->post_smem = (F3P_FR * F3_PSTRIDE + F3P_FR * 44 + t.mel_maxw * 40) * 8 + 128 * 16;
   HONK_CUDA(cudaFuncSetAttribute(fe3_post_kernel<F3_PSTRIDE, 40, 40>, cudaFuncAttributeMaxDynamicSharedMemorySize, p->post_smem));
+  {
+    // set-up, with this plan's device current (honk_frontend_create selected it): the device address of the static scratch.
+    // A failure here must not take the ordinary paths down: only the no-alloc entry point reports it.
+    void* sp = nullptr;
+    if (cudaGetSymbolAddress(&sp, f3_static_P) == cudaSuccess) p->d_static_P = static_cast<float*>(sp);
+    else (void)cudaGetLastError();
+  }
   *out = p.release();
   return HONK_OK;
 }
@@ -844,6 +858,38 @@ int fe3_mfcc(const Fe3Plan* p, const FeDev& t, const short* d_pcm, int64_t n_cli
       HONK_LAUNCH_CHECK();
     }
   }
+  return HONK_OK;
+}
+
+// The same two kernels as fe3_mfcc with the power spectrum staged in the file-scope static array: no cudaMalloc / cudaFree,
+// no event or stream creation, no caller workspace.  Every call on a device shares that array, so calls that overlap on
+// the GPU (two streams, two threads) race; nothing in it has to start at zero (every float the post kernel uses is written
+// by the DFT kernel of the same call; the 120th pad float of a row is read but multiplied by no mel weight).
+int fe3_mfcc_noalloc(const Fe3Plan* p, const FeDev& t, const short* d_pcm, int64_t n_clips, int64_t n_samples, int64_t clip_stride,
+                     float* d_mfcc, cudaStream_t s) {
+  HONK_CHECK(p->d_static_P, HONK_ERR_CUDA, "honk_frontend_mfcc_noalloc: cudaGetSymbolAddress of the static scratch failed at set-up");
+  const int n_frames = static_cast<int>(1 + n_samples / F3_HOP);
+  const long long total_frames = n_clips * n_frames;
+  HONK_CHECK(total_frames <= HONK_NOALLOC_MAX_FRAMES, HONK_ERR_INVALID,
+             "honk_frontend_mfcc_noalloc: %lld clips x %d frames = %lld frames exceed the static scratch (HONK_NOALLOC_MAX_FRAMES = %d)",
+             static_cast<long long>(n_clips), n_frames, total_frames, HONK_NOALLOC_MAX_FRAMES);
+  Fe3Args a;
+  a.pcm = d_pcm;
+  a.clip_stride = clip_stride;
+  a.n_samples = static_cast<int>(n_samples);
+  a.n_frames = n_frames;
+  a.rpc = n_frames + 2;
+  a.total_rows = n_clips * a.rpc;
+  const long long n_tiles = (a.total_rows + 127) / 128;
+  a.n_tilepairs = static_cast<int>((n_tiles + 1) / 2);
+  a.bslab = p->d_bslab;
+  a.P = p->d_static_P;
+  fe3_dft_kernel<<<2 * std::min(a.n_tilepairs, p->max_pairs), F3_THREADS, F3_SMEM, s>>>(a);
+  HONK_LAUNCH_CHECK();
+  const int n_items = static_cast<int>((total_frames + F3P_FR - 1) / F3P_FR);
+  fe3_post_kernel<F3_PSTRIDE, 40, 40><<<std::min(n_items, p->n_sms * 8), 128, p->post_smem, s>>>(t, p->d_static_P, total_frames, n_items,
+                                                                                               d_mfcc, nullptr, n_frames);
+  HONK_LAUNCH_CHECK();
   return HONK_OK;
 }
 

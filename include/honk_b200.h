@@ -94,6 +94,17 @@ HONK_API int honk_frontend_mfcc(const honk_frontend* fe, const void* d_pcm, int 
  * int16 PCM with the default geometry goes through the integer-limb tensor-core DFT, which stages the float32
  * power spectrum (480 B per frame, at most 4096 clips at a time) between its two kernels. */
 HONK_API int64_t honk_frontend_workspace_bytes(const honk_frontend* fe, int64_t n_clips, int64_t n_samples, int dtype);
+/* Allocation-free variant of honk_frontend_mfcc for int16 PCM.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  It takes no workspace and calls no cudaMalloc / cudaFree or other allocating routine: the float32
+ * power spectrum between its two kernels lives in a file-scope static device array of HONK_NOALLOC_MAX_FRAMES x 480 B
+ * (3.1 MB, held by every GPU that loads the library until exit).  n_clips x frames per clip must not exceed
+ * HONK_NOALLOC_MAX_FRAMES (64 one-second clips) or the call fails with HONK_ERR_INVALID; the front end must have the default
+ * geometry (HONK_ERR_UNSUPPORTED otherwise).  Inputs and outputs as for honk_frontend_mfcc with dtype HONK_PCM_I16.  All
+ * calls on a device share the array: calls that overlap on the GPU (two streams, two threads) race - serialise them. */
+#define HONK_NOALLOC_MAX_FRAMES 6464
+HONK_API int honk_frontend_mfcc_noalloc(const honk_frontend* fe, const int16_t* d_pcm, int64_t n_clips, int64_t n_samples,
+                               int64_t clip_stride, float* d_mfcc, void* stream);
 /* Name of the path int16 PCM takes through this front end: "tcgen05-i8-limbs" (exact integer DFT on the tensor
  * cores), "fp64-dmma" or "fp64-dfma". */
 HONK_API const char* honk_frontend_path(const honk_frontend* fe);

@@ -345,6 +345,7 @@ def main():
             out = step_device()
         if gatherer is not None:
             gatherer.flush()
+            gatherer.seconds_in_submit = 0.0       # the first call created the NCCL communicator: not part of a step
         barrier()
         # ---------------- timed region (device-resident inputs) ----------------
         N.profile_reset()
@@ -391,7 +392,7 @@ def main():
     if world > 1:
         # per-rank breakdown: whose step sets the max, and is it the conv kernel (power-cap spread) or something else?
         mine = torch.tensor([ms, e2e_ms, spans.get(conv_span, (0.0, 0))[0] / max(1, args.steps), spans.get("frontend", (0.0, 0))[0] / max(1, args.steps),
-                             (clocks.get("sm_mhz") or 0.0), gatherer.seconds_in_submit * 1e3 / max(1, args.steps + args.warmup)],
+                             (clocks.get("sm_mhz") or 0.0), gatherer.seconds_in_submit * 1e3 / max(1, args.steps)],
                             device=dev, dtype=torch.float64)
         allr = torch.empty((world, mine.numel()), device=dev, dtype=torch.float64)
         dist.all_gather_into_tensor(allr, mine)

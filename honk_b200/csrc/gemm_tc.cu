@@ -1,0 +1,494 @@
+// Generic tcgen05 path for the Google cnn-* family (SpeechModel.forward, utils/model.py:186-205) other than the
+// cnn-trad-pool2 geometry (which has its own fused kernel, cnn_tc.cu): every layer - conv1, conv2 (strided, pooled,
+// full-height kernels), lin, dnn1, dnn2, output (model.py:385-407 configs) - is ONE GEMM on the tensor cores,
+//     C[M][N] = act(A[M][K] B[N][K]^T + bias),     f16 operands, FP32 accumulators in TMEM,
+// fed by a pack kernel that writes the layer's A operand (im2col rows, with the previous layer's MaxPool folded in) in the
+// tiled layout the MMA reads:
+//     A: [M tile of 128 rows][K plane of 8 elements][128 rows][8 halves]   (one 16-byte unit per row and plane; a stage of
+//        KC planes of one tile is one contiguous bulk copy; UMMA K-major no-swizzle: SBO = 128 B, LBO = one plane)
+//     B: [N tile][K plane][NT rows][8 halves], packed once at model load.
+// Row m of A = (clip, output position), k = (kh * KW + kw) * Cs + c over the NHWC f16 activation of the previous layer
+// (conv1: k = kh * KW + kw over the float32 MFCC image).  Linear layers are the 1 x 1 case over a 1 x 1 map with C = K; their
+// weights are permuted at load from the reference's (C, H, W) flatten order (model.py:195) to the (H, W, C) order stored here.
+//
+// gemm_tc_kernel: persistent, one CTA per SM over (M tile, N tile) pairs.  warp 0 = bulk-copy producer (4 stages of KC = 8
+// planes: 16 KB of A + NT * 128 B of B), warp 1 = MMA issuer (M = 128, N = NT <= 256, K = 16 per tcgen05.mma, two TMEM
+// accumulator buffers), warps 2-5 = epilogue (TMEM -> + bias -> ReLU -> f16 / f32 rows in global memory).
+#include "umma.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <memory>
+#include <vector>
+
+#include "model.cuh"
+
+namespace honk {
+
+using namespace umma;
+
+namespace {
+
+constexpr int GT_THREADS = 192;
+constexpr int GT_KC = 8;                 // K planes (of 8 elements) per stage
+constexpr int GT_NSTAGE = 4;
+constexpr int GT_MAXNT = 256;
+
+struct GemmTcParams {
+  const unsigned char* A;      // tiled, see above
+  const unsigned char* B;
+  const float* bias;           // [n_ntiles * NT] (zero in padded columns)
+  void* C;                     // row-major [M][ldc], f16 or f32
+  long long M;
+  int KP;                      // K planes (multiple of 2)
+  int NT, n_ntiles;            // N tile (multiple of 16, <= 256) and count
+  int ldc;                     // elements per output row
+  int n_store;                 // columns of C that exist (<= ldc); columns >= n_store are not written
+  int relu, out_f32;
+  long long n_mtiles;
+};
+
+__device__ __forceinline__ uint32_t gt_elect_one() {
+  uint32_t pred = 0;
+  asm volatile("{\n\t.reg .pred px;\n\telect.sync _|px, 0xFFFFFFFF;\n\t@px mov.s32 %0, 1;\n\t}" : "+r"(pred));
+  return pred;
+}
+__device__ __forceinline__ void gt_bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t mbar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+               "r"(bytes), "r"(mbar)
+               : "memory");
+}
+__device__ __forceinline__ uint32_t gt_pack_h2(float a, float b) {
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+  return r;
+}
+
+__global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const __grid_constant__ GemmTcParams p) {
+  extern __shared__ __align__(1024) unsigned char gt_smem[];
+  __shared__ __align__(8) uint64_t bar_full[GT_NSTAGE], bar_empty[GT_NSTAGE], bar_accfull[2], bar_accempty[2];
+  __shared__ uint32_t tmem_base_s;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const int a_stage = GT_KC * 2048, b_stage = GT_KC * p.NT * 16, stage_bytes = a_stage + b_stage;
+  const uint32_t a_full = smem_u32(&bar_full[0]), a_empty = smem_u32(&bar_empty[0]);
+  const uint32_t a_accfull = smem_u32(&bar_accfull[0]), a_accempty = smem_u32(&bar_accempty[0]);
+  if (tid == 0) {
+    for (int s = 0; s < GT_NSTAGE; ++s) {
+      mbar_init(a_full + 8 * s, 1);
+      mbar_init(a_empty + 8 * s, 1);
+    }
+    for (int k = 0; k < 2; ++k) {
+      mbar_init(a_accfull + 8 * k, 1);
+      mbar_init(a_accempty + 8 * k, 4);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(smem_u32(&tmem_base_s), 512);
+  fence_before();
+  __syncthreads();
+  fence_after();
+  const uint32_t tmem = tmem_base_s;
+  const long long n_tiles = p.n_mtiles * p.n_ntiles;
+  const int n_ks = (p.KP + GT_KC - 1) / GT_KC;                      // stages per tile
+
+  if (warp == 0) {
+    // ======================================= producer =======================================
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (long long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        const long long mt = t / p.n_ntiles;
+        const int nt = static_cast<int>(t - mt * p.n_ntiles);
+        const unsigned char* At = p.A + mt * (static_cast<long long>(p.KP) * 2048);
+        const unsigned char* Bt = p.B + static_cast<long long>(nt) * p.KP * p.NT * 16;
+        for (int ks = 0; ks < n_ks; ++ks, ++it) {
+          const uint32_t s = it % GT_NSTAGE;
+          if (it >= GT_NSTAGE) mbar_wait(a_empty + 8 * s, ((it / GT_NSTAGE) & 1) ^ 1);
+          const int kc = min(GT_KC, p.KP - ks * GT_KC);
+          mbar_expect_tx(a_full + 8 * s, kc * 2048 + kc * p.NT * 16);
+          gt_bulk_load(smem_u32(gt_smem + s * stage_bytes), At + static_cast<long long>(ks) * GT_KC * 2048, kc * 2048, a_full + 8 * s);
+          gt_bulk_load(smem_u32(gt_smem + s * stage_bytes + a_stage), Bt + static_cast<long long>(ks) * GT_KC * p.NT * 16, kc * p.NT * 16,
+                       a_full + 8 * s);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ======================================= MMA issuer =====================================
+    const uint32_t idesc = make_idesc(128, p.NT, 0);
+    const uint64_t a_hi = make_desc(0, 2048, 128) & 0xFFFFFFFFFFFF0000ull;             // LBO = one plane of 128 rows
+    const uint64_t b_hi = make_desc(0, p.NT * 16, 128) & 0xFFFFFFFFFFFF0000ull;
+    uint32_t it = 0, c = 0;
+    for (long long t = blockIdx.x; t < n_tiles; t += gridDim.x, ++c) {
+      const uint32_t ab = c & 1;
+      if (c >= 2) {
+        mbar_wait(a_accempty + 8 * ab, ((c >> 1) & 1) ^ 1);
+        fence_after();
+      }
+      const uint32_t d = tmem + ab * GT_MAXNT;
+      for (int ks = 0; ks < n_ks; ++ks, ++it) {
+        const uint32_t s = it % GT_NSTAGE;
+        mbar_wait(a_full + 8 * s, (it / GT_NSTAGE) & 1);
+        fence_after();
+        const int kc = min(GT_KC, p.KP - ks * GT_KC);
+        if (gt_elect_one()) {
+          const uint32_t sa = smem_u32(gt_smem + s * stage_bytes), sb = sa + a_stage;
+          for (int j = 0; j < kc / 2; ++j) {
+            const uint64_t ad = a_hi | ((sa + j * 2 * 2048) >> 4);
+            const uint64_t bd = b_hi | ((sb + j * 2 * p.NT * 16) >> 4);
+            mma_f16_ss(d, ad, bd, idesc, (ks > 0 || j > 0) ? 1u : 0u);
+          }
+          commit(a_empty + 8 * s);
+          if (ks == n_ks - 1) commit(a_accfull + 8 * ab);
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // ======================================= epilogue =======================================
+    const int quad = warp & 3, row = quad * 32 + lane;
+    const uint32_t tlane = static_cast<uint32_t>(quad * 32) << 16;
+    uint32_t c = 0;
+    for (long long t = blockIdx.x; t < n_tiles; t += gridDim.x, ++c) {
+      const long long mt = t / p.n_ntiles;
+      const int nt = static_cast<int>(t - mt * p.n_ntiles);
+      const uint32_t ab = c & 1;
+      mbar_wait(a_accfull + 8 * ab, (c >> 1) & 1);
+      fence_after();
+      const long long m = mt * 128 + row;
+      const int col0 = nt * p.NT;
+      for (int c0 = 0; c0 < p.NT; c0 += 16) {
+        uint32_t v[16];
+        tmem_ld16(tmem + tlane + ab * GT_MAXNT + c0, v);
+        tmem_ld_wait();
+        if (c0 + 16 >= p.NT) {                                     // the accumulator is in registers: hand it back
+          fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(a_accempty + 8 * ab);
+        }
+        if (m >= p.M || col0 + c0 >= p.n_store) continue;
+        float f[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          f[k] = __uint_as_float(v[k]) + __ldg(p.bias + col0 + c0 + k);
+          if (p.relu) f[k] = fmaxf(f[k], 0.f);
+        }
+        if (p.out_f32) {
+          float* dst = static_cast<float*>(p.C) + m * p.ldc + col0 + c0;
+#pragma unroll
+          for (int k = 0; k < 16; ++k)
+            if (col0 + c0 + k < p.n_store) dst[k] = f[k];
+        } else {
+          __half* dst = static_cast<__half*>(p.C) + m * p.ldc + col0 + c0;
+          if (col0 + c0 + 16 <= p.n_store && (p.ldc & 7) == 0) {
+            *reinterpret_cast<uint4*>(dst) = make_uint4(gt_pack_h2(f[0], f[1]), gt_pack_h2(f[2], f[3]), gt_pack_h2(f[4], f[5]), gt_pack_h2(f[6], f[7]));
+            *reinterpret_cast<uint4*>(dst + 8) =
+                make_uint4(gt_pack_h2(f[8], f[9]), gt_pack_h2(f[10], f[11]), gt_pack_h2(f[12], f[13]), gt_pack_h2(f[14], f[15]));
+          } else {
+#pragma unroll
+            for (int k = 0; k < 16; ++k)
+              if (col0 + c0 + k < p.n_store) dst[k] = __float2half_rn(fminf(fmaxf(f[k], -65504.f), 65504.f));
+          }
+        }
+      }
+    }
+  }
+  fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
+
+// A operand of one layer (see the file comment).  One thread per 16-byte unit (row m, K plane), consecutive threads =
+// consecutive rows of one plane (coalesced 16-byte stores).  The previous layer's MaxPool(ph, pw) (floor mode, model.py:190,193)
+// is applied while reading: max over the window of the stored, already ReLU-ed f16 activation (max commutes with the f16 rounding).
+struct PackParams {
+  const void* in;              // float32 [B][Hin][Win] (in_f32) or f16 NHWC [B][Hin][Win][Cs]
+  unsigned char* A;
+  long long M, n_units;        // rows = B * Ho * Wo; units = n_mtiles * KP * 128
+  int in_f32, Hin, Win, Cs;    // stored input map (before the pool); Cs = channel stride (multiple of 8; 1 for float32)
+  int ph, pw;                  // pool window applied to the input
+  int KH, KW, sh, sw, Ho, Wo;  // kernel over the POOLED map, strides, output map
+  int K, KP;                   // real K = KH * KW * Cs and planes (multiple of 2)
+};
+
+__device__ __forceinline__ uint32_t pk_hmax2(uint32_t a, uint32_t b) {
+  uint32_t o;
+  asm("max.f16x2 %0, %1, %2;" : "=r"(o) : "r"(a), "r"(b));
+  return o;
+}
+
+__global__ void __launch_bounds__(256) gemm_pack_kernel(const PackParams p) {
+  for (long long u = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x; u < p.n_units; u += static_cast<long long>(gridDim.x) * 256) {
+    const int r = static_cast<int>(u & 127);
+    const long long tp = u >> 7;
+    const int plane = static_cast<int>(tp % p.KP);
+    const long long m = (tp / p.KP) * 128 + r;
+    uint4 o = make_uint4(0, 0, 0, 0);
+    if (m < p.M) {
+      const int P = p.Ho * p.Wo;
+      const long long clip = m / P;
+      const int pos = static_cast<int>(m - clip * P), ho = pos / p.Wo, wo = pos - ho * p.Wo;
+      if (p.in_f32) {
+        const float* x = static_cast<const float*>(p.in) + clip * p.Hin * p.Win;
+        uint32_t h[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const int k = plane * 8 + e;
+          float v = 0.f;
+          if (k < p.K) {
+            const int kh = k / p.KW, kw = k - kh * p.KW;
+            v = fminf(fmaxf(__ldg(x + (ho * p.sh + kh) * p.Win + wo * p.sw + kw), -60000.f), 60000.f);
+          }
+          h[e] = __half_as_ushort(__float2half_rn(v));
+        }
+        o = make_uint4(h[0] | (h[1] << 16), h[2] | (h[3] << 16), h[4] | (h[5] << 16), h[6] | (h[7] << 16));
+      } else {
+        const int k0 = plane * 8;
+        if (k0 < p.K) {
+          const int tap = k0 / p.Cs, c0 = k0 - tap * p.Cs;
+          const int kh = tap / p.KW, kw = tap - kh * p.KW;
+          const int hp = ho * p.sh + kh, wp = wo * p.sw + kw;          // position in the pooled map
+          const __half* base = static_cast<const __half*>(p.in) + ((clip * p.Hin + hp * p.ph) * p.Win + wp * p.pw) * p.Cs + c0;
+          o = __ldg(reinterpret_cast<const uint4*>(base));
+          for (int i = 0; i < p.ph; ++i)
+            for (int j = 0; j < p.pw; ++j) {
+              if (i == 0 && j == 0) continue;
+              const uint4 q = __ldg(reinterpret_cast<const uint4*>(base + (i * p.Win + j) * p.Cs));
+              o.x = pk_hmax2(o.x, q.x); o.y = pk_hmax2(o.y, q.y); o.z = pk_hmax2(o.z, q.z); o.w = pk_hmax2(o.w, q.w);
+            }
+        }
+      }
+    }
+    reinterpret_cast<uint4*>(p.A)[u] = o;
+  }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+struct GemmLayer {
+  // geometry
+  int in_f32 = 0, Hin = 0, Win = 0, Cs = 1, ph = 1, pw = 1, KH = 1, KW = 1, sh = 1, sw = 1, Ho = 1, Wo = 1;
+  int K = 0, KP = 0, N = 0, NT = 16, n_ntiles = 1, relu = 0;
+  unsigned char* d_B = nullptr;
+  float* d_bias = nullptr;
+  int ldc() const { return NT * n_ntiles; }
+};
+
+struct CnnGemmPlan {
+  std::vector<GemmLayer> layers;
+  int n_labels = 12, n_sms = 148, H0 = 101, W0 = 40;
+  int64_t chunk = 1024;                 // clips per pass (bounds the workspace: the im2col A operand is the large buffer)
+  int64_t a_bytes_per_clip = 0, act_bytes_per_clip = 0;
+  std::vector<void*> owned;
+};
+
+void cnn_gemm_plan_free(CnnGemmPlan* p) {
+  if (!p) return;
+  for (void* q : p->owned) cudaFree(q);
+  delete p;
+}
+
+namespace {
+
+template <typename T>
+int gt_up(CnnGemmPlan* p, const std::vector<T>& h, T** d) {
+  void* ptr = nullptr;
+  HONK_CUDA(cudaMalloc(&ptr, std::max<size_t>(h.size(), 1) * sizeof(T)));
+  p->owned.push_back(ptr);
+  HONK_CUDA(cudaMemcpy(ptr, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice));
+  *d = static_cast<T*>(ptr);
+  return HONK_OK;
+}
+
+// Packs one layer's weights: wk(n, kh, kw, c) is the weight of output n for tap (kh, kw) and REAL input channel c < Cin;
+// stored input channels c >= Cin (the previous layer's padding) get zero.
+template <typename F>
+int gt_pack_weights(CnnGemmPlan* p, GemmLayer& L, int Cin, const std::vector<float>& bias, F wk) {
+  L.K = L.KH * L.KW * L.Cs;
+  L.KP = (L.K + 15) / 16 * 2;
+  const int npad = (L.N + 15) / 16 * 16;
+  L.n_ntiles = (npad + GT_MAXNT - 1) / GT_MAXNT;
+  L.NT = ((npad + L.n_ntiles - 1) / L.n_ntiles + 15) / 16 * 16;
+  std::vector<__half> B(static_cast<size_t>(L.n_ntiles) * L.KP * L.NT * 8, __float2half(0.f));
+  std::vector<float> b(static_cast<size_t>(L.n_ntiles) * L.NT, 0.f);
+  for (int n = 0; n < L.N; ++n) {
+    const int nt = n / L.NT, nr = n - nt * L.NT;
+    b[n] = bias[n];
+    for (int kh = 0; kh < L.KH; ++kh)
+      for (int kw = 0; kw < L.KW; ++kw)
+        for (int c = 0; c < Cin; ++c) {
+          const int k = (kh * L.KW + kw) * L.Cs + c;
+          B[((static_cast<size_t>(nt) * L.KP + k / 8) * L.NT + nr) * 8 + k % 8] = __float2half(wk(n, kh, kw, c));
+        }
+  }
+  __half* d = nullptr;
+  HONK_TRY(gt_up(p, B, &d));
+  L.d_B = reinterpret_cast<unsigned char*>(d);
+  HONK_TRY(gt_up(p, b, &L.d_bias));
+  return HONK_OK;
+}
+
+}  // namespace
+
+// Every cnn-* configuration (model.py:385-407); *out stays nullptr only when a layer does not fit the kernel's limits.
+int cnn_gemm_plan_create(honk_model* m, CnnGemmPlan** out) {
+  *out = nullptr;
+  const honk_model_config& c = m->cfg;
+  if (c.family != HONK_FAMILY_CNN) return HONK_OK;
+  if (const char* e = getenv("HONK_DISABLE_GEMM_TC"))
+    if (atoi(e)) return HONK_OK;
+  std::unique_ptr<CnnGemmPlan, void (*)(CnnGemmPlan*)> p(new CnnGemmPlan(), cnn_gemm_plan_free);
+  p->n_labels = c.n_labels;
+  p->n_sms = m->n_sms;
+  p->H0 = m->H0;
+  p->W0 = m->W0;
+  auto conv_out = [](int n, int k, int s) { return (n - k) / s + 1; };
+  // ---- conv1 (model.py:187-190): float32 MFCC image in, NHWC f16 out
+  int H, W, C, Cs, ph, pw;                      // stored map of the latest conv layer and the pool still to be applied to it
+  {
+    GemmLayer L;
+    L.in_f32 = 1; L.Hin = m->H0; L.Win = m->W0; L.Cs = 1;
+    L.KH = c.conv1_size[0]; L.KW = c.conv1_size[1]; L.sh = c.conv1_stride[0]; L.sw = c.conv1_stride[1];
+    L.Ho = conv_out(m->H0, L.KH, L.sh); L.Wo = conv_out(m->W0, L.KW, L.sw);
+    L.N = c.n_feature_maps1; L.relu = 1;
+    if (L.Ho < 1 || L.Wo < 1) return HONK_OK;
+    const HostTensor& w = m->host.at("conv1.weight");
+    const int KH = L.KH, KW = L.KW;
+    HONK_TRY(gt_pack_weights(p.get(), L, 1, m->host.at("conv1.bias").data,
+                             [&](int n, int kh, int kw, int) { return w.data[(static_cast<size_t>(n) * KH + kh) * KW + kw]; }));
+    H = L.Ho; W = L.Wo; C = L.N; Cs = L.ldc(); ph = c.conv1_pool[0]; pw = c.conv1_pool[1];
+    p->layers.push_back(L);
+  }
+  // ---- conv2 (model.py:191-194)
+  if (c.has_conv2) {
+    GemmLayer L;
+    L.Hin = H; L.Win = W; L.Cs = Cs; L.ph = ph; L.pw = pw;
+    L.KH = c.conv2_size[0]; L.KW = c.conv2_size[1]; L.sh = c.conv2_stride[0]; L.sw = c.conv2_stride[1];
+    L.Ho = conv_out(H / ph, L.KH, L.sh); L.Wo = conv_out(W / pw, L.KW, L.sw);
+    L.N = c.n_feature_maps2; L.relu = 1;
+    if (L.Ho < 1 || L.Wo < 1) return HONK_OK;
+    const HostTensor& w = m->host.at("conv2.weight");
+    const int KH = L.KH, KW = L.KW, Cin = C;
+    HONK_TRY(gt_pack_weights(p.get(), L, Cin, m->host.at("conv2.bias").data, [&](int n, int kh, int kw, int ci) {
+      return w.data[((static_cast<size_t>(n) * Cin + ci) * KH + kh) * KW + kw];
+    }));
+    H = L.Ho; W = L.Wo; C = L.N; Cs = L.ldc(); ph = c.conv2_pool[0]; pw = c.conv2_pool[1];
+    p->layers.push_back(L);
+  }
+  // ---- linear layers (model.py:195-205): the first one is a convolution whose kernel covers the whole pooled map, with the
+  // weights permuted from the reference's (C, H, W) flatten order; the others are 1 x 1 over a 1 x 1 map
+  std::vector<std::pair<std::string, int>> fcs;       // (name, relu)
+  if (!c.tf_variant) fcs.push_back({"lin", 0});
+  if (c.dnn1_size > 0) {
+    fcs.push_back({"dnn1", c.tf_variant ? 0 : 1});
+    if (c.dnn2_size > 0) fcs.push_back({"dnn2", 0});
+  }
+  fcs.push_back({"output", 0});
+  bool first = true;
+  for (auto& fc : fcs) {
+    const HostTensor& w = m->host.at(fc.first + ".weight");
+    GemmLayer L;
+    L.Hin = H; L.Win = W; L.Cs = Cs; L.ph = ph; L.pw = pw;
+    L.KH = H / ph; L.KW = W / pw; L.Ho = 1; L.Wo = 1;
+    L.N = static_cast<int>(w.dims[0]); L.relu = fc.second;
+    const int KH = L.KH, KW = L.KW, Cin = C;
+    if (KH < 1 || KW < 1 || static_cast<int64_t>(w.dims[1]) != static_cast<int64_t>(Cin) * KH * KW)
+      return set_error(HONK_ERR_KEY, "size mismatch for \"%s.weight\"", fc.first.c_str());
+    (void)first;
+    HONK_TRY(gt_pack_weights(p.get(), L, Cin, m->host.at(fc.first + ".bias").data, [&](int n, int kh, int kw, int ci) {
+      return w.data[static_cast<size_t>(n) * Cin * KH * KW + (static_cast<size_t>(ci) * KH + kh) * KW + kw];   // flatten index c*H*W + h*W + w
+    }));
+    H = 1; W = 1; C = L.N; Cs = L.ldc(); ph = 1; pw = 1;
+    first = false;
+    p->layers.push_back(L);
+  }
+  // workspace per clip: the largest A operand and the largest activation (two ping-pong buffers)
+  for (const GemmLayer& L : p->layers) {
+    p->a_bytes_per_clip = std::max<int64_t>(p->a_bytes_per_clip, static_cast<int64_t>(L.Ho) * L.Wo * L.KP * 16);
+    p->act_bytes_per_clip = std::max<int64_t>(p->act_bytes_per_clip, static_cast<int64_t>(L.Ho) * L.Wo * L.ldc() * 2);
+    if (L.KP > 65535 * 2) return HONK_OK;
+  }
+  // clips per pass: keep the A operand of a pass under ~1 GB
+  p->chunk = std::max<int64_t>(128, std::min<int64_t>(4096, (1ll << 30) / std::max<int64_t>(p->a_bytes_per_clip, 1) / 128 * 128));
+  if (const char* e = getenv("HONK_GEMM_CHUNK")) p->chunk = std::max(1, atoi(e));      // tests: several passes on a small batch
+  int max_smem = 0;
+  HONK_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, m->device));
+  const int smem = GT_NSTAGE * (GT_KC * 2048 + GT_KC * GT_MAXNT * 16) + 1024;
+  if (smem + 1024 > max_smem) return HONK_OK;
+  HONK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  *out = p.release();
+  return HONK_OK;
+}
+
+static int64_t gt_a_bytes(const CnnGemmPlan* p, int64_t n) {
+  int64_t mx = 0;
+  for (const GemmLayer& L : p->layers) mx = std::max<int64_t>(mx, (n * L.Ho * L.Wo + 127) / 128 * L.KP * 2048);
+  return mx;
+}
+
+int64_t cnn_gemm_workspace_bytes(const CnnGemmPlan* p, int64_t n_clips) {
+  const int64_t n = std::min(n_clips, p->chunk);
+  Arena a(nullptr, 0);
+  a.take<unsigned char>(gt_a_bytes(p, n));
+  a.take<unsigned char>(n * p->act_bytes_per_clip);
+  a.take<unsigned char>(n * p->act_bytes_per_clip);
+  return align_up(a.off, 256);
+}
+
+int cnn_gemm_forward(const CnnGemmPlan* p, const float* d_mfcc, int64_t n_clips, float* d_logits, void* ws, int64_t ws_bytes,
+                     cudaStream_t s) {
+  const int64_t nmax = std::min(n_clips, p->chunk);
+  Arena ar(ws, ws_bytes);
+  unsigned char* A = ar.take<unsigned char>(gt_a_bytes(p, nmax));
+  unsigned char* act[2];
+  act[0] = ar.take<unsigned char>(nmax * p->act_bytes_per_clip);
+  act[1] = ar.take<unsigned char>(nmax * p->act_bytes_per_clip);
+  HONK_CHECK(ar.ok(), HONK_ERR_WORKSPACE, "internal: tcgen05 workspace overrun");
+  ProfSpan span("cnn_conv", s);
+  for (int64_t c0 = 0; c0 < n_clips; c0 += p->chunk) {
+    const int64_t n = std::min(p->chunk, n_clips - c0);
+    const void* in = d_mfcc + c0 * p->H0 * p->W0;
+    for (size_t li = 0; li < p->layers.size(); ++li) {
+      const GemmLayer& L = p->layers[li];
+      const bool last = li + 1 == p->layers.size();
+      PackParams pk{};
+      pk.in = in; pk.A = A;
+      pk.M = n * L.Ho * L.Wo;
+      const long long n_mtiles = (pk.M + 127) / 128;
+      pk.n_units = n_mtiles * L.KP * 128;
+      pk.in_f32 = L.in_f32; pk.Hin = L.Hin; pk.Win = L.Win; pk.Cs = L.Cs; pk.ph = L.ph; pk.pw = L.pw;
+      pk.KH = L.KH; pk.KW = L.KW; pk.sh = L.sh; pk.sw = L.sw; pk.Ho = L.Ho; pk.Wo = L.Wo; pk.K = L.K; pk.KP = L.KP;
+      static const char* kPack[] = {"gt_pack0", "gt_pack1", "gt_pack2", "gt_pack3", "gt_pack4", "gt_pack5"};
+      static const char* kGemm[] = {"gt_gemm0", "gt_gemm1", "gt_gemm2", "gt_gemm3", "gt_gemm4", "gt_gemm5"};
+      {
+        ProfSpan sp(kPack[std::min<size_t>(li, 5)], s);
+        gemm_pack_kernel<<<static_cast<unsigned>(std::min<long long>((pk.n_units + 255) / 256, 32ll * p->n_sms)), 256, 0, s>>>(pk);
+        HONK_LAUNCH_CHECK();
+      }
+      GemmTcParams g{};
+      g.A = A; g.B = L.d_B; g.bias = L.d_bias;
+      g.C = last ? static_cast<void*>(d_logits + c0 * p->n_labels) : static_cast<void*>(act[li & 1]);
+      g.M = pk.M; g.KP = L.KP; g.NT = L.NT; g.n_ntiles = L.n_ntiles;
+      g.ldc = last ? p->n_labels : L.ldc();
+      g.n_store = last ? p->n_labels : L.ldc();
+      g.relu = L.relu; g.out_f32 = last ? 1 : 0;
+      g.n_mtiles = n_mtiles;
+      const long long n_tiles = n_mtiles * L.n_ntiles;
+      const int smem = GT_NSTAGE * (GT_KC * 2048 + GT_KC * L.NT * 16) + 1024;
+      {
+        ProfSpan sp(kGemm[std::min<size_t>(li, 5)], s);
+        gemm_tc_kernel<<<static_cast<unsigned>(std::min<long long>(n_tiles, p->n_sms)), GT_THREADS, smem, s>>>(g);
+        HONK_LAUNCH_CHECK();
+      }
+      in = act[li & 1];
+    }
+  }
+  return HONK_OK;
+}
+
+}  // namespace honk

@@ -283,7 +283,8 @@ extern "C" int honk_model_create(const honk_model_config* cfg, const honk_tensor
     }
   } else if (cfg->precision == 0) {
     HONK_TRY(cnn_tc_plan_create(m.get(), &m->ctc));
-    if (m->ctc) m->path = "tcgen05-f16";
+    if (!m->ctc) HONK_TRY(cnn_gemm_plan_create(m.get(), &m->cgm));
+    if (m->ctc || m->cgm) m->path = "tcgen05-f16";
   }
   *out = m.release();
   return HONK_OK;
@@ -294,6 +295,7 @@ extern "C" int honk_model_destroy(honk_model* m) {
   if (m->tc) res_tc_plan_free(m->tc);
   if (m->tc2) res_tc2_plan_free(m->tc2);
   if (m->ctc) cnn_tc_plan_free(m->ctc);
+  if (m->cgm) cnn_gemm_plan_free(m->cgm);
   for (void* p : m->owned) cudaFree(p);
   delete m;
   return HONK_OK;
@@ -305,6 +307,7 @@ extern "C" int64_t honk_model_workspace_bytes(const honk_model* m, int64_t n_cli
   if (!m || n_clips <= 0) return 0;
   if (m->tc2) return res_tc2_workspace_bytes(m->tc2, n_clips);
   if (m->ctc) return cnn_tc_workspace_bytes(m->ctc, n_clips);
+  if (m->cgm) return cnn_gemm_workspace_bytes(m->cgm, n_clips);
   return m->tc ? res_tc_workspace_bytes(m, n_clips) : f32_workspace(m, n_clips);
 }
 
@@ -323,6 +326,7 @@ extern "C" int honk_model_forward(const honk_model* m, const float* d_mfcc, int6
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (m->tc2) return res_tc2_forward(m->tc2, d_mfcc, n_clips, d_logits, d_workspace, workspace_bytes, s);
   if (m->ctc) return cnn_tc_forward(m->ctc, d_mfcc, n_clips, d_logits, d_workspace, workspace_bytes, s);
+  if (m->cgm) return cnn_gemm_forward(m->cgm, d_mfcc, n_clips, d_logits, d_workspace, workspace_bytes, s);
   if (m->tc) return res_tc_forward(m, d_mfcc, n_clips, d_logits, d_workspace, workspace_bytes, s);
   ProfSpan span("f32_model", s);
   const int64_t in_per = static_cast<int64_t>(m->H0) * m->W0;
@@ -511,7 +515,7 @@ int pcm_elem_bytes(int dtype) { return dtype == HONK_PCM_I16 ? 2 : (dtype == HON
 double est_device_us_per_clip(const honk_model* m) {
   const honk_model_config& c = m->cfg;
   if (m->tc2 || m->tc) return 0.3 + 18.0 * c.n_feature_maps * c.n_feature_maps * m->Hr * m->Wr * c.n_layers / 7e8;
-  if (m->ctc) return 0.6;
+  if (m->ctc || m->cgm) return 0.6;
   return 20.0;
 }
 

@@ -26,6 +26,8 @@ struct ResTc2Plan;  // res_tc2.cu
 void res_tc2_plan_free(ResTc2Plan*);
 struct CnnTcPlan;   // cnn_tc.cu
 void cnn_tc_plan_free(CnnTcPlan*);
+struct CnnGemmPlan; // gemm_tc.cu
+void cnn_gemm_plan_free(CnnGemmPlan*);
 
 }  // namespace honk
 
@@ -40,6 +42,7 @@ struct honk_model {
   honk::ResTcPlan* tc = nullptr;                     // non-null => per-layer tcgen05 path (pooled res8/res26)
   honk::ResTc2Plan* tc2 = nullptr;                   // non-null => persistent multi-layer tcgen05 path (res15)
   honk::CnnTcPlan* ctc = nullptr;                    // non-null => tcgen05 path for the cnn-trad-pool2 geometry
+  honk::CnnGemmPlan* cgm = nullptr;                  // non-null => generic tcgen05 GEMM path for the other cnn-* configs
   std::string path = "cuda-core-f32";
   // geometry derived from cfg
   int H0 = 101, W0 = 40;                             // input
@@ -65,6 +68,11 @@ int fe_forward_x0(const honk_frontend* fe, const void* d_pcm, int dtype, int64_t
 bool fe_can_x0(const honk_frontend* fe, int dtype, int64_t n_clips, int64_t n_samples);
 int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, float* d_logits, void* ws, int64_t ws_bytes,
                     cudaStream_t s);
+// gemm_tc.cu: every layer of a cnn-* model as one tcgen05 GEMM (im2col pack + gemm_tc_kernel)
+int cnn_gemm_plan_create(honk_model* m, CnnGemmPlan** out);
+int64_t cnn_gemm_workspace_bytes(const CnnGemmPlan* p, int64_t n_clips);
+int cnn_gemm_forward(const CnnGemmPlan* p, const float* d_mfcc, int64_t n_clips, float* d_logits, void* ws, int64_t ws_bytes,
+                     cudaStream_t s);
 // cnn_tc.cu: tcgen05 conv1 + conv2 for cnn-trad-pool2; *out == nullptr when the geometry differs.
 int cnn_tc_plan_create(honk_model* m, CnnTcPlan** out);
 int64_t cnn_tc_workspace_bytes(const CnnTcPlan* p, int64_t n_clips);

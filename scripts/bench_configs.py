@@ -86,11 +86,12 @@ def throughput(name, B, pre, base):
         y = m.forward_pcm(pcm, pre)
         torch.cuda.synchronize()
         N.profile_enable(False)
-        spans = {k: N.profile_get(k)[0] for k in ("frontend", "res_conv0_pool", "res_conv", "cnn_pack_x8", "cnn_conv", "cnn_fc", "f32_model")
+        spans = {k: N.profile_get(k)[0] for k in ("frontend", "res_conv0_pool", "res_conv", "cnn_pack_x8", "cnn_conv", "cnn_fc", "f32_model") +
+                 tuple("gt_%s%d" % (k, i) for k in ("pack", "gemm") for i in range(6))
                  if N.profile_get(k)[1]}
     ms = e0.elapsed_time(e1) / 10
     flops = orc.conv_flops_per_clip(name, cfg)
-    cpu, ref, n = cpu_reference(name, cfg, sd, base)
+    cpu, ref, n = cpu_reference(name, cfg, sd, base[:min(len(base), B)])
     got = y[:n].cpu().numpy()
     tf, src = peaks()
     return {"config": name, "batch": B, "path": m.native_path, "frontend_path": pre.native_path, "ms_per_step": ms, "clips_per_s": B / ms * 1e3,

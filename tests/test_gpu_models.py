@@ -344,3 +344,41 @@ def _res_stream(orc, sd, cfg, mf):
             mu = torch.as_tensor(sd["bn%d.running_mean" % i], dtype=torch.float64)[None, :, None, None]
             var = torch.as_tensor(sd["bn%d.running_var" % i], dtype=torch.float64)[None, :, None, None]
             x = (x - mu) / torch.sqrt(var + 1e-5)
+
+
+CNN_GEMM = ["cnn-one-stride1", "cnn-one-fpool3", "cnn-one-fstride4", "cnn-one-fstride8", "cnn-tpool2", "cnn-tpool3", "cnn-tstride2",
+            "cnn-tstride4", "cnn-tstride8"]
+
+
+@pytest.mark.parametrize("name", CNN_GEMM)
+def test_cnn_family_on_tensor_cores(golden_dir, name, monkeypatch):
+    # the nine cnn-* configs other than cnn-trad-pool2 (model.py:385-407) run every layer as a tcgen05 GEMM
+    # (gemm_tc.cu).  Golden logits of the reference's own classes, ragged batch sizes (one clip, a partial M tile, more clips
+    # than one pass of the im2col workspace holds) against the FP32 CUDA-core path, and the oracle at 12 labels.
+    from oracle import honk_oracle as orc
+    g, cfg, sd = load_golden(golden_dir, name)
+    m16, m32 = build(name, cfg, sd, 0), build(name, cfg, sd, 1)
+    x = torch.from_numpy(g["x"]).cuda()
+    y = m16(x).cpu().numpy()
+    m32(x)
+    assert m16.native_path == "tcgen05-f16" and m32.native_path == "cuda-core-f32"
+    ref = g[name + "/logits_f64"]
+    assert np.abs(y - ref).max() / np.abs(ref).max() <= TOL["tcgen05-f16"]
+    rng = np.random.default_rng(7)
+    monkeypatch.setenv("HONK_GEMM_CHUNK", "256")                      # several passes without a multi-GB batch
+    m16b = build(name, cfg, sd, 0)
+    for n in (1, 3, 130, 700):
+        xb = torch.from_numpy((rng.standard_normal((n, 101, 40)) * np.abs(g["x"]).std()).astype(np.float32)).cuda()
+        y16, y32 = m16b(xb).cpu().numpy(), m32(xb).cpu().numpy()
+        assert y16.shape == (n, cfg["n_labels"])
+        assert np.abs(y16 - y32).max() / np.abs(y32).max() <= TOL["tcgen05-f16"], (name, n)
+        assert np.array_equal(m16b(xb).cpu().numpy(), y16)            # no atomics on this path: deterministic
+    cfg12 = dict(cfg)
+    cfg12["n_labels"] = 12
+    sd12 = synth.make_state_dict(name, cfg12, seed=17)
+    clips = synth.make_clips(40, start=6100)
+    mf = orc.AudioPreprocessorOracle().compute_mfccs_batch([orc.pcm16_to_float(c) for c in clips])
+    ref = orc.cnn_forward(sd12, cfg12, mf, torch.float64).numpy()
+    import honk_b200 as hb
+    yp = build(name, cfg12, sd12, 0).forward_pcm(torch.from_numpy(clips).cuda(), hb.AudioPreprocessor()).cpu().numpy()
+    assert np.abs(yp - ref).max() / np.abs(ref).max() <= TOL["tcgen05-f16"]

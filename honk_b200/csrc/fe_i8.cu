@@ -193,6 +193,24 @@ __device__ __forceinline__ float f3_round_f32(long long S, uint32_t a) {
   return __int2float_rn(W) * __int_as_float((127 + e) << 23);
 }
 
+// The same rounding with the 64-bit integer -> float32 conversion of the XU pipe (I2F.F32.S64, round to nearest even), which
+// runs beside the ALU pipe the Horner steps saturate: Z = T when it fits 64 bits (|V| < 2^55), else V with r as a sticky
+// bit (V then has at least 56 significant bits, so bit 0 lies far below the rounding position).  -DF3_ROUND_ALU selects the
+// all-ALU version above (measured slower: profiles/r04_fe3_round.txt).
+__device__ __forceinline__ float f3_round_f32_xu(long long S, uint32_t a) {
+  const long long V = S + static_cast<long long>(static_cast<int>(a) >> 8);
+  const uint32_t r = a & 255u;
+  const int32_t vhi = static_cast<int32_t>(V >> 32);
+  const bool fits = static_cast<uint32_t>(vhi + (1 << 23)) < (1u << 24);                 // |V| < 2^55
+  const long long Z = fits ? ((V << 8) | static_cast<long long>(r)) : (V | static_cast<long long>(r != 0u));
+  return __ll2float_rn(Z) * __int_as_float((127 + (fits ? -61 : -53)) << 23);
+}
+#ifdef F3_ROUND_ALU
+#define F3_ROUND f3_round_f32
+#else
+#define F3_ROUND f3_round_f32_xu
+#endif
+
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(F3_THREADS, 1) fe3_dft_kernel(const __grid_constant__ Fe3Args a) {
   extern __shared__ __align__(1024) unsigned char f3_smem[];
   __shared__ __align__(8) uint64_t bar_bfull[F3_NSTAGE], bar_bempty[F3_NSTAGE], bar_afull[2], bar_aempty[2];
@@ -567,8 +585,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(F3_THREADS, 1) fe3_d
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
                 const int kk = g * 8 + 2 * e;
-                const float re = f3_round_f32((static_cast<long long>(sh[kk]) << 32) | Sl[q * 16 + kk], v[kk]);
-                const float im = f3_round_f32((static_cast<long long>(sh[kk + 1]) << 32) | Sl[q * 16 + kk + 1], v[kk + 1]);
+                const float re = F3_ROUND((static_cast<long long>(sh[kk]) << 32) | Sl[q * 16 + kk], v[kk]);
+                const float im = F3_ROUND((static_cast<long long>(sh[kk + 1]) << 32) | Sl[q * 16 + kk + 1], v[kk + 1]);
                 // np.abs(complex64)**2 is hypotf(re, im)^2 in float32; re*re + im*im with one fused rounding is within 2 float32
                 // ulps of it (both are within 1.5 ulp of the exact sum) - 1e-7 relative in a mel energy, 1e-7 absolute in a log
                 pw[e] = fmaf(re, re, im * im);
@@ -632,18 +650,21 @@ __global__ void __launch_bounds__(128, 4) fe3_post_kernel(const FeDev t, const f
 #pragma unroll
     for (int ks = 0; ks < NKD; ++ks) bd[c][ks] = c < nct ? __ldg(t.dct + (8 * (ct0 + c) + row) * NM + 4 * ks + kq) : 0.0;
   __syncthreads();
+  static_assert((F3P_FR * KPC) % 128 == 0, "whole rounds of the 128 threads");
+  constexpr int NLD = F3P_FR * KPC / 128;
+  float pv[NLD];                                                     // the NEXT item's power values: loaded under this item's arithmetic
+  auto fetch = [&](int item) {
+    const long long g0 = static_cast<long long>(item) * F3P_FR;
+    const long long lim = (total_frames - g0) * KPC;                 // the item's frames are contiguous rows of Pg
+#pragma unroll
+    for (int u = 0; u < NLD; ++u) pv[u] = (item < n_items && tid + u * 128 < lim) ? __ldg(Pg + g0 * KPC + tid + u * 128) : 0.f;
+  };
+  fetch(blockIdx.x);
   for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
     const long long g0 = static_cast<long long>(item) * F3P_FR;
-    {
-      static_assert((F3P_FR * KPC) % 128 == 0, "whole rounds of the 128 threads");
-      constexpr int NLD = F3P_FR * KPC / 128;
-      float pv[NLD];
-      const long long lim = (total_frames - g0) * KPC;               // the item's frames are contiguous rows of Pg
 #pragma unroll
-      for (int u = 0; u < NLD; ++u) pv[u] = (tid + u * 128 < lim) ? __ldg(Pg + g0 * KPC + tid + u * 128) : 0.f;
-#pragma unroll
-      for (int u = 0; u < NLD; ++u) P[tid + u * 128] = fe2_f32_to_f64(pv[u]);
-    }
+    for (int u = 0; u < NLD; ++u) P[tid + u * 128] = fe2_f32_to_f64(pv[u]);
+    fetch(item + gridDim.x);
     __syncthreads();
     if (act) {
       const double* Pb = P + lo;

@@ -219,49 +219,106 @@ __device__ __forceinline__ uint32_t pk_hmax2(uint32_t a, uint32_t b) {
   return o;
 }
 
+// One thread per ROW m of A: (clip, ho, wo) is decoded once, then the thread walks the K planes of its row.  Consecutive threads
+// are consecutive rows, so every plane step of a warp is 32 adjacent 16-byte stores, and neighbouring rows read overlapping
+// input (L1 hits).  The input of a pooled layer has been pooled by gemm_pool_kernel before (ph = pw = 1 here).
 __global__ void __launch_bounds__(256) gemm_pack_kernel(const PackParams p) {
+  const long long n_rows = (p.M + 127) / 128 * 128;
+  for (long long m = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x; m < n_rows; m += static_cast<long long>(gridDim.x) * 256) {
+    uint4* dst = reinterpret_cast<uint4*>(p.A) + (m >> 7) * (static_cast<long long>(p.KP) * 128) + (m & 127);
+    if (m >= p.M) {
+      for (int pl = 0; pl < p.KP; ++pl) dst[static_cast<long long>(pl) * 128] = make_uint4(0, 0, 0, 0);
+      continue;
+    }
+    const int P = p.Ho * p.Wo;
+    const long long clip = m / P;
+    const int pos = static_cast<int>(m - clip * P), ho = pos / p.Wo, wo = pos - ho * p.Wo;
+    if (p.in_f32) {
+      const float* x = static_cast<const float*>(p.in) + (clip * p.Hin + ho * p.sh) * p.Win + wo * p.sw;
+      if (p.KW == 8) {                                       // every reference config: one kernel row = one plane
+        for (int kh = 0; kh < p.KP; ++kh) {
+          uint4 o = make_uint4(0, 0, 0, 0);
+          if (kh < p.KH) {
+            uint32_t h[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) h[e] = __half_as_ushort(__float2half_rn(fminf(fmaxf(__ldg(x + kh * p.Win + e), -60000.f), 60000.f)));
+            o = make_uint4(h[0] | (h[1] << 16), h[2] | (h[3] << 16), h[4] | (h[5] << 16), h[6] | (h[7] << 16));
+          }
+          dst[static_cast<long long>(kh) * 128] = o;
+        }
+      } else {
+        for (int pl = 0; pl < p.KP; ++pl) {
+          uint32_t h[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const int k = pl * 8 + e;
+            float v = 0.f;
+            if (k < p.K) {
+              const int kh = k / p.KW, kw = k - kh * p.KW;
+              v = fminf(fmaxf(__ldg(x + kh * p.Win + kw), -60000.f), 60000.f);
+            }
+            h[e] = __half_as_ushort(__float2half_rn(v));
+          }
+          dst[static_cast<long long>(pl) * 128] = make_uint4(h[0] | (h[1] << 16), h[2] | (h[3] << 16), h[4] | (h[5] << 16), h[6] | (h[7] << 16));
+        }
+      }
+    } else {
+      const int cpt = p.Cs >> 3;                             // planes per tap
+      const uint4* base = reinterpret_cast<const uint4*>(static_cast<const __half*>(p.in) + ((clip * p.Hin + ho * p.sh) * p.Win + wo * p.sw) * p.Cs);
+      int pl = 0;
+      for (int kh = 0; kh < p.KH; ++kh)
+        for (int kw = 0; kw < p.KW; ++kw) {
+          const uint4* src = base + (kh * p.Win + kw) * cpt;
+          for (int c = 0; c < cpt; ++c, ++pl) dst[static_cast<long long>(pl) * 128] = __ldg(src + c);
+        }
+      for (; pl < p.KP; ++pl) dst[static_cast<long long>(pl) * 128] = make_uint4(0, 0, 0, 0);
+    }
+  }
+}
+
+// The same operand with one thread per 16-byte unit (row, plane): for layers with few rows and a long K (the first linear layer
+// after the convolutions: M = clips, K = the whole map), where a thread per row would leave most of the GPU idle.  NHWC input only.
+__global__ void __launch_bounds__(256) gemm_pack_units_kernel(const PackParams p) {
+  const int cpt = p.Cs >> 3, n_taps = p.KH * p.KW;
   for (long long u = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x; u < p.n_units; u += static_cast<long long>(gridDim.x) * 256) {
     const int r = static_cast<int>(u & 127);
     const long long tp = u >> 7;
     const int plane = static_cast<int>(tp % p.KP);
     const long long m = (tp / p.KP) * 128 + r;
     uint4 o = make_uint4(0, 0, 0, 0);
-    if (m < p.M) {
+    const int tap = plane / cpt, c = plane - tap * cpt;
+    if (m < p.M && tap < n_taps) {
       const int P = p.Ho * p.Wo;
       const long long clip = m / P;
       const int pos = static_cast<int>(m - clip * P), ho = pos / p.Wo, wo = pos - ho * p.Wo;
-      if (p.in_f32) {
-        const float* x = static_cast<const float*>(p.in) + clip * p.Hin * p.Win;
-        uint32_t h[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const int k = plane * 8 + e;
-          float v = 0.f;
-          if (k < p.K) {
-            const int kh = k / p.KW, kw = k - kh * p.KW;
-            v = fminf(fmaxf(__ldg(x + (ho * p.sh + kh) * p.Win + wo * p.sw + kw), -60000.f), 60000.f);
-          }
-          h[e] = __half_as_ushort(__float2half_rn(v));
-        }
-        o = make_uint4(h[0] | (h[1] << 16), h[2] | (h[3] << 16), h[4] | (h[5] << 16), h[6] | (h[7] << 16));
-      } else {
-        const int k0 = plane * 8;
-        if (k0 < p.K) {
-          const int tap = k0 / p.Cs, c0 = k0 - tap * p.Cs;
-          const int kh = tap / p.KW, kw = tap - kh * p.KW;
-          const int hp = ho * p.sh + kh, wp = wo * p.sw + kw;          // position in the pooled map
-          const __half* base = static_cast<const __half*>(p.in) + ((clip * p.Hin + hp * p.ph) * p.Win + wp * p.pw) * p.Cs + c0;
-          o = __ldg(reinterpret_cast<const uint4*>(base));
-          for (int i = 0; i < p.ph; ++i)
-            for (int j = 0; j < p.pw; ++j) {
-              if (i == 0 && j == 0) continue;
-              const uint4 q = __ldg(reinterpret_cast<const uint4*>(base + (i * p.Win + j) * p.Cs));
-              o.x = pk_hmax2(o.x, q.x); o.y = pk_hmax2(o.y, q.y); o.z = pk_hmax2(o.z, q.z); o.w = pk_hmax2(o.w, q.w);
-            }
-        }
-      }
+      const int kh = tap / p.KW, kw = tap - kh * p.KW;
+      o = __ldg(reinterpret_cast<const uint4*>(static_cast<const __half*>(p.in) + ((clip * p.Hin + ho * p.sh + kh) * p.Win + wo * p.sw + kw) * p.Cs) + c);
     }
     reinterpret_cast<uint4*>(p.A)[u] = o;
+  }
+}
+
+// MaxPool(ph, pw), floor mode (model.py:190, 193), over an NHWC f16 map: [B][Hin][Win][Cs] -> [B][Hin / ph][Win / pw][Cs].
+// One thread per 16-byte unit (8 channels) of the output.
+__global__ void __launch_bounds__(256) gemm_pool_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, long long n_units, int Hin, int Win,
+                                                        int cpt, int ph, int pw) {
+  const int Hp = Hin / ph, Wp = Win / pw;
+  for (long long u = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x; u < n_units; u += static_cast<long long>(gridDim.x) * 256) {
+    const int c = static_cast<int>(u % cpt);
+    long long t = u / cpt;
+    const int wp = static_cast<int>(t % Wp);
+    t /= Wp;
+    const int hp = static_cast<int>(t % Hp);
+    const long long clip = t / Hp;
+    const uint4* src = in + ((clip * Hin + hp * ph) * Win + wp * pw) * cpt + c;
+    uint4 o = __ldg(src);
+    for (int i = 0; i < ph; ++i)
+      for (int j = 0; j < pw; ++j) {
+        if (i == 0 && j == 0) continue;
+        const uint4 q = __ldg(src + (i * Win + j) * cpt);
+        o.x = pk_hmax2(o.x, q.x); o.y = pk_hmax2(o.y, q.y); o.z = pk_hmax2(o.z, q.z); o.w = pk_hmax2(o.w, q.w);
+      }
+    out[u] = o;
   }
 }
 
@@ -283,7 +340,7 @@ struct CnnGemmPlan {
   std::vector<GemmLayer> layers;
   int n_labels = 12, n_sms = 148, H0 = 101, W0 = 40;
   int64_t chunk = 1024;                 // clips per pass (bounds the workspace: the im2col A operand is the large buffer)
-  int64_t a_bytes_per_clip = 0, act_bytes_per_clip = 0;
+  int64_t a_bytes_per_clip = 0, act_bytes_per_clip = 0, pool_bytes_per_clip = 0;
   std::vector<void*> owned;
 };
 
@@ -411,6 +468,8 @@ int cnn_gemm_plan_create(honk_model* m, CnnGemmPlan** out) {
   for (const GemmLayer& L : p->layers) {
     p->a_bytes_per_clip = std::max<int64_t>(p->a_bytes_per_clip, static_cast<int64_t>(L.Ho) * L.Wo * L.KP * 16);
     p->act_bytes_per_clip = std::max<int64_t>(p->act_bytes_per_clip, static_cast<int64_t>(L.Ho) * L.Wo * L.ldc() * 2);
+    if (!L.in_f32 && L.ph * L.pw > 1)
+      p->pool_bytes_per_clip = std::max<int64_t>(p->pool_bytes_per_clip, static_cast<int64_t>(L.Hin / L.ph) * (L.Win / L.pw) * L.Cs * 2);
     if (L.KP > 65535 * 2) return HONK_OK;
   }
   // clips per pass: keep the A operand of a pass under ~1 GB
@@ -437,6 +496,7 @@ int64_t cnn_gemm_workspace_bytes(const CnnGemmPlan* p, int64_t n_clips) {
   a.take<unsigned char>(gt_a_bytes(p, n));
   a.take<unsigned char>(n * p->act_bytes_per_clip);
   a.take<unsigned char>(n * p->act_bytes_per_clip);
+  a.take<unsigned char>(n * p->pool_bytes_per_clip);
   return align_up(a.off, 256);
 }
 
@@ -448,6 +508,7 @@ int cnn_gemm_forward(const CnnGemmPlan* p, const float* d_mfcc, int64_t n_clips,
   unsigned char* act[2];
   act[0] = ar.take<unsigned char>(nmax * p->act_bytes_per_clip);
   act[1] = ar.take<unsigned char>(nmax * p->act_bytes_per_clip);
+  unsigned char* pooled = ar.take<unsigned char>(nmax * p->pool_bytes_per_clip);
   HONK_CHECK(ar.ok(), HONK_ERR_WORKSPACE, "internal: tcgen05 workspace overrun");
   ProfSpan span("cnn_conv", s);
   for (int64_t c0 = 0; c0 < n_clips; c0 += p->chunk) {
@@ -456,18 +517,32 @@ int cnn_gemm_forward(const CnnGemmPlan* p, const float* d_mfcc, int64_t n_clips,
     for (size_t li = 0; li < p->layers.size(); ++li) {
       const GemmLayer& L = p->layers[li];
       const bool last = li + 1 == p->layers.size();
+      static const char* kPack[] = {"gt_pack0", "gt_pack1", "gt_pack2", "gt_pack3", "gt_pack4", "gt_pack5"};
+      static const char* kGemm[] = {"gt_gemm0", "gt_gemm1", "gt_gemm2", "gt_gemm3", "gt_gemm4", "gt_gemm5"};
+      int Hin = L.Hin, Win = L.Win;
+      if (!L.in_f32 && L.ph * L.pw > 1) {                    // the previous layer's MaxPool, once, before the im2col reads it many times
+        ProfSpan sp(kPack[std::min<size_t>(li, 5)], s);
+        Hin = L.Hin / L.ph;
+        Win = L.Win / L.pw;
+        const long long units = n * Hin * Win * (L.Cs >> 3);
+        gemm_pool_kernel<<<static_cast<unsigned>(std::min<long long>((units + 255) / 256, 32ll * p->n_sms)), 256, 0, s>>>(
+            static_cast<const uint4*>(in), reinterpret_cast<uint4*>(pooled), units, L.Hin, L.Win, L.Cs >> 3, L.ph, L.pw);
+        HONK_LAUNCH_CHECK();
+        in = pooled;
+      }
       PackParams pk{};
       pk.in = in; pk.A = A;
       pk.M = n * L.Ho * L.Wo;
       const long long n_mtiles = (pk.M + 127) / 128;
       pk.n_units = n_mtiles * L.KP * 128;
-      pk.in_f32 = L.in_f32; pk.Hin = L.Hin; pk.Win = L.Win; pk.Cs = L.Cs; pk.ph = L.ph; pk.pw = L.pw;
+      pk.in_f32 = L.in_f32; pk.Hin = Hin; pk.Win = Win; pk.Cs = L.Cs; pk.ph = 1; pk.pw = 1;
       pk.KH = L.KH; pk.KW = L.KW; pk.sh = L.sh; pk.sw = L.sw; pk.Ho = L.Ho; pk.Wo = L.Wo; pk.K = L.K; pk.KP = L.KP;
-      static const char* kPack[] = {"gt_pack0", "gt_pack1", "gt_pack2", "gt_pack3", "gt_pack4", "gt_pack5"};
-      static const char* kGemm[] = {"gt_gemm0", "gt_gemm1", "gt_gemm2", "gt_gemm3", "gt_gemm4", "gt_gemm5"};
       {
         ProfSpan sp(kPack[std::min<size_t>(li, 5)], s);
-        gemm_pack_kernel<<<static_cast<unsigned>(std::min<long long>((pk.n_units + 255) / 256, 32ll * p->n_sms)), 256, 0, s>>>(pk);
+        if (!L.in_f32 && n_mtiles * 128 < 512ll * p->n_sms && L.KP >= 64)
+          gemm_pack_units_kernel<<<static_cast<unsigned>(std::min<long long>((pk.n_units + 255) / 256, 32ll * p->n_sms)), 256, 0, s>>>(pk);
+        else
+          gemm_pack_kernel<<<static_cast<unsigned>(std::min<long long>((n_mtiles * 128 + 255) / 256, 32ll * p->n_sms)), 256, 0, s>>>(pk);
         HONK_LAUNCH_CHECK();
       }
       GemmTcParams g{};

@@ -31,6 +31,33 @@ def f3_round_f32(S, a):
     return np.float32(np.float32(W) * np.float32(2.0 ** e))
 
 
+def _rn_int(z, scale_exp):
+    """float32(z * 2^scale_exp) with one round-to-nearest-even from the exact integer z (what I2F.F32.S64 + a power-of-two
+    scale give)."""
+    if z == 0:
+        return np.float32(0)
+    sign, m = (-1 if z < 0 else 1), abs(z)
+    nb = m.bit_length()
+    if nb > 24:
+        shift = nb - 24
+        q, rem = divmod(m, 1 << shift)
+        half = 1 << (shift - 1)
+        if rem > half or (rem == half and (q & 1)):
+            q += 1
+        return np.float32(sign * float(q) * 2.0 ** (shift + scale_exp))
+    return np.float32(sign * m * 2.0 ** scale_exp)
+
+
+def f3_round_f32_xu(S, a):
+    """Mirror of the XU-pipe variant (the default): Z = T if |V| < 2^55 else V | sticky, one 64-bit integer conversion."""
+    V = S + (_s32(a) >> 8)
+    r = a & 255
+    fits = -(1 << 55) <= V < (1 << 55)
+    Z = (V << 8) | r if fits else (V | (1 if r else 0))
+    assert -(1 << 63) <= Z < (1 << 63)
+    return _rn_int(Z, -61 if fits else -53)
+
+
 def exact_rn(S, a):
     T = 256 * S + _s32(a)
     if T == 0:
@@ -63,6 +90,7 @@ def test_integer_rounding_matches_exact_rn():
             a = rnd.choice([0, 128, 255, 256, 0xFFFFFF00, 0xFFFFFF80, 1, 0xFFFFFFFF])
         S = max(-(2 ** 62), min(2 ** 62, S))
         assert f3_round_f32(S, a) == exact_rn(S, a), (S, _s32(a))
+        assert f3_round_f32_xu(S, a) == exact_rn(S, a), (S, _s32(a))
     # ties: T = (2 q + 1) * 2^(shift - 1) exactly
     for q in (2 ** 23, 2 ** 23 + 1, 2 ** 24 - 1, 2 ** 24 - 2):
         for shift in (1, 2, 7, 8, 9, 16, 30, 40):
@@ -70,3 +98,4 @@ def test_integer_rounding_matches_exact_rn():
             for sgn in (1, -1):
                 S, a = divmod(sgn * T, 256)
                 assert f3_round_f32(S, a) == exact_rn(S, a), (q, shift, sgn)
+                assert f3_round_f32_xu(S, a) == exact_rn(S, a), (q, shift, sgn)

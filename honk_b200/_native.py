@@ -25,6 +25,8 @@ EXPORTS = [
     "honk_model_forward_pcm_host", "honk_model_label_pcm_host", "honk_model_workspace_bytes_pcm_host",
     "honk_label_from_logits", "honk_eval_metrics", "honk_load_audio", "honk_listen", "honk_listen_num_windows", "honk_listen_workspace_bytes", "honk_launch_count", "honk_model_path", "honk_profile_enable",
     "honk_profile_reset", "honk_profile_get",
+    "honk_trainer_create", "honk_trainer_destroy", "honk_trainer_workspace_bytes", "honk_trainer_step",
+    "honk_trainer_reset_optimizer", "honk_trainer_steps", "honk_trainer_read",
 ]
 
 
@@ -42,6 +44,10 @@ class ModelConfig(C.Structure):
                 ("conv2_size", C.c_int32 * 2), ("conv2_pool", C.c_int32 * 2), ("conv2_stride", C.c_int32 * 2),
                 ("tf_variant", C.c_int32), ("dnn1_size", C.c_int32), ("dnn2_size", C.c_int32),
                 ("precision", C.c_int32)]
+
+
+class Sgd(C.Structure):
+    _fields_ = [("lr", C.c_float), ("momentum", C.c_float), ("weight_decay", C.c_float), ("nesterov", C.c_int32)]
 
 
 class Tensor(C.Structure):
@@ -106,6 +112,15 @@ def lib():
         L.honk_profile_enable.argtypes = [C.c_int]
         L.honk_profile_get.argtypes = [C.c_char_p, C.POINTER(C.c_double), C.POINTER(i64)]
         L.honk_model_path.restype = C.c_char_p
+        L.honk_trainer_create.argtypes = [C.POINTER(ModelConfig), C.POINTER(Tensor), i32, C.c_int, C.POINTER(vp)]
+        L.honk_trainer_destroy.argtypes = [vp]
+        L.honk_trainer_workspace_bytes.argtypes = [vp, i64]
+        L.honk_trainer_workspace_bytes.restype = i64
+        L.honk_trainer_step.argtypes = [vp, vp, vp, i64, i32, i32, C.POINTER(Sgd), vp, vp, vp, i64, vp]
+        L.honk_trainer_reset_optimizer.argtypes = [vp]
+        L.honk_trainer_steps.argtypes = [vp]
+        L.honk_trainer_steps.restype = i64
+        L.honk_trainer_read.argtypes = [vp, C.c_char_p, vp, i64]
         if L.honk_abi_version() != 2:
             raise RuntimeError("honk_b200: ABI version mismatch")
         _lib = L

@@ -9,7 +9,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libhonk_b200.so")
-SOURCES = ["core.cu", "frontend.cu", "fe_i8.cu", "generic_ops.cu", "model.cu", "res_tc.cu", "res_tc_conv.cu", "res_tc2.cu", "cnn_tc.cu", "gemm_tc.cu"]
+SOURCES = ["core.cu", "frontend.cu", "fe_i8.cu", "generic_ops.cu", "model.cu", "res_tc.cu", "res_tc_conv.cu", "res_tc2.cu", "cnn_tc.cu", "gemm_tc.cu", "train.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-fvisibility=hidden", "--expt-relaxed-constexpr"]
 

@@ -149,3 +149,460 @@ __global__ void flip_weights_kernel(const float* __restrict__ w, float* __restri
     wt[(ci * Cout + co) * 9 + (8 - tap)] = w[i];
   }
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// weight gradient of a 3x3 stride-1 convolution with pad == dilation == d:
+//   dw[co][ci][kh][kw] = sum_{b,h,w} dy[b][co][h][w] * x[b][ci][h + (kh-1)d][w + (kw-1)d]
+// grid (Cin, nsplit, co-chunks of WG_CO); one thread per (co, tap) of the chunk; the block walks its share of the B*H
+// rows, staging dy[b][chunk][h][:] and the three x rows (zero-padded by d on both sides) in shared memory.
+// Partials go to part[split][co][ci][9]; wgrad_reduce_kernel adds them in a fixed order (deterministic).
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int WG_CO = 28, WG_THREADS = 256;
+
+__global__ void __launch_bounds__(WG_THREADS) wgrad3x3_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                                                              float* __restrict__ part, int B, int Cin, int Cout, int H, int W, int d) {
+  extern __shared__ float wg_smem[];
+  const int Wp = W + 2 * d;
+  float* dys = wg_smem;                 // [WG_CO][W]
+  float* xs = wg_smem + WG_CO * W;      // [3][Wp]
+  const int ci = blockIdx.x, sp = blockIdx.y, co0 = blockIdx.z * WG_CO;
+  const int nco = min(WG_CO, Cout - co0);
+  const int tid = threadIdx.x;
+  const long long rows = static_cast<long long>(B) * H;
+  const long long per = (rows + gridDim.y - 1) / gridDim.y;
+  const long long r0 = sp * per, r1 = min(rows, r0 + per);
+  const int o_co = tid / 9, o_tap = tid - o_co * 9;
+  const bool active = o_co < nco;
+  const float* a_row = dys + o_co * W;
+  const float* b_row = xs + (o_tap / 3) * Wp + (o_tap % 3) * d;
+  for (int i = tid; i < 3 * Wp; i += WG_THREADS) xs[i] = 0.f;   // the side pads stay zero from here on
+  float acc = 0.f;
+  for (long long r = r0; r < r1; ++r) {
+    const int b = static_cast<int>(r / H), h = static_cast<int>(r - static_cast<long long>(b) * H);
+    __syncthreads();
+    for (int i = tid; i < nco * W; i += WG_THREADS) {
+      const int co = i / W, w = i - co * W;
+      dys[i] = dy[((static_cast<long long>(b) * Cout + co0 + co) * H + h) * W + w];
+    }
+    for (int i = tid; i < 3 * W; i += WG_THREADS) {
+      const int kh = i / W, w = i - kh * W;
+      const int hh = h + (kh - 1) * d;
+      xs[kh * Wp + d + w] = (hh >= 0 && hh < H) ? x[((static_cast<long long>(b) * Cin + ci) * H + hh) * W + w] : 0.f;
+    }
+    __syncthreads();
+    if (active) {
+#pragma unroll 8
+      for (int w = 0; w < W; ++w) acc = fmaf(a_row[w], b_row[w], acc);
+    }
+  }
+  if (active) part[((static_cast<long long>(sp) * Cout + co0 + o_co) * Cin + ci) * 9 + o_tap] = acc;
+}
+
+__global__ void wgrad_reduce_kernel(const float* __restrict__ part, float* __restrict__ dw, int nsplit, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double s = 0.0;
+  for (int k = 0; k < nsplit; ++k) s += part[static_cast<long long>(k) * n + i];
+  dw[i] = static_cast<float>(s);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// head: CrossEntropyLoss (mean) forward + gradient, Linear backward, mean-pool backward
+// ---------------------------------------------------------------------------------------------------------------------
+// One thread per clip: dlogits = (softmax - onehot) / B; rowloss[b] = logsumexp - logit[target] (NaN for a bad target).
+__global__ void ce_fwd_bwd_kernel(const float* __restrict__ logits, const long long* __restrict__ labels, float* __restrict__ dlogits,
+                                  float* __restrict__ rowloss, int B, int L) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const float* z = logits + static_cast<long long>(b) * L;
+  float mx = z[0];
+  for (int l = 1; l < L; ++l) mx = fmaxf(mx, z[l]);
+  float se = 0.f;
+  for (int l = 0; l < L; ++l) se += expf(z[l] - mx);
+  const float lse = mx + logf(se);
+  const long long t = labels[b];
+  const bool ok = t >= 0 && t < L;
+  rowloss[b] = ok ? lse - z[t] : __int_as_float(0x7fc00000);
+  const float inv = 1.f / static_cast<float>(B);
+  for (int l = 0; l < L; ++l) dlogits[static_cast<long long>(b) * L + l] = (expf(z[l] - lse) - ((ok && l == t) ? 1.f : 0.f)) * inv;
+}
+
+// One block: loss = mean(rowloss) in FP64, summed in index order.
+__global__ void loss_mean_kernel(const float* __restrict__ rowloss, float* __restrict__ loss, int B) {
+  __shared__ double sh[8];
+  double s = 0.0;
+  for (int i = threadIdx.x; i < B; i += blockDim.x) s += rowloss[i];
+  s = block_sum(s, sh);
+  if (threadIdx.x == 0) *loss = static_cast<float>(s / B);
+}
+
+// dW[l][c] = sum_b dlogits[b][l] * pooled[b][c];  db[l] = sum_b dlogits[b][l]   (one thread per (l, c); c == C is the bias)
+__global__ void linear_wgrad_kernel(const float* __restrict__ dlogits, const float* __restrict__ pooled, float* __restrict__ dW,
+                                    float* __restrict__ db, int B, int L, int C) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= L * (C + 1)) return;
+  const int l = i / (C + 1), c = i - l * (C + 1);
+  double s = 0.0;
+  for (int b = 0; b < B; ++b) s += static_cast<double>(dlogits[static_cast<long long>(b) * L + l]) * (c < C ? pooled[static_cast<long long>(b) * C + c] : 1.f);
+  if (c < C) dW[l * C + c] = static_cast<float>(s);
+  else db[l] = static_cast<float>(s);
+}
+
+// dx[b][c][:] = (sum_l dlogits[b][l] * W[l][c]) / HW     (gradient of mean over the map followed by the Linear layer)
+__global__ void head_dgrad_kernel(const float* __restrict__ dlogits, const float* __restrict__ Wout, float* __restrict__ dx, int L, int C, int HW) {
+  const long long bc = blockIdx.x;
+  const int c = static_cast<int>(bc % C);
+  const long long b = bc / C;
+  float s = 0.f;
+  for (int l = 0; l < L; ++l) s = fmaf(dlogits[b * L + l], Wout[l * C + c], s);
+  s /= static_cast<float>(HW);
+  for (int i = threadIdx.x; i < HW; i += blockDim.x) dx[bc * HW + i] = s;
+}
+
+// torch.optim.SGD.step (weight_decay, momentum with dampening 0, optional Nesterov); first == 1: momentum buffer = grad.
+__global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ mom, int n, float lr, float momentum,
+                           float weight_decay, int nesterov, int first) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float grad = g[i];
+  if (weight_decay != 0.f) grad = fmaf(weight_decay, p[i], grad);
+  if (momentum != 0.f) {
+    const float buf = first ? grad : fmaf(momentum, mom[i], grad);
+    mom[i] = buf;
+    grad = nesterov ? fmaf(momentum, buf, grad) : buf;
+  }
+  p[i] = p[i] - lr * grad;
+}
+
+inline int ew_blocks(long long n) { return static_cast<int>(std::min<long long>((n + 255) / 256, 148 * 16)); }
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------------------------------
+// handle
+// ---------------------------------------------------------------------------------------------------------------------
+struct TrainParam {
+  std::string name;
+  int64_t numel = 0;
+  float* p = nullptr;     // parameter
+  float* g = nullptr;     // gradient of the last step
+  float* mom = nullptr;   // SGD momentum buffer
+};
+
+struct honk_trainer {
+  honk_model_config cfg{};
+  int device = 0;
+  int H0 = 101, W0 = 40, Hr = 101, Wr = 40;
+  std::vector<TrainParam> params;            // conv0.weight, conv1.weight .. conv_n.weight, output.weight, output.bias
+  std::vector<float*> running_mean, running_var, bn_mean, bn_invstd;   // [n_layers] of [C]
+  float* bn_sums = nullptr;                  // [2C]
+  double* partial = nullptr;                 // [C][kStatSplit][2]
+  float* wflip = nullptr;                    // [C*C*9]
+  std::vector<void*> owned;
+  bool momentum_ready = false;               // false: the next step initialises the momentum buffers with the gradient
+  int64_t steps = 0;                         // num_batches_tracked of every BatchNorm layer
+  int64_t base_tracked = 0;
+};
+
+namespace {
+
+int t_alloc(honk_trainer* t, int64_t n_bytes, void** out) {
+  void* p = nullptr;
+  HONK_CUDA(cudaMalloc(&p, std::max<int64_t>(n_bytes, 4)));
+  t->owned.push_back(p);
+  HONK_CUDA(cudaMemset(p, 0, std::max<int64_t>(n_bytes, 4)));
+  *out = p;
+  return HONK_OK;
+}
+
+int t_dilation(const honk_model_config& c, int i) { return c.use_dilation ? (1 << ((i - 1) / 3)) : 1; }
+
+struct TrainWs {
+  float *y0 = nullptr, *stem = nullptr;      // relu(conv0) before the pool (pooled models) / conv1's input
+  std::vector<float*> y, x;                  // per layer: relu(conv_i), BatchNorm output
+  float* res[2] = {nullptr, nullptr};        // residual stream, ping-pong
+  float *pooled = nullptr, *logits = nullptr, *dlogits = nullptr, *rowloss = nullptr;
+  float *dx = nullptr, *dc = nullptr, *dold = nullptr, *wpart = nullptr;
+  int wsplit_main = 1, wsplit_stem = 1;
+};
+
+int wgrad_split(int Cin, int Cout, long long rows) {
+  const int chunks = ceil_div(Cout, WG_CO);
+  long long s = ceil_div(148 * 8, Cin * chunks);
+  s = std::max<long long>(1, std::min<long long>(s, std::min<long long>(rows, 1024)));
+  return static_cast<int>(s);
+}
+
+void carve(const honk_trainer* t, int64_t B, Arena& a, TrainWs& w) {
+  const honk_model_config& c = t->cfg;
+  const int C = c.n_feature_maps, n = c.n_layers;
+  const int64_t big = B * C * t->H0 * t->W0, map = B * C * t->Hr * t->Wr;
+  const bool pooled = c.res_pool[0] > 0;
+  if (pooled) w.y0 = a.take<float>(big);
+  w.stem = a.take<float>(map);
+  if (!pooled) w.y0 = w.stem;
+  w.y.resize(n);
+  w.x.resize(n);
+  for (int i = 0; i < n; ++i) {
+    w.y[i] = a.take<float>(map);
+    w.x[i] = a.take<float>(map);
+  }
+  w.res[0] = a.take<float>(map);
+  w.res[1] = a.take<float>(map);
+  w.pooled = a.take<float>(B * C);
+  w.logits = a.take<float>(B * c.n_labels);
+  w.dlogits = a.take<float>(B * c.n_labels);
+  w.rowloss = a.take<float>(B);
+  w.dx = a.take<float>(map);
+  w.dc = a.take<float>(big);
+  w.dold = a.take<float>(map);
+  w.wsplit_main = wgrad_split(C, C, B * t->Hr);
+  w.wsplit_stem = wgrad_split(1, C, B * t->H0);
+  w.wpart = a.take<float>(std::max<int64_t>(static_cast<int64_t>(w.wsplit_main) * C * C * 9, static_cast<int64_t>(w.wsplit_stem) * C * 9));
+}
+
+int wgrad(const float* x, const float* dy, float* part, float* dw, int B, int Cin, int Cout, int H, int W, int d, int nsplit, cudaStream_t s) {
+  const size_t smem = (static_cast<size_t>(WG_CO) * W + 3 * (W + 2 * d)) * sizeof(float);
+  HONK_CHECK(smem <= 48 * 1024, HONK_ERR_UNSUPPORTED, "training: map width %d too large for the weight-gradient kernel", W);
+  wgrad3x3_kernel<<<dim3(Cin, nsplit, ceil_div(Cout, WG_CO)), WG_THREADS, smem, s>>>(x, dy, part, B, Cin, Cout, H, W, d);
+  HONK_LAUNCH_CHECK();
+  const int n = Cout * Cin * 9;
+  wgrad_reduce_kernel<<<ceil_div(n, 256), 256, 0, s>>>(part, dw, nsplit, n);
+  HONK_LAUNCH_CHECK();
+  return HONK_OK;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------------------------------
+extern "C" int honk_trainer_create(const honk_model_config* cfg, const honk_tensor* tensors, int32_t n_tensors, int device,
+                                   honk_trainer** out) {
+  HONK_CHECK(cfg && out && tensors, HONK_ERR_INVALID, "honk_trainer_create: null argument");
+  HONK_CHECK(cfg->family == HONK_FAMILY_RES, HONK_ERR_UNSUPPORTED,
+             "honk_trainer_create: only the res* family trains on the GPU (the cnn-* models draw torch's dropout masks)");
+  // the strict state_dict check (names, shapes) is the model handle's: build one and take its validated host copy
+  honk_model* m = nullptr;
+  HONK_TRY(honk_model_create(cfg, tensors, n_tensors, device, &m));
+  std::unique_ptr<honk_model, int (*)(honk_model*)> guard(m, honk_model_destroy);
+  HONK_CUDA(cudaSetDevice(device));
+  std::unique_ptr<honk_trainer> t(new honk_trainer());
+  t->cfg = *cfg;
+  t->device = device;
+  t->H0 = m->H0; t->W0 = m->W0; t->Hr = m->Hr; t->Wr = m->Wr;
+  const int C = cfg->n_feature_maps, n = cfg->n_layers;
+  auto fail = [&](int rc) {
+    for (void* p : t->owned) cudaFree(p);
+    return rc;
+  };
+  auto add_param = [&](const std::string& name) -> int {
+    const HostTensor& h = m->host.at(name);
+    TrainParam p;
+    p.name = name;
+    p.numel = h.numel();
+    HONK_TRY(t_alloc(t.get(), p.numel * 4, reinterpret_cast<void**>(&p.p)));
+    HONK_TRY(t_alloc(t.get(), p.numel * 4, reinterpret_cast<void**>(&p.g)));
+    HONK_TRY(t_alloc(t.get(), p.numel * 4, reinterpret_cast<void**>(&p.mom)));
+    HONK_CUDA(cudaMemcpy(p.p, h.data.data(), p.numel * 4, cudaMemcpyHostToDevice));
+    t->params.push_back(p);
+    return HONK_OK;
+  };
+  int rc = add_param("conv0.weight");
+  for (int i = 1; rc == HONK_OK && i <= n; ++i) rc = add_param("conv" + std::to_string(i) + ".weight");
+  if (rc == HONK_OK) rc = add_param("output.weight");
+  if (rc == HONK_OK) rc = add_param("output.bias");
+  if (rc != HONK_OK) return fail(rc);
+  auto upload_stat = [&](const std::string& name, float** d) -> int {
+    const HostTensor& h = m->host.at(name);
+    HONK_TRY(t_alloc(t.get(), C * 4, reinterpret_cast<void**>(d)));
+    HONK_CUDA(cudaMemcpy(*d, h.data.data(), C * 4, cudaMemcpyHostToDevice));
+    return HONK_OK;
+  };
+  t->running_mean.resize(n); t->running_var.resize(n); t->bn_mean.resize(n); t->bn_invstd.resize(n);
+  for (int i = 0; rc == HONK_OK && i < n; ++i) {
+    const std::string s = "bn" + std::to_string(i + 1);
+    rc = upload_stat(s + ".running_mean", &t->running_mean[i]);
+    if (rc == HONK_OK) rc = upload_stat(s + ".running_var", &t->running_var[i]);
+    if (rc == HONK_OK) rc = t_alloc(t.get(), C * 4, reinterpret_cast<void**>(&t->bn_mean[i]));
+    if (rc == HONK_OK) rc = t_alloc(t.get(), C * 4, reinterpret_cast<void**>(&t->bn_invstd[i]));
+  }
+  if (rc == HONK_OK) rc = t_alloc(t.get(), 2 * C * 4, reinterpret_cast<void**>(&t->bn_sums));
+  if (rc == HONK_OK) rc = t_alloc(t.get(), static_cast<int64_t>(C) * kStatSplit * 2 * 8, reinterpret_cast<void**>(&t->partial));
+  if (rc == HONK_OK) rc = t_alloc(t.get(), static_cast<int64_t>(C) * C * 9 * 4, reinterpret_cast<void**>(&t->wflip));
+  if (rc != HONK_OK) return fail(rc);
+  *out = t.release();
+  return HONK_OK;
+}
+
+extern "C" int honk_trainer_destroy(honk_trainer* t) {
+  if (!t) return HONK_OK;
+  cudaSetDevice(t->device);
+  for (void* p : t->owned) cudaFree(p);
+  delete t;
+  return HONK_OK;
+}
+
+extern "C" int64_t honk_trainer_workspace_bytes(const honk_trainer* t, int64_t n_clips) {
+  if (!t || n_clips <= 0) return 0;
+  Arena a(nullptr, 0);
+  TrainWs w;
+  carve(t, n_clips, a, w);
+  return align_up(a.off, 256);
+}
+
+extern "C" int honk_trainer_reset_optimizer(honk_trainer* t) {
+  HONK_CHECK(t, HONK_ERR_INVALID, "honk_trainer_reset_optimizer: null handle");
+  t->momentum_ready = false;
+  return HONK_OK;
+}
+
+extern "C" int64_t honk_trainer_steps(const honk_trainer* t) { return t ? t->steps : 0; }
+
+// name: a state_dict key ("conv3.weight", "bn2.running_var", "output.bias"), or "grad:<parameter>" / "momentum:<parameter>".
+extern "C" int honk_trainer_read(const honk_trainer* t, const char* name, float* h_out, int64_t numel) {
+  HONK_CHECK(t && name && h_out, HONK_ERR_INVALID, "honk_trainer_read: null argument");
+  HONK_CUDA(cudaSetDevice(t->device));
+  std::string key(name);
+  int what = 0;
+  if (key.rfind("grad:", 0) == 0) { what = 1; key = key.substr(5); }
+  else if (key.rfind("momentum:", 0) == 0) { what = 2; key = key.substr(9); }
+  const float* src = nullptr;
+  int64_t n = 0;
+  for (const TrainParam& p : t->params)
+    if (p.name == key) { src = what == 0 ? p.p : what == 1 ? p.g : p.mom; n = p.numel; }
+  if (!src && what == 0) {
+    for (int i = 0; i < t->cfg.n_layers; ++i) {
+      const std::string s = "bn" + std::to_string(i + 1);
+      if (key == s + ".running_mean") { src = t->running_mean[i]; n = t->cfg.n_feature_maps; }
+      if (key == s + ".running_var") { src = t->running_var[i]; n = t->cfg.n_feature_maps; }
+    }
+  }
+  HONK_CHECK(src, HONK_ERR_INVALID, "honk_trainer_read: unknown tensor '%s'", name);
+  HONK_CHECK(n == numel, HONK_ERR_INVALID, "honk_trainer_read: '%s' has %lld elements, caller expects %lld", name,
+             static_cast<long long>(n), static_cast<long long>(numel));
+  HONK_CUDA(cudaDeviceSynchronize());
+  HONK_CUDA(cudaMemcpy(h_out, src, n * 4, cudaMemcpyDeviceToHost));
+  return HONK_OK;
+}
+
+// One optimisation step (train.py:127-139).  d_scores [n_clips, n_labels] receives the TRAINING-mode scores the reference
+// prints its "train step" accuracy from; d_loss one float, the mean CrossEntropyLoss.  Either may be nullptr.
+extern "C" int honk_trainer_step(honk_trainer* t, const float* d_mfcc, const int64_t* d_labels, int64_t n_clips, int32_t height,
+                                 int32_t width, const honk_sgd* opt, float* d_scores, float* d_loss, void* d_workspace,
+                                 int64_t workspace_bytes, void* stream) {
+  HONK_CHECK(t && d_mfcc && d_labels && opt, HONK_ERR_INVALID, "honk_trainer_step: null argument");
+  HONK_CHECK(height == t->H0 && width == t->W0, HONK_ERR_INVALID, "honk_trainer_step: clips are %d x %d, the model takes %d x %d",
+             height, width, t->H0, t->W0);
+  HONK_CHECK(n_clips >= 2 && n_clips <= 65536, HONK_ERR_INVALID,
+             "honk_trainer_step: batch of %lld clips (BatchNorm in training mode needs at least 2; at most 65536)",
+             static_cast<long long>(n_clips));
+  HONK_CHECK(opt->momentum >= 0.f && opt->weight_decay >= 0.f && (!opt->nesterov || opt->momentum > 0.f), HONK_ERR_INVALID,
+             "honk_trainer_step: bad SGD settings (Nesterov needs a momentum)");
+  HONK_CUDA(cudaSetDevice(t->device));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const honk_model_config& c = t->cfg;
+  const int B = static_cast<int>(n_clips), C = c.n_feature_maps, n = c.n_layers, L = c.n_labels;
+  const int H0 = t->H0, W0 = t->W0, Hr = t->Hr, Wr = t->Wr, HW = Hr * Wr;
+  const bool pooled = c.res_pool[0] > 0;
+  Arena a(d_workspace, workspace_bytes);
+  TrainWs w;
+  carve(t, n_clips, a, w);
+  HONK_CHECK(d_workspace && a.ok(), HONK_ERR_WORKSPACE, "honk_trainer_step: workspace of %lld bytes, %lld needed",
+             static_cast<long long>(workspace_bytes), static_cast<long long>(align_up(a.off, 256)));
+  const long long map = static_cast<long long>(B) * C * HW, big = static_cast<long long>(B) * C * H0 * W0;
+  const long long count = static_cast<long long>(B) * HW;
+  TrainParam& P0 = t->params[0];
+  TrainParam& Pw = t->params[n + 1];
+  TrainParam& Pb = t->params[n + 2];
+
+  // ---- forward, training mode -----------------------------------------------------------------------------------
+  {
+    ProfSpan sp("train_fwd", s);
+    ConvGeom g0{B, 1, H0, W0, C, 3, 3, 1, 1, 1, 1, 1, 1, 0, 0};
+    conv_out_dims(g0);
+    HONK_TRY(conv2d_f32(d_mfcc, P0.p, nullptr, w.y0, g0, true, s));
+    if (pooled) HONK_TRY(pool2d_f32(w.y0, w.stem, B * C, H0, W0, c.res_pool[0], c.res_pool[1], false, s));
+    const float* cur = w.stem;
+    const float* old = w.stem;
+    int flip = 0;
+    for (int i = 1; i <= n; ++i) {
+      const int d = t_dilation(c, i);
+      ConvGeom gi{B, C, Hr, Wr, C, 3, 3, 1, 1, d, d, d, d, 0, 0};
+      conv_out_dims(gi);
+      HONK_TRY(conv2d_f32(cur, t->params[i].p, nullptr, w.y[i - 1], gi, true, s));
+      const float* r = w.y[i - 1];
+      if (i % 2 == 0) {
+        add_f32_kernel<<<ew_blocks(map), 256, 0, s>>>(w.y[i - 1], old, w.res[flip], map);
+        HONK_LAUNCH_CHECK();
+        r = old = w.res[flip];
+        flip ^= 1;
+      }
+      chan_sums_kernel<<<dim3(C, kStatSplit), 256, 0, s>>>(r, nullptr, t->partial, B, C, HW);
+      HONK_LAUNCH_CHECK();
+      bn_train_finalize_kernel<<<ceil_div(C, 128), 128, 0, s>>>(t->partial, kStatSplit, count, t->bn_mean[i - 1], t->bn_invstd[i - 1],
+                                                               t->running_mean[i - 1], t->running_var[i - 1], C);
+      HONK_LAUNCH_CHECK();
+      bn_apply_kernel<<<ew_blocks(map), 256, 0, s>>>(r, t->bn_mean[i - 1], t->bn_invstd[i - 1], w.x[i - 1], C, HW, map);
+      HONK_LAUNCH_CHECK();
+      cur = w.x[i - 1];
+    }
+    HONK_TRY(mean_hw_f32(cur, w.pooled, B * C, HW, s));
+    ConvGeom gl{B, C, 1, 1, L, 1, 1, 1, 1, 0, 0, 1, 1, 1, 1};
+    HONK_TRY(conv2d_f32(w.pooled, Pw.p, Pb.p, w.logits, gl, false, s));
+    ce_fwd_bwd_kernel<<<ceil_div(B, 128), 128, 0, s>>>(w.logits, reinterpret_cast<const long long*>(d_labels), w.dlogits, w.rowloss, B, L);
+    HONK_LAUNCH_CHECK();
+    if (d_loss) {
+      loss_mean_kernel<<<1, 256, 0, s>>>(w.rowloss, d_loss, B);
+      HONK_LAUNCH_CHECK();
+    }
+    if (d_scores) HONK_CUDA(cudaMemcpyAsync(d_scores, w.logits, static_cast<size_t>(B) * L * 4, cudaMemcpyDeviceToDevice, s));
+  }
+
+  // ---- backward -------------------------------------------------------------------------------------------------
+  {
+    ProfSpan sp("train_bwd", s);
+    linear_wgrad_kernel<<<ceil_div(L * (C + 1), 128), 128, 0, s>>>(w.dlogits, w.pooled, Pw.g, Pb.g, B, L, C);
+    HONK_LAUNCH_CHECK();
+    head_dgrad_kernel<<<B * C, 128, 0, s>>>(w.dlogits, Pw.p, w.dx, L, C, HW);
+    HONK_LAUNCH_CHECK();
+    bool have_dold = false;
+    for (int i = n; i >= 1; --i) {
+      const int d = t_dilation(c, i);
+      const float* xin = i == 1 ? w.stem : w.x[i - 2];
+      chan_sums_kernel<<<dim3(C, kStatSplit), 256, 0, s>>>(w.dx, w.x[i - 1], t->partial, B, C, HW);
+      HONK_LAUNCH_CHECK();
+      bn_bwd_finalize_kernel<<<ceil_div(C, 128), 128, 0, s>>>(t->partial, kStatSplit, count, t->bn_sums, C);
+      HONK_LAUNCH_CHECK();
+      const bool even = i % 2 == 0;
+      bn_relu_bwd_kernel<<<ew_blocks(map), 256, 0, s>>>(w.dx, w.x[i - 1], w.y[i - 1], t->bn_sums, t->bn_invstd[i - 1],
+                                                       (even && have_dold) ? w.dold : nullptr, even ? w.dold : nullptr, w.dc, C, HW, map);
+      HONK_LAUNCH_CHECK();
+      if (even) have_dold = true;
+      HONK_TRY(wgrad(xin, w.dc, w.wpart, t->params[i].g, B, C, C, Hr, Wr, d, w.wsplit_main, s));
+      flip_weights_kernel<<<ceil_div(C * C * 9, 256), 256, 0, s>>>(t->params[i].p, t->wflip, C, C);
+      HONK_LAUNCH_CHECK();
+      ConvGeom gi{B, C, Hr, Wr, C, 3, 3, 1, 1, d, d, d, d, 0, 0};
+      conv_out_dims(gi);
+      HONK_TRY(conv2d_f32(w.dc, t->wflip, nullptr, w.dx, gi, false, s));   // dx now holds the gradient at conv_i's input
+    }
+    stem_bwd_kernel<<<ew_blocks(big), 256, 0, s>>>(w.dx, have_dold ? w.dold : nullptr, w.y0, w.dc, H0, W0, pooled ? c.res_pool[0] : 1,
+                                                  pooled ? c.res_pool[1] : 1, Hr, Wr, big);
+    HONK_LAUNCH_CHECK();
+    HONK_TRY(wgrad(d_mfcc, w.dc, w.wpart, P0.g, B, 1, C, H0, W0, 1, w.wsplit_stem, s));
+  }
+
+  // ---- torch.optim.SGD.step ---------------------------------------------------------------------------------------
+  {
+    ProfSpan sp("train_sgd", s);
+    const int first = t->momentum_ready ? 0 : 1;
+    for (TrainParam& p : t->params) {
+      sgd_kernel<<<ceil_div(static_cast<int>(p.numel), 256), 256, 0, s>>>(p.p, p.g, p.mom, static_cast<int>(p.numel), opt->lr, opt->momentum,
+                                                                         opt->weight_decay, opt->nesterov, first);
+      HONK_LAUNCH_CHECK();
+    }
+    if (opt->momentum != 0.f) t->momentum_ready = true;
+  }
+  t->steps += 1;
+  return HONK_OK;
+}

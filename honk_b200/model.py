@@ -99,6 +99,21 @@ def _pair(v):
     return (int(v[0]), int(v[1]))
 
 
+def native_tensors(sd):
+    """``honk_tensor[]`` over host copies of a state_dict; returns ``(host tensors to keep alive, ctypes array)``."""
+    keep, arr = [], (N.Tensor * len(sd))()
+    for i, (name, t) in enumerate(sd.items()):
+        h = t.detach().to("cpu")
+        h = h.to(torch.float32).contiguous() if h.is_floating_point() else h.to(torch.int64).contiguous()
+        keep.append(h)
+        arr[i].name = name.encode()
+        arr[i].h_data = h.data_ptr()
+        arr[i].ndim = h.dim()
+        for d in range(h.dim()):
+            arr[i].dims[d] = h.shape[d]
+    return keep, arr
+
+
 class SerializableModule(nn.Module):
     """``save`` / ``load`` with the reference's bare-state_dict format (model.py:72-80)."""
 
@@ -170,16 +185,7 @@ class SerializableModule(nn.Module):
         cfg = self._native_config()
         cfg.precision = int(self.precision)
         sd = self.state_dict()
-        keep, arr = [], (N.Tensor * len(sd))()
-        for i, (name, t) in enumerate(sd.items()):
-            h = t.detach().to("cpu")
-            h = h.to(torch.float32).contiguous() if h.is_floating_point() else h.to(torch.int64).contiguous()
-            keep.append(h)
-            arr[i].name = name.encode()
-            arr[i].h_data = h.data_ptr()
-            arr[i].ndim = h.dim()
-            for d in range(h.dim()):
-                arr[i].dims[d] = h.shape[d]
+        keep, arr = native_tensors(sd)
         handle = C.c_void_p()
         N.check(N.lib().honk_model_create(C.byref(cfg), arr, len(sd), device.index or 0, C.byref(handle)))
         self._native = handle.value

@@ -237,6 +237,45 @@ HONK_API int honk_load_audio(const float* d_pcm, int64_t n_clips, int64_t clip_s
                     const int32_t* d_shifts, const float* d_noise_gain, const int64_t* d_noise_offset,
                     const float* d_bg_noise, int32_t input_length, float* d_out, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Training step of the res* family (replaces the body of the reference's
+ * training loop, utils/train.py:127-139: model.train(), scores = model(model_in), CrossEntropyLoss,
+ * loss.backward(), torch.optim.SGD.step()).  FP32 on the CUDA cores; BatchNorm2d(affine=False) in
+ * training mode (batch statistics, running statistics moved by momentum 0.1; utils/model.py:98).
+ * The cnn-* family is refused with HONK_ERR_UNSUPPORTED: its nn.Dropout draws torch's random masks
+ * (utils/model.py:139, 191-200), which no other implementation can reproduce.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct honk_trainer honk_trainer;
+
+/* The arguments of torch.optim.SGD as train.py:100 passes them (dampening 0). */
+typedef struct honk_sgd {
+  float lr, momentum, weight_decay;
+  int32_t nesterov;
+} honk_sgd;
+
+/* Same strict state_dict check as honk_model_create; the trainer owns device copies of the parameters,
+ * their gradients, the momentum buffers and the BatchNorm running statistics. */
+HONK_API int honk_trainer_create(const honk_model_config* cfg, const honk_tensor* tensors, int32_t n_tensors, int device,
+                                 honk_trainer** out);
+HONK_API int honk_trainer_destroy(honk_trainer* t);
+/* Scratch bytes of one step on n_clips clips (the activations of every layer are kept for the backward pass). */
+HONK_API int64_t honk_trainer_workspace_bytes(const honk_trainer* t, int64_t n_clips);
+/* One step on d_mfcc float32 [n_clips, height, width] with d_labels int64 [n_clips] (2 <= n_clips <= 65536).
+ * d_scores float32 [n_clips, n_labels] receives the training-mode scores (what train.py:132 hands to print_eval),
+ * d_loss one float32, the mean CrossEntropyLoss of the batch BEFORE the update (train.py:134); either may be NULL.
+ * A label outside [0, n_labels) makes the loss NaN (the reference raises IndexError; the Python host checks first). */
+HONK_API int honk_trainer_step(honk_trainer* t, const float* d_mfcc, const int64_t* d_labels, int64_t n_clips, int32_t height,
+                               int32_t width, const honk_sgd* opt, float* d_scores, float* d_loss, void* d_workspace,
+                               int64_t workspace_bytes, void* stream);
+/* train.py:141-143 builds a NEW torch.optim.SGD when the learning-rate schedule advances, which drops the momentum
+ * buffers; this does the same (the next step initialises them with its gradient). */
+HONK_API int honk_trainer_reset_optimizer(honk_trainer* t);
+/* Steps taken by this handle (what every bn<i>.num_batches_tracked has advanced by). */
+HONK_API int64_t honk_trainer_steps(const honk_trainer* t);
+/* Copies one tensor to the host (synchronises the device): a state_dict key ("conv3.weight", "bn2.running_var",
+ * "output.bias"), or "grad:<parameter>" / "momentum:<parameter>" for the last step's gradient / the SGD buffer. */
+HONK_API int honk_trainer_read(const honk_trainer* t, const char* name, float* h_out, int64_t numel);
+
 /* Number of kernels the library has launched in this process (for bench.py's gpu_launches). */
 HONK_API int64_t honk_launch_count(void);
 

@@ -272,6 +272,81 @@ def res_forward(state, config, x, dtype=None):
     return F.linear(x, _t(state["output.weight"], dtype), _t(state["output.bias"], dtype))
 
 
+def res_train_logits(params, stats, config, x, momentum=0.1, eps=1e-5):
+    """``SpeechResModel.forward`` in TRAINING mode (utils/model.py:104-121 after ``model.train()``, train.py:128):
+    ``nn.BatchNorm2d(n_maps, affine=False)`` (model.py:98) normalises with the batch mean / biased variance and moves
+    ``stats`` (running_mean / running_var torch tensors, updated IN PLACE) by ``momentum`` towards the batch mean /
+    unbiased variance.  ``params``: torch tensors (leaf, requires_grad) under the reference's key names."""
+    import torch.nn.functional as F
+    x = x.unsqueeze(1)
+    dil = bool(config["use_dilation"])
+    old_x = None
+    for i in range(config["n_layers"] + 1):
+        d = 1 if (i == 0 or not dil) else int(2 ** ((i - 1) // 3))
+        y = F.relu(F.conv2d(x, params["conv%d.weight" % i], None, 1, d, d))
+        if i == 0:
+            if "res_pool" in config:
+                y = F.avg_pool2d(y, tuple(config["res_pool"]))
+            old_x = y
+        if i > 0 and i % 2 == 0:
+            x = y + old_x
+            old_x = x
+        else:
+            x = y
+        if i > 0:
+            x = F.batch_norm(x, stats["bn%d.running_mean" % i], stats["bn%d.running_var" % i], None, None, True, momentum, eps)
+    x = x.reshape(x.size(0), x.size(1), -1).mean(2)
+    return F.linear(x, params["output.weight"], params["output.bias"])
+
+
+def sgd_train_steps(state, config, batches, lr=0.001, momentum=0.9, weight_decay=0.00001, nesterov=False, dtype=None):
+    """The reference's inner training loop (utils/train.py:127-139) for a res* model, restated without nn.Module /
+    torch.optim: forward in training mode, mean CrossEntropyLoss (train.py:104), autograd for the gradients, then the
+    update rule of ``torch.optim.SGD`` (dampening 0): g += wd * p; buf = g on the first step, else momentum * buf + g;
+    g = g + momentum * buf (Nesterov) or buf; p -= lr * g.
+
+    ``state``: numpy state_dict; ``batches``: list of ``(mfcc [B, T, F], labels [B])``.  Returns a dict with the final
+    ``state`` (numpy, num_batches_tracked advanced), per-step ``losses``, ``scores`` and ``grads`` (list of dicts)."""
+    import torch
+    import torch.nn.functional as F
+    dtype = dtype or torch.float32
+    params, stats, tracked = {}, {}, {}
+    for k, v in state.items():
+        if k.endswith("num_batches_tracked"):
+            tracked[k] = int(np.asarray(v))
+        elif "running_" in k:
+            stats[k] = _t(v, dtype).clone()
+        else:
+            params[k] = _t(v, dtype).clone().requires_grad_()
+    bufs = {}
+    losses, scores, grads = [], [], []
+    for x, y in batches:
+        for p in params.values():
+            p.grad = None
+        logits = res_train_logits(params, stats, config, _t(x, dtype))
+        loss = F.cross_entropy(logits, torch.as_tensor(np.asarray(y), dtype=torch.int64))
+        loss.backward()
+        losses.append(float(loss.detach()))
+        scores.append(logits.detach().numpy().copy())
+        grads.append({k: p.grad.detach().numpy().copy() for k, p in params.items()})
+        with torch.no_grad():
+            for k, p in params.items():
+                g = p.grad
+                if weight_decay != 0:
+                    g = g + weight_decay * p
+                if momentum != 0:
+                    bufs[k] = g.clone() if k not in bufs else bufs[k] * momentum + g
+                    g = g + momentum * bufs[k] if nesterov else bufs[k]
+                p -= lr * g
+        for k in tracked:
+            tracked[k] += 1
+    out = {k: v.detach().numpy().copy() for k, v in params.items()}
+    out.update({k: v.numpy().copy() for k, v in stats.items()})
+    out.update({k: np.asarray(v, dtype=np.int64) for k, v in tracked.items()})
+    return {"state": out, "losses": losses, "scores": scores, "grads": grads,
+            "momentum": {k: v.numpy().copy() for k, v in bufs.items()}}
+
+
 def cnn_forward(state, config, x, dtype=None):
     """``SpeechModel.forward`` in eval mode (utils/model.py:186-205); dropout is identity."""
     import torch

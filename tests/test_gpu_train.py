@@ -20,11 +20,40 @@ def make_model(name, cfg, state):
     return model.cuda()
 
 
+def rel_err(a, truth):
+    return float(np.abs(np.asarray(a, np.float64) - truth).max() / max(np.abs(truth).max(), 1e-30))
+
+
+def float32_noise(c, truth, trials=6):
+    """How far float32 arithmetic itself may land from the float64 result on this case: the float32 oracle on inputs and
+    weights perturbed by about one ulp (6e-8 relative, seeded), worst relative error over the gradient tensors of step 0
+    and over the final state.  The outcome is bimodal - ~4e-6 when no ReLU changes side, ~1.7e-3 when one activation
+    within an ulp of zero does (res26-narrow, batch 8) - which is why a fixed small tolerance cannot be the bar."""
+    lr, mom, wd, nest = c["hyper"]
+    rng = np.random.default_rng(123)
+    g_noise = max(rel_err(v, truth["grads"][0][k]) for k, v in c["grad0"].items())          # the reference's own run
+    s_noise = max(rel_err(v, truth["state"][k]) for k, v in c["final"].items() if not k.endswith("num_batches_tracked"))
+    for _ in range(trials):
+        init = {k: (v * (1 + 6e-8 * rng.standard_normal(v.shape))).astype(np.float32) if k.endswith("weight") else v
+                for k, v in c["init"].items()}
+        batches = [((x * (1 + 6e-8 * rng.standard_normal(x.shape))).astype(np.float32), y) for x, y in c["batches"]]
+        o = orc.sgd_train_steps(init, c["config"], batches, lr=lr, momentum=mom, weight_decay=wd, nesterov=bool(nest))
+        g_noise = max(g_noise, max(rel_err(o["grads"][0][k], t) for k, t in truth["grads"][0].items()))
+        s_noise = max(s_noise, max(rel_err(o["state"][k], t) for k, t in truth["state"].items() if not k.endswith("num_batches_tracked")))
+    return g_noise, s_noise
+
+
 @pytest.mark.parametrize("name", CASES)
 def test_three_steps_match_the_reference_run(golden_dir, name):
+    """Loss and scores against the reference's float32 run directly.  Gradients and the final state are judged against
+    the float64 oracle with float32's own noise on the case as the yardstick (float32_noise): every tensor must be within
+    2 x that noise + 2e-4 - about 2e-4 for the well-conditioned res8 cases, which is where an arithmetic slip shows."""
     from honk_b200 import train
     c = load_case(golden_dir, name)
     lr, mom, wd, nest = c["hyper"]
+    truth = orc.sgd_train_steps(c["init"], c["config"], c["batches"], lr=lr, momentum=mom, weight_decay=wd, nesterov=bool(nest),
+                                dtype=torch.float64)
+    g_noise, s_noise = float32_noise(c, truth)
     model = make_model(name, c["config"], c["init"])
     tr = train.SgdTrainer(model, lr=lr, momentum=mom, weight_decay=wd, nesterov=bool(nest))
     for s, (x, y) in enumerate(c["batches"]):
@@ -33,9 +62,9 @@ def test_three_steps_match_the_reference_run(golden_dir, name):
         ref = c["scores"][s]
         assert np.abs(scores.cpu().numpy() - ref).max() <= 1e-3 * np.abs(ref).max() + 1e-4, s
         if s == 0:
-            for k, v in c["grad0"].items():
-                g = tr.read("grad:" + k)
-                assert np.abs(g - v).max() <= 1e-3 * np.abs(v).max() + 1e-7, (k, np.abs(g - v).max(), np.abs(v).max())
+            for k in c["grad0"]:
+                e_gpu = rel_err(tr.read("grad:" + k), truth["grads"][0][k])
+                assert e_gpu <= 2 * g_noise + 2e-4, (k, e_gpu, g_noise)
     assert tr.steps == len(c["batches"])
     tr.sync()
     sd = model.state_dict()
@@ -44,7 +73,8 @@ def test_three_steps_match_the_reference_run(golden_dir, name):
         if k.endswith("num_batches_tracked"):
             assert int(got) == int(v)
         else:
-            assert np.allclose(got, v, atol=2e-4, rtol=1e-3), (k, np.abs(got - v).max())
+            e_gpu = rel_err(got, truth["state"][k])
+            assert e_gpu <= 2 * s_noise + 2e-4, (k, e_gpu, s_noise)
     # the synced module serves inference with the trained weights (eval mode, running statistics)
     model.eval()
     model.precision = 1
@@ -68,24 +98,30 @@ def test_batch64_against_oracle_and_schedule_reset():
     model = make_model("res15-narrow", cfg, state)
     tr = train.SgdTrainer(model, lr=0.05, momentum=0.9, weight_decay=1e-5)
     batches = [(mfcc[i * 64:(i + 1) * 64].cpu().numpy(), labels[i * 64:(i + 1) * 64].astype(np.int64)) for i in range(4)]
-    o1 = orc.sgd_train_steps(state, cfg, batches[:2], lr=0.05, momentum=0.9, weight_decay=1e-5)
-    o2 = orc.sgd_train_steps(o1["state"], cfg, batches[2:], lr=0.01, momentum=0.9, weight_decay=1e-5)   # new SGD: no buffers
+    def run(dtype):
+        o1 = orc.sgd_train_steps(state, cfg, batches[:2], lr=0.05, momentum=0.9, weight_decay=1e-5, dtype=dtype)
+        o2 = orc.sgd_train_steps(o1["state"], cfg, batches[2:], lr=0.01, momentum=0.9, weight_decay=1e-5, dtype=dtype)   # new SGD: no buffers
+        return o1["losses"] + o2["losses"], o2
+    ref_losses, ref = run(torch.float32)
+    true_losses, truth = run(torch.float64)
     losses = []
     for i, (x, y) in enumerate(batches):
         if i == 2:
             tr.new_optimizer(0.01)
         _, loss = tr.step(torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda())
         losses.append(float(loss))
-    assert np.allclose(losses, o1["losses"] + o2["losses"], atol=2e-4), (losses, o1["losses"] + o2["losses"])
-    for k, v in o2["momentum"].items():
-        assert np.abs(tr.read("momentum:" + k) - v).max() <= 2e-3 * np.abs(v).max() + 1e-7, k
+    assert np.allclose(losses, true_losses, atol=2e-4), (losses, true_losses)
+    e_ref = max(rel_err(ref["momentum"][k], t) for k, t in truth["momentum"].items())
+    for k, t in truth["momentum"].items():
+        assert rel_err(tr.read("momentum:" + k), t) <= 5 * e_ref + 2e-4, (k, e_ref)
     tr.sync()
-    for k, v in o2["state"].items():
+    e_ref = max(rel_err(ref["state"][k], t) for k, t in truth["state"].items() if not k.endswith("num_batches_tracked"))
+    for k, t in truth["state"].items():
         got = model.state_dict()[k].cpu().numpy()
         if k.endswith("num_batches_tracked"):
-            assert int(got) == int(v) == 104
+            assert int(got) == int(t) == 104
         else:
-            assert np.allclose(got, v, atol=3e-4, rtol=2e-3), (k, np.abs(got - v).max())
+            assert rel_err(got, t) <= 5 * e_ref + 2e-4, (k, rel_err(got, t), e_ref)
 
 
 def test_training_loss_falls_and_train_loop_runs(tmp_path, capsys):

@@ -967,6 +967,307 @@ __global__ void __launch_bounds__(256) tc2_conv0_pool_mma_kernel(const float* __
   }
 }
 
+// Pooled models, default pre-pass since r04: conv0 + ReLU + AvgPool on tcgen05.  One CTA walks groups of S clips; per clip
+//   * 4 builder warps turn the MFCCs into conv0's operand image in shared memory (double-buffered): per coefficient
+//     plane w and row r a 16-byte unit (x_hi, x_lo, x_hi, 0, x'_hi, x'_lo, x'_hi, 0) of frames r and r' = r + 1, with zero
+//     frames above and below the clip;
+//   * one warp issues ONE M128 x N(3 NB) x K16 MMA per INPUT column c: the A descriptor's second K chunk sits two rows
+//     (32 bytes) after the first, so the chunks carry the time taps kh = (0, 1) and (2, -), and the three coefficient taps kw
+//     are stacked along N against B = (w_hi, w_hi, w_lo) per tap: block kw lands on OUTPUT column c - (kw - 1).  Output
+//     columns sit in adjacent NB-column blocks of a ring of three TMEM buffers (one per pooled column = pw outputs), so the
+//     three contributions to an output add up inside the accumulator ("ring accumulate", as in tc2_res_kernel); an MMA
+//     that would straddle the ring's end is issued in two pieces;
+//   * 8 epilogue warps (two per TMEM lane quarter, half the channels each) read a finished buffer, hand it back ZEROED
+//     (every MMA accumulates), apply the ReLU per conv position, add the pw columns, add the ph time rows with a
+//     halving exchange of lane shuffles and store f16 into the persistent kernel's stacked input image y0 (same bytes as
+//     tc2_conv0_pool_mma_kernel writes, zero units included).
+// x*w is (x_hi + x_lo)*w_hi + x_hi*w_lo with FP32 accumulation, like both other conv0 formulations.
+constexpr int T2C0_NI = 1;            // MMA-issuing warps (more than one makes the accumulation order, hence the last bit, vary run to run)
+constexpr int T2C0_E0 = T2C0_NI + 4;  // first epilogue warp (T2C0_E0 % 4 may be anything: the TMEM lane quarter is warp % 4)
+#ifndef T2C0_NSET
+#define T2C0_NSET 1
+#endif
+constexpr int T2C0_THREADS = (T2C0_E0 + 8 * T2C0_NSET) * 32;   // issuer, 4 builders, T2C0_NSET sets of 8 epilogue warps (alternate pooled columns)
+constexpr int T2C0_PADROWS = 32;      // rows past the last plane that the 128-row A tiles (+3 rows of taps) may read
+constexpr int T2C0_NBUF = 3;
+constexpr int T2C0_W0 = 40;           // MFCC coefficients per frame (compile-time)
+constexpr int T2C0_TAIL = 2 * 3 * 48 * 16 + 256;   // B tile (largest NB) + barriers + TMEM slot, after the two images
+
+
+// One of the T2C0_NI issuing warps of tc2_conv0_pool_tc_kernel: input columns c with c % T2C0_NI == WI.  Pooled column j of
+// every clip uses ring buffer j % 3, so the per-column schedule (which outputs an input column touches, where they sit in
+// TMEM, which buffer this warp touches first / last) unrolls into constants.  A warp waits for a buffer before ITS first MMA
+// into it and commits to the buffer's "full" barrier after ITS last one (the barrier counts T2C0_NI arrivals).
+template <int NCG, int PW, int WI>
+__device__ __forceinline__ void c0_issue(int n_groups, int n_clips, int S, int Hi, uint32_t img_a, int img_bytes, uint32_t wt_a,
+                                         uint32_t tmem_base, uint32_t b_img_full, uint32_t b_img_empty, uint32_t b_grp_full,
+                                         uint32_t b_grp_empty, int mode) {
+  constexpr int NB = NCG * 8, W0 = T2C0_W0, Wc = W0 / PW, n_out = Wc * PW, BUF = PW * NB, NI = T2C0_NI;
+  uint32_t n = 0, uses[T2C0_NBUF] = {0, 0, 0};                   // clips started; uses of each ring buffer so far
+  uint64_t bdesc[3];
+#pragma unroll
+  for (int blk = 0; blk < 3; ++blk) bdesc[blk] = make_desc(wt_a + blk * NB * 16, 3 * NB * 16, 128);
+  for (int g = blockIdx.x; g < n_groups; g += gridDim.x) {
+    const int n_here = min(S, n_clips - g * S);
+    for (int sc = 0; sc < n_here; ++sc, ++n) {
+      const uint32_t ib = n & 1;
+      mbar_wait(b_img_full + 8 * ib, (n >> 1) & 1);
+      fence_after();
+      const uint64_t a_base = make_desc(img_a + ib * img_bytes, 32, 128);
+      const uint32_t plane16 = static_cast<uint32_t>(Hi);         // plane stride in 16-byte units
+#pragma unroll
+      for (int c = WI; c < W0; c += NI) {
+        const int o_lo = c - 1 < 0 ? 0 : c - 1, o_hi = c + 1 > n_out - 1 ? n_out - 1 : c + 1;
+        if (o_lo > o_hi) continue;
+        const int g_lo = o_lo / PW, g_hi = o_hi / PW;
+        // this warp's first MMA into a pooled column's buffer: it must have been drained (and zeroed) by the epilogue.  The
+        // inputs of pooled column gg are columns max(0, gg*PW - 1) .. min(W0 - 1, gg*PW + PW).
+#pragma unroll
+        for (int gg = g_lo; gg <= g_hi; ++gg) {
+          const int first_in = gg * PW - 1 < 0 ? 0 : gg * PW - 1;
+          const int mine = first_in + ((WI - first_in) % NI + NI) % NI;                  // first column >= first_in of this warp
+          if (c == mine) {
+            mbar_wait(b_grp_empty + 8 * (gg % T2C0_NBUF), (uses[gg % T2C0_NBUF] & 1) ^ 1);
+            ++uses[gg % T2C0_NBUF];
+            fence_after();
+          }
+        }
+        if (elect_one()) {
+          const uint64_t adesc = a_base + static_cast<uint64_t>(c * plane16);
+          const int b_lo = g_lo % T2C0_NBUF, b_hi = g_hi % T2C0_NBUF;
+          const int split = (g_lo != g_hi && b_hi != b_lo + 1) ? g_hi * PW : o_hi + 1;    // first output of the second piece
+#pragma unroll
+          for (int piece = 0; piece < 2; ++piece) {
+            const int oa = piece == 0 ? o_lo : split, ob = piece == 0 ? (o_hi < split - 1 ? o_hi : split - 1) : o_hi;
+            if (oa > ob || (mode & 4)) continue;
+            const int ga = oa / PW;
+            mma_f16_ss(tmem_base + (ga % T2C0_NBUF) * BUF + (oa - ga * PW) * NB, adesc, bdesc[oa - (c - 1)],
+                       make_idesc(128, (ob - oa + 1) * NB, 0), 1);
+          }
+          // this warp's last MMA into a pooled column's buffer
+#pragma unroll
+          for (int gg = g_lo; gg <= g_hi; ++gg) {
+            const int last_in = gg == Wc - 1 ? (W0 - 1 < n_out ? W0 - 1 : n_out) : gg * PW + PW;
+            const int mine = last_in - ((last_in - WI) % NI + NI) % NI;                  // last column <= last_in of this warp
+            if (c == mine) commit(b_grp_full + 8 * (gg % T2C0_NBUF));
+          }
+          if (c + NI >= W0) commit(b_img_empty + 8 * ib);          // this warp's last column: its reads of the image are done
+        }
+        __syncwarp();
+      }
+    }
+  }
+}
+
+template <int NCG, int PW>
+__global__ void __launch_bounds__(T2C0_THREADS, 1) tc2_conv0_pool_tc_kernel(const float* __restrict__ mfcc, const unsigned char* __restrict__ wt,
+                                                                            unsigned char* __restrict__ y0, int n_clips, int H0, int ph,
+                                                                            int Hc, int S, int plane_rows, long long slot_stride,
+                                                                            int img_bytes, int mode) {
+  constexpr int W0 = T2C0_W0, pw = PW, Wc = W0 / PW;
+  // mode (HONK_TC2_C0_MODE, timing experiments only - results are garbage): bit 0 builders skip their loads and stores,
+  // bit 1 the epilogue skips its pooling and stores, bit 2 the issuer skips the MMAs, bit 3 no zeroing of y0's pad units
+  constexpr int NB = NCG * 8, HB = NB / 2, TILE = 2 * 3 * NB * 16;
+  extern __shared__ __align__(128) unsigned char c0_smem[];
+  unsigned char* wts = c0_smem + 2 * img_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(wts + TILE);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4 + 2 * T2C0_NBUF);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int Hi = H0 + 2, plane_bytes = Hi * 16, HW = H0 * W0;
+  const uint32_t img_a = smem_u32(c0_smem), wt_a = smem_u32(wts);
+  const uint32_t b_img_full = smem_u32(bars + 0), b_img_empty = smem_u32(bars + 2), b_grp_full = smem_u32(bars + 4),
+                 b_grp_empty = smem_u32(bars + 4 + T2C0_NBUF);
+  for (int i = tid; i < 2 * img_bytes / 16; i += T2C0_THREADS) reinterpret_cast<uint4*>(c0_smem)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = tid; i < TILE / 16; i += T2C0_THREADS) reinterpret_cast<uint4*>(wts)[i] = __ldg(reinterpret_cast<const uint4*>(wt) + i);
+  if (tid == 0) {
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(b_img_full + 8 * b, 128);
+      mbar_init(b_img_empty + 8 * b, T2C0_NI);
+    }
+    for (int b = 0; b < T2C0_NBUF; ++b) {
+      mbar_init(b_grp_full + 8 * b, T2C0_NI);
+      mbar_init(b_grp_empty + 8 * b, 8);
+    }
+    fence_mbar_init();
+  }
+  fence_async_smem();
+  if (warp == 0) tmem_alloc(smem_u32(tmem_slot), 512);
+  fence_before();
+  __syncthreads();
+  fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  static_assert(Wc * PW >= W0 - 1 && PW >= 2 && T2C0_NBUF * PW * NB <= 512, "schedule assumes every input column feeds an output");
+  const int n_groups = (n_clips + S - 1) / S, Hp1 = Hc + 1;
+  constexpr int buf_cols = PW * NB;
+  if (warp >= T2C0_E0) {                                        // all accumulators start at zero: every MMA accumulates
+    const int lq = warp & 3, ch = ((warp - T2C0_E0) & 7) >> 2;
+    for (int i = 0; i < T2C0_NBUF * PW; ++i)
+      tmem_zero_cols<HB>(tmem_base + (static_cast<uint32_t>(lq * 32) << 16) + i * NB + ch * HB);
+    tmem_st_wait();
+  }
+  fence_before();
+  __syncthreads();
+  fence_after();
+
+  if (warp < T2C0_NI) {
+    // ---- MMA issuers: T2C0_NI warps take alternate input columns (all MMAs accumulate, so their order does not matter) ------
+    if (T2C0_NI == 1 || warp == 0)
+      c0_issue<NCG, PW, 0>(n_groups, n_clips, S, Hi, img_a, img_bytes, wt_a, tmem_base, b_img_full, b_img_empty, b_grp_full, b_grp_empty, mode);
+    else
+      c0_issue<NCG, PW, T2C0_NI - 1>(n_groups, n_clips, S, Hi, img_a, img_bytes, wt_a, tmem_base, b_img_full, b_img_empty, b_grp_full, b_grp_empty, mode);
+  } else if (warp < T2C0_NI + 4) {
+    // ---- operand-image builders (and the zero units of the group's output buffer) -----------------------------------
+    const int bt = tid - 32 * T2C0_NI;
+    uint32_t n = 0;
+    for (int g = blockIdx.x; g < n_groups; g += gridDim.x) {
+      const int n_here = min(S, n_clips - g * S);
+      if (!(mode & 8)) {
+        // zero units of the group's buffer: rows that are not a real position of a present clip (same test for every plane,
+        // made once per lane for its rows lane, lane + 32, ...), and the slot's tail
+        const int Hk = S * Hp1 - 1, bw = warp - T2C0_NI;
+        uint4* dst = reinterpret_cast<uint4*>(y0 + static_cast<long long>(g) * slot_stride);
+        const int n_units16 = static_cast<int>(slot_stride / 16), n_planes = Wc * NCG;
+        uint32_t zero_rows = 0;
+        for (int k = 0; k * 32 + lane < plane_rows; ++k) {
+          const int hk = k * 32 + lane - T2_PAD;
+          bool real = false;
+          if (hk >= 0 && hk < Hk) {
+            const int sc = hk / Hp1;
+            real = (hk - sc * Hp1) < Hc && sc < n_here;
+          }
+          if (!real) zero_rows |= 1u << k;
+        }
+        for (int pl = bw; pl < n_planes; pl += 4)
+          for (int k = 0; k * 32 + lane < plane_rows; ++k)
+            if ((zero_rows >> k) & 1) dst[pl * plane_rows + k * 32 + lane] = make_uint4(0, 0, 0, 0);
+        for (int i = n_planes * plane_rows + bt; i < n_units16; i += 128) dst[i] = make_uint4(0, 0, 0, 0);
+      }
+      for (int sc = 0; sc < n_here; ++sc, ++n) {
+        const uint32_t ib = n & 1;
+        const float* src = mfcc + (static_cast<long long>(g) * S + sc) * HW;
+        unsigned char* img = c0_smem + ib * img_bytes;
+        bool waited = false;
+        if (mode & 1) {
+          mbar_wait(b_img_empty + 8 * ib, ((n >> 1) & 1) ^ 1);
+          waited = true;
+        }
+        for (int e0 = bt; e0 < HW && !(mode & 1); e0 += 128 * 16) {
+          float v[16];
+#pragma unroll
+          for (int u = 0; u < 16; ++u) v[u] = (e0 + u * 128 < HW) ? __ldg(src + e0 + u * 128) : 0.f;
+          if (!waited) {                                         // the loads are in flight while the buffer drains
+            mbar_wait(b_img_empty + 8 * ib, ((n >> 1) & 1) ^ 1);
+            waited = true;
+          }
+#pragma unroll
+          for (int u = 0; u < 16; ++u) {
+            const int e = e0 + u * 128;
+            if (e < HW) {
+              const int h = e / W0, w = e - h * W0;
+              const float x = fminf(fmaxf(v[u], -60000.f), 60000.f);                 // stays finite in f16
+              const __half hi = __float2half_rn(x);
+              const __half lo = __float2half_rn(x - __half2float(hi));
+              const uint32_t uh = __half_as_ushort(hi), ul = __half_as_ushort(lo);
+              const uint2 val = make_uint2(uh | (ul << 16), uh);
+              unsigned char* unit = img + (w * Hi + h + 1) * 16;                     // frame h is image row h + 1
+              *reinterpret_cast<uint2*>(unit) = val;                                 // as frame r of its own row
+              *reinterpret_cast<uint2*>(unit - 16 + 8) = val;                        // as frame r + 1 of the row above
+            }
+          }
+        }
+        fence_async_smem();
+        mbar_arrive(b_img_full + 8 * ib);
+      }
+    }
+  } else {
+    // ---- epilogue: ReLU per conv position, sum of the pool window, f16 store ---------------------------------------------
+    // Two sets of 8 warps take alternate pooled columns.  A warp owns one TMEM lane quarter (32 frames) and half the channels:
+    // it adds relu() of the PW conv columns per frame, hands the buffer back zeroed, then pools ph frames through a private
+    // shared-memory tile (row stride HB + 4 floats: conflict-free 16-byte stores) - lane l sums the ph rows of cell l / nq for
+    // its share l % nq of the channels and stores them.
+    const int ew = (warp - T2C0_E0) & 7, set = (warp - T2C0_E0) >> 3, lq = warp & 3, ch = ew >> 2;   // TMEM lane quarter = warp id % 4
+    constexpr int TS = HB + 4;                                   // tile row stride in floats
+    float* tile = reinterpret_cast<float*>(c0_smem + 2 * img_bytes + T2C0_TAIL) + (warp - T2C0_E0) * 32 * TS;
+    // pooling role of this lane (ph = 4: 8 cells x 4 channel quarters; ph = 2: 16 cells x 2 channel halves)
+    const int nq = ph == 4 ? 4 : 2, cell = lane / nq, part = lane - cell * nq, PC = HB / nq;      // PC channels per lane
+    const int hp = (lq * 32) / ph + cell;
+    const bool row_ok = hp < Hc && (ph == 4 || ph == 2);
+    const float inv = 1.f / static_cast<float>(ph * PW);
+    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(lq * 32) << 16) + ch * HB;
+    const int chn0 = ch * HB + part * PC;                        // first channel this lane stores
+    uint32_t uses[T2C0_NBUF] = {0, 0, 0}, turn = 0;
+    for (int g = blockIdx.x; g < n_groups; g += gridDim.x) {
+      const int n_here = min(S, n_clips - g * S);
+      for (int sc = 0; sc < n_here; ++sc) {
+        // this lane's first 4-byte store of pooled column 0: unit (j * NCG + chn / 8) * plane_rows + T2_PAD + sc * Hp1 + hp
+        unsigned char* out = y0 + static_cast<long long>(g) * slot_stride + (static_cast<long long>(T2_PAD + sc * Hp1 + hp)) * 16;
+#pragma unroll 3
+        for (int j = 0; j < Wc; ++j, ++turn) {
+          const uint32_t b = j % T2C0_NBUF;
+          const uint32_t phase = (b == 0 ? uses[0] : (b == 1 ? uses[1] : uses[2])) & 1;
+          if (b == 0) ++uses[0]; else if (b == 1) ++uses[1]; else ++uses[2];
+          if (T2C0_NSET > 1 && (turn % T2C0_NSET) != static_cast<uint32_t>(set)) continue;      // another set's pooled column
+          mbar_wait(b_grp_full + 8 * b, phase);
+          fence_after();
+          const uint32_t taddr = t_lane + b * buf_cols;
+          float acc[HB];
+          uint32_t v[PW][HB];
+#pragma unroll
+          for (int c = 0; c < PW; ++c) tmem_ld_cols<HB>(taddr + c * NB, v[c]);
+          tmem_ld_wait();
+#pragma unroll
+          for (int c = 0; c < PW; ++c) tmem_zero_cols<HB>(taddr + c * NB);
+#pragma unroll
+          for (int k = 0; k < HB; ++k) {
+            float a = fmaxf(__uint_as_float(v[0][k]), 0.f);
+#pragma unroll
+            for (int c = 1; c < PW; ++c) a += fmaxf(__uint_as_float(v[c][k]), 0.f);
+            acc[k] = a;
+          }
+          tmem_st_wait();
+          fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(b_grp_empty + 8 * b);           // the buffer goes back zeroed: every MMA accumulates
+          if (mode & 2) continue;
+#pragma unroll
+          for (int k = 0; k < HB; k += 4) *reinterpret_cast<float4*>(tile + lane * TS + k) = make_float4(acc[k], acc[k + 1], acc[k + 2], acc[k + 3]);
+          __syncwarp();
+          if (row_ok) {
+            const float* src = tile + cell * ph * TS + part * PC;
+            if (ph == 4) {
+#pragma unroll
+              for (int k = 0; k < HB / 4; k += 2) {
+                const float2 r0 = *reinterpret_cast<const float2*>(src + k), r1 = *reinterpret_cast<const float2*>(src + TS + k),
+                             r2 = *reinterpret_cast<const float2*>(src + 2 * TS + k), r3 = *reinterpret_cast<const float2*>(src + 3 * TS + k);
+                const int chn = chn0 + k;
+                uint32_t o = pack_h2(((r0.x + r1.x) + (r2.x + r3.x)) * inv, ((r0.y + r1.y) + (r2.y + r3.y)) * inv);
+                if (chn >= NB - 2) o = 0x3C003C00u;                                  // the two constant-one channels
+                *reinterpret_cast<uint32_t*>(out + (static_cast<long long>(j * NCG + (chn >> 3)) * plane_rows) * 16 + (chn & 7) * 2) = o;
+              }
+            } else {
+#pragma unroll
+              for (int k = 0; k < HB / 2; k += 2) {
+                const float2 r0 = *reinterpret_cast<const float2*>(src + k), r1 = *reinterpret_cast<const float2*>(src + TS + k);
+                const int chn = chn0 + k;
+                uint32_t o = pack_h2((r0.x + r1.x) * inv, (r0.y + r1.y) * inv);
+                if (chn >= NB - 2) o = 0x3C003C00u;
+                *reinterpret_cast<uint32_t*>(out + (static_cast<long long>(j * NCG + (chn >> 3)) * plane_rows) * 16 + (chn & 7) * 2) = o;
+              }
+            }
+          }
+          __syncwarp();                                              // the tile is free for this warp's next pooled column
+        }
+      }
+    }
+  }
+  fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
 // Zeroes exactly the 16-byte units of the activation arena that no layer ever stores and that must read as zero: the
 // T2_PAD rows above every channel plane (time padding), the S - 1 separator rows of a stacked group, and each slot's tail.
 __global__ void __launch_bounds__(256) tc2_zero_pads_kernel(unsigned char* __restrict__ act, long long slot_stride, int n_slots2,
@@ -1018,6 +1319,9 @@ struct ResTc2Plan {
   float* d_w0 = nullptr;          // pooled models: conv0 weights [9][NB] float (FP32 variant of the conv0 + pool pre-pass)
   uint32_t* d_w0b = nullptr;      // pooled models: conv0 weights as mma.sync B pairs [NB][16] (tc2_conv0_pool_mma_kernel)
   bool conv0_f32 = false;         // HONK_TC2_CONV0_F32=1: FP32 CUDA-core pre-pass instead of the tensor-core one
+  __half* d_w0t = nullptr;        // pooled models: conv0 weights as six tcgen05 B tiles [kw][kh pair | kh 2][2 K chunks][NB][8 halves]
+  bool conv0_tc = false;          // tcgen05 pre-pass (tc2_conv0_pool_tc_kernel); HONK_TC2_CONV0_MMA=1 keeps the mma.sync one
+  int c0_img_bytes = 0, c0_smem = 0;
   int K = 2;                      // clips per team in flight: 37 teams x 2 x 2 buffers x 449 KB = 66 MB of L2 (K = 3: 100 MB starts
                                   // evicting dirty activations to HBM, and the extra DRAM power costs SM clock under the power cap)
   std::vector<T2Layer> layers;    // [0] = conv0, [1..n_layers] = the C->C layers
@@ -1192,6 +1496,35 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
       for (int mm = 9; mm < 14; ++mm) wb[co * 16 + mm] = static_cast<uint32_t>(lo[2 * (mm - 9)]) | (static_cast<uint32_t>(lo[2 * (mm - 9) + 1]) << 16);
     }
     HONK_TRY(up(p.get(), wb, &p->d_w0b));
+    {
+      // tcgen05 formulation: ONE B tile [K chunk][row = blk * NB + co][8 halves], blk <-> kw = 2 - blk (block blk of input
+      // column c lands on output column c - 1 + blk); chunk 0 = time taps kh 0 | 1, chunk 1 = kh 2 | none; a tap's four
+      // halves are (w_hi, w_hi, w_lo, 0) against the operand image's (x_hi, x_lo, x_hi, 0)
+      std::vector<__half> wt6(static_cast<size_t>(2) * 3 * N * 8, __float2half(0.f));
+      for (int chunk = 0; chunk < 2; ++chunk)
+        for (int half = 0; half < 2; ++half) {
+          const int kh = chunk * 2 + half;
+          if (kh > 2) continue;
+          for (int blk = 0; blk < 3; ++blk) {
+            const int kw = 2 - blk;
+            for (int co = 0; co < C; ++co) {
+              const float v = w.data[co * 9 + kh * 3 + kw];
+              const __half hi = __float2half(v);
+              const __half lo = __float2half(v - __half2float(hi));
+              __half* row = wt6.data() + ((static_cast<size_t>(chunk) * 3 * N) + blk * N + co) * 8 + half * 4;
+              row[0] = hi;
+              row[1] = hi;
+              row[2] = lo;
+            }
+          }
+        }
+      HONK_TRY(up(p.get(), wt6, &p->d_w0t));
+      p->c0_img_bytes = static_cast<int>(align_up((static_cast<int64_t>(p->W0) * (p->H0 + 2) + T2C0_PADROWS) * 16, 128));
+      p->c0_smem = 2 * p->c0_img_bytes + T2C0_TAIL + 8 * T2C0_NSET * 32 * (N / 2 + 4) * 4;
+      const bool pow2 = (p->pool_h & (p->pool_h - 1)) == 0;
+      p->conv0_tc = (p->pool_h == 2 || p->pool_h == 4) && (p->pool_w == 2 || p->pool_w == 3) && p->W0 == T2C0_W0 && p->W == p->W0 / p->pool_w && p->H0 <= 126 && p->c0_smem + 1024 <= max_smem &&
+                    m->Hr * p->pool_h <= 128 && !(getenv("HONK_TC2_CONV0_MMA") && atoi(getenv("HONK_TC2_CONV0_MMA")) != 0);
+    }
     if (const char* e = getenv("HONK_TC2_CONV0_F32")) p->conv0_f32 = atoi(e) != 0;
   } else {
     // conv0 (bias-free, model.py:107): B tile kh = [K half][n = blk*NB + co][8]; input channels 0..2 = (x_hi, x_lo, x_hi)
@@ -1285,6 +1618,12 @@ int res_tc2_plan_create(honk_model* m, ResTc2Plan** out) {
     const int sm0 = S * (p->H0 + 2) * (p->W0 + 2) * static_cast<int>(sizeof(float));
     if (sm0 + 1024 > max_smem) return HONK_OK;
     HONK_TRY(set_smem(tc2_conv0_pool_mma_kernel<6>, sm0));
+    if (p->conv0_tc) {
+      HONK_TRY(set_smem(tc2_conv0_pool_tc_kernel<6, 3>, p->c0_smem));
+      HONK_TRY(set_smem(tc2_conv0_pool_tc_kernel<4, 3>, p->c0_smem));
+      HONK_TRY(set_smem(tc2_conv0_pool_tc_kernel<6, 2>, p->c0_smem));
+      HONK_TRY(set_smem(tc2_conv0_pool_tc_kernel<4, 2>, p->c0_smem));
+    }
     HONK_TRY(set_smem(tc2_conv0_pool_mma_kernel<4>, sm0));
     HONK_TRY(set_smem(tc2_conv0_pool_kernel<6, 4, 3>, sm0));
     HONK_TRY(set_smem(tc2_conv0_pool_kernel<4, 4, 3>, sm0));
@@ -1396,7 +1735,20 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
   tc2_conv0_pool_kernel<NCG_, PH_, PW_><<<grid, NCG_ * 64, smem, s>>>(d_mfcc, p->d_w0, x0, static_cast<int>(n_clips), p->H0, p->W0, \
                                                                       p->pool_h, p->pool_w, p->Hc, p->W, p->S, p->plane_rows, p->slot_stride)
     const int pk = (p->pool_h == 4 && p->pool_w == 3) ? 1 : ((p->pool_h == 2 && p->pool_w == 2) ? 2 : 0);
-    if (!p->conv0_f32) {
+    if (!p->conv0_f32 && p->conv0_tc) {
+      const dim3 gtc(static_cast<unsigned>(std::min<long long>(n_groups, p->n_sms)));
+      static const int c0_mode = getenv("HONK_TC2_C0_MODE") ? atoi(getenv("HONK_TC2_C0_MODE")) : 0;
+#define T2_C0TC(NCG_, PW_)                                                                                                          \
+  tc2_conv0_pool_tc_kernel<NCG_, PW_><<<gtc, T2C0_THREADS, p->c0_smem, s>>>(d_mfcc, reinterpret_cast<const unsigned char*>(p->d_w0t), x0, \
+                                                                           static_cast<int>(n_clips), p->H0, p->pool_h, p->Hc, p->S,      \
+                                                                           p->plane_rows, p->slot_stride, p->c0_img_bytes, c0_mode)
+      if (p->ncg == 6) {
+        if (p->pool_w == 3) T2_C0TC(6, 3); else T2_C0TC(6, 2);
+      } else {
+        if (p->pool_w == 3) T2_C0TC(4, 3); else T2_C0TC(4, 2);
+      }
+#undef T2_C0TC
+    } else if (!p->conv0_f32) {
       if (p->ncg == 6)
         tc2_conv0_pool_mma_kernel<6><<<grid, 256, smem, s>>>(d_mfcc, p->d_w0b, x0, static_cast<int>(n_clips), p->H0, p->W0, p->pool_h,
                                                              p->pool_w, p->Hc, p->W, p->S, p->plane_rows, p->slot_stride);

@@ -151,51 +151,102 @@ __global__ void flip_weights_kernel(const float* __restrict__ w, float* __restri
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// weight gradient of a 3x3 stride-1 convolution with pad == dilation == d:
-//   dw[co][ci][kh][kw] = sum_{b,h,w} dy[b][co][h][w] * x[b][ci][h + (kh-1)d][w + (kw-1)d]
-// grid (Cin, nsplit, co-chunks of WG_CO); one thread per (co, tap) of the chunk; the block walks its share of the B*H
-// rows, staging dy[b][chunk][h][:] and the three x rows (zero-padded by d on both sides) in shared memory.
-// Partials go to part[split][co][ci][9]; wgrad_reduce_kernel adds them in a fixed order (deterministic).
+// weight gradient of a 3x3 stride-1 convolution with pad == dilation == d, as a split-K FP32 GEMM:
+//   dw[co][ci*9 + tap] = sum_pos dy[b][co][pos] * x[b][ci][h + (kh-1)d][w + (kw-1)d],   pos = (b, h, w)
+// M = Cout (tile BM), N = Cin * 9 (tile 64), K = B*H*W positions, BK = 16 per stage.  grid (N tiles, splits, M tiles);
+// each block reduces its contiguous share of the positions; partials go to part[split][co][ci*9 + tap] and
+// wgrad_reduce_kernel adds them in a fixed order (deterministic).  Both operands are read with the position as the
+// fastest index across a half-warp, i.e. 64-byte segments along w.
 // ---------------------------------------------------------------------------------------------------------------------
-constexpr int WG_CO = 28, WG_THREADS = 256;
+constexpr int WG_BN = 64, WG_BK = 16, WG_THREADS = 256;
 
-__global__ void __launch_bounds__(WG_THREADS) wgrad3x3_kernel(const float* __restrict__ x, const float* __restrict__ dy,
-                                                              float* __restrict__ part, int B, int Cin, int Cout, int H, int W, int d) {
-  extern __shared__ float wg_smem[];
-  const int Wp = W + 2 * d;
-  float* dys = wg_smem;                 // [WG_CO][W]
-  float* xs = wg_smem + WG_CO * W;      // [3][Wp]
-  const int ci = blockIdx.x, sp = blockIdx.y, co0 = blockIdx.z * WG_CO;
-  const int nco = min(WG_CO, Cout - co0);
+template <int BM>
+__global__ void __launch_bounds__(WG_THREADS) wgrad_gemm_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                                                                float* __restrict__ part, int B, int Cin, int Cout, int H, int W, int d,
+                                                                long long k_per_split) {
+  constexpr int TM = BM / 16, TN = 4, LA = BM / 16;            // LA: A loads per thread per stage
+  __shared__ float As[WG_BK][BM + 4];
+  __shared__ float Bs[WG_BK][WG_BN + 4];
   const int tid = threadIdx.x;
-  const long long rows = static_cast<long long>(B) * H;
-  const long long per = (rows + gridDim.y - 1) / gridDim.y;
-  const long long r0 = sp * per, r1 = min(rows, r0 + per);
-  const int o_co = tid / 9, o_tap = tid - o_co * 9;
-  const bool active = o_co < nco;
-  const float* a_row = dys + o_co * W;
-  const float* b_row = xs + (o_tap / 3) * Wp + (o_tap % 3) * d;
-  for (int i = tid; i < 3 * Wp; i += WG_THREADS) xs[i] = 0.f;   // the side pads stay zero from here on
-  float acc = 0.f;
-  for (long long r = r0; r < r1; ++r) {
-    const int b = static_cast<int>(r / H), h = static_cast<int>(r - static_cast<long long>(b) * H);
-    __syncthreads();
-    for (int i = tid; i < nco * W; i += WG_THREADS) {
-      const int co = i / W, w = i - co * W;
-      dys[i] = dy[((static_cast<long long>(b) * Cout + co0 + co) * H + h) * W + w];
-    }
-    for (int i = tid; i < 3 * W; i += WG_THREADS) {
-      const int kh = i / W, w = i - kh * W;
-      const int hh = h + (kh - 1) * d;
-      xs[kh * Wp + d + w] = (hh >= 0 && hh < H) ? x[((static_cast<long long>(b) * Cin + ci) * H + hh) * W + w] : 0.f;
-    }
-    __syncthreads();
-    if (active) {
-#pragma unroll 8
-      for (int w = 0; w < W; ++w) acc = fmaf(a_row[w], b_row[w], acc);
+  const int HW = H * W, N = Cin * 9;
+  const long long K = static_cast<long long>(B) * HW;
+  const int n0 = blockIdx.x * WG_BN, m0 = blockIdx.z * BM, sp = blockIdx.y;
+  const long long k_lo = sp * k_per_split, k_hi = min(K, k_lo + k_per_split);
+  // load roles: position kk = tid % 16 of the stage; rows tid / 16 + 16 * i of the tile
+  const int kk = tid & 15, row = tid >> 4;
+  // this thread's position (b, h, w), advanced by 16 per stage
+  long long pos = k_lo + kk;
+  int b = static_cast<int>(pos / HW);
+  int rem = static_cast<int>(pos - static_cast<long long>(b) * HW);
+  int h = rem / W, w = rem - h * W;
+  // B-operand columns of this thread: (ci, dh, dw) for n = n0 + row + 16 * i
+  int b_ci[4], b_dh[4], b_dw[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int n = n0 + row + 16 * i;
+    if (n < N) {
+      const int ci = n / 9, tap = n - ci * 9;
+      b_ci[i] = ci;
+      b_dh[i] = (tap / 3 - 1) * d;
+      b_dw[i] = (tap % 3 - 1) * d;
+    } else {
+      b_ci[i] = -1; b_dh[i] = 0; b_dw[i] = 0;
     }
   }
-  if (active) part[((static_cast<long long>(sp) * Cout + co0 + o_co) * Cin + ci) * 9 + o_tap] = acc;
+  const int tm = (tid & 15) * TM, tn = (tid >> 4) * TN;
+  float acc[TM][TN];
+#pragma unroll
+  for (int i = 0; i < TM; ++i)
+#pragma unroll
+    for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+
+  for (long long k0 = k_lo; k0 < k_hi; k0 += WG_BK) {
+    const bool k_ok = k0 + kk < k_hi;
+    float av[LA], bv[4];
+#pragma unroll
+    for (int i = 0; i < LA; ++i) {
+      const int m = m0 + row + 16 * i;
+      av[i] = (k_ok && m < Cout) ? __ldg(dy + (static_cast<long long>(b) * Cout + m) * HW + h * W + w) : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int hh = h + b_dh[i], ww = w + b_dw[i];
+      bv[i] = (k_ok && b_ci[i] >= 0 && hh >= 0 && hh < H && ww >= 0 && ww < W)
+                  ? __ldg(x + (static_cast<long long>(b) * Cin + b_ci[i]) * HW + hh * W + ww) : 0.f;
+    }
+    __syncthreads();                       // the previous stage's reads are done
+#pragma unroll
+    for (int i = 0; i < LA; ++i) As[kk][row + 16 * i] = av[i];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) Bs[kk][row + 16 * i] = bv[i];
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < WG_BK; ++q) {
+      float a[TM], bb[TN];
+#pragma unroll
+      for (int i = 0; i < TM; ++i) a[i] = As[q][tm + i];
+#pragma unroll
+      for (int j = 0; j < TN; ++j) bb[j] = Bs[q][tn + j];
+#pragma unroll
+      for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], bb[j], acc[i][j]);
+    }
+    // advance this thread's position by one stage
+    w += WG_BK;
+    while (w >= W) { w -= W; ++h; }
+    while (h >= H) { h -= H; ++b; }
+  }
+#pragma unroll
+  for (int i = 0; i < TM; ++i) {
+    const int m = m0 + tm + i;
+    if (m >= Cout) continue;
+#pragma unroll
+    for (int j = 0; j < TN; ++j) {
+      const int n = n0 + tn + j;
+      if (n < N) part[(static_cast<long long>(sp) * Cout + m) * N + n] = acc[i][j];
+    }
+  }
 }
 
 __global__ void wgrad_reduce_kernel(const float* __restrict__ part, float* __restrict__ dw, int nsplit, int n) {
@@ -326,10 +377,12 @@ struct TrainWs {
   int wsplit_main = 1, wsplit_stem = 1;
 };
 
-int wgrad_split(int Cin, int Cout, long long rows) {
-  const int chunks = ceil_div(Cout, WG_CO);
-  long long s = ceil_div(148 * 8, Cin * chunks);
-  s = std::max<long long>(1, std::min<long long>(s, std::min<long long>(rows, 1024)));
+int wgrad_bm(int Cout) { return Cout <= 32 ? 32 : 64; }
+
+int wgrad_split(int Cin, int Cout, long long K) {
+  const int tiles = ceil_div(Cin * 9, WG_BN) * ceil_div(Cout, wgrad_bm(Cout));
+  long long s = ceil_div(148 * 6, tiles);
+  s = std::max<long long>(1, std::min<long long>(s, std::min<long long>((K + 255) / 256, 1024)));
   return static_cast<int>(s);
 }
 
@@ -356,15 +409,18 @@ void carve(const honk_trainer* t, int64_t B, Arena& a, TrainWs& w) {
   w.dx = a.take<float>(map);
   w.dc = a.take<float>(big);
   w.dold = a.take<float>(map);
-  w.wsplit_main = wgrad_split(C, C, B * t->Hr);
-  w.wsplit_stem = wgrad_split(1, C, B * t->H0);
+  w.wsplit_main = wgrad_split(C, C, B * t->Hr * t->Wr);
+  w.wsplit_stem = wgrad_split(1, C, B * t->H0 * t->W0);
   w.wpart = a.take<float>(std::max<int64_t>(static_cast<int64_t>(w.wsplit_main) * C * C * 9, static_cast<int64_t>(w.wsplit_stem) * C * 9));
 }
 
 int wgrad(const float* x, const float* dy, float* part, float* dw, int B, int Cin, int Cout, int H, int W, int d, int nsplit, cudaStream_t s) {
-  const size_t smem = (static_cast<size_t>(WG_CO) * W + 3 * (W + 2 * d)) * sizeof(float);
-  HONK_CHECK(smem <= 48 * 1024, HONK_ERR_UNSUPPORTED, "training: map width %d too large for the weight-gradient kernel", W);
-  wgrad3x3_kernel<<<dim3(Cin, nsplit, ceil_div(Cout, WG_CO)), WG_THREADS, smem, s>>>(x, dy, part, B, Cin, Cout, H, W, d);
+  const long long K = static_cast<long long>(B) * H * W;
+  const long long per = align_up((K + nsplit - 1) / nsplit, WG_BK);
+  const int bm = wgrad_bm(Cout);
+  const dim3 grid(ceil_div(Cin * 9, WG_BN), nsplit, ceil_div(Cout, bm));
+  if (bm == 32) wgrad_gemm_kernel<32><<<grid, WG_THREADS, 0, s>>>(x, dy, part, B, Cin, Cout, H, W, d, per);
+  else wgrad_gemm_kernel<64><<<grid, WG_THREADS, 0, s>>>(x, dy, part, B, Cin, Cout, H, W, d, per);
   HONK_LAUNCH_CHECK();
   const int n = Cout * Cin * 9;
   wgrad_reduce_kernel<<<ceil_div(n, 256), 256, 0, s>>>(part, dw, nsplit, n);

@@ -26,7 +26,8 @@ EXPORTS = [
     "honk_label_from_logits", "honk_eval_metrics", "honk_load_audio", "honk_listen", "honk_listen_num_windows", "honk_listen_workspace_bytes", "honk_launch_count", "honk_model_path", "honk_profile_enable",
     "honk_profile_reset", "honk_profile_get",
     "honk_trainer_create", "honk_trainer_destroy", "honk_trainer_workspace_bytes", "honk_trainer_step",
-    "honk_trainer_reset_optimizer", "honk_trainer_steps", "honk_trainer_read",
+    "honk_trainer_reset_optimizer", "honk_trainer_steps", "honk_trainer_read", "honk_trainer_set_dropout",
+    "honk_trainer_set_dropout_masks",
 ]
 
 
@@ -121,6 +122,8 @@ def lib():
         L.honk_trainer_steps.argtypes = [vp]
         L.honk_trainer_steps.restype = i64
         L.honk_trainer_read.argtypes = [vp, C.c_char_p, vp, i64]
+        L.honk_trainer_set_dropout.argtypes = [vp, C.c_float, C.c_uint64]
+        L.honk_trainer_set_dropout_masks.argtypes = [vp, C.POINTER(vp), i32]
         if L.honk_abi_version() != 2:
             raise RuntimeError("honk_b200: ABI version mismatch")
         _lib = L

@@ -1,5 +1,6 @@
-// One SGD training step of the res* family on the GPU (reference: utils/train.py:127-139 - model.train(), forward,
-// CrossEntropyLoss, backward, torch.optim.SGD.step - over SpeechResModel, utils/model.py:82-121).
+// One SGD training step on the GPU (reference: utils/train.py:127-139 - model.train(), forward, CrossEntropyLoss, backward,
+// torch.optim.SGD.step) over SpeechResModel (utils/model.py:82-121) and SpeechModel (utils/model.py:123-205; second half of
+// this file: conv + bias + ReLU -> Dropout -> MaxPool, Linear layers with Dropout).
 //
 // All arithmetic is FP32 on the CUDA cores (reductions accumulate in FP64) so that the step agrees with the reference's
 // FP32 autograd to summation-order noise; nothing here calls a library.  The step is, per layer i = 1..n,
@@ -140,21 +141,21 @@ __global__ void stem_bwd_kernel(const float* __restrict__ da, const float* __res
   }
 }
 
-// wt[ci][co][kh][kw] = w[co][ci][2-kh][2-kw]: the data gradient of a 3x3 stride-1 convolution with pad == dilation is
-// the same convolution of dy with these weights.
-__global__ void flip_weights_kernel(const float* __restrict__ w, float* __restrict__ wt, int Cout, int Cin) {
-  const int n = Cout * Cin * 9;
+// wt[ci][co][KH-1-kh][KW-1-kw] = w[co][ci][kh][kw]: the data gradient of a stride-1 convolution is the same kind of
+// convolution of dy with these weights (pad' = dilation * (K - 1) - pad, which equals pad for the res* layers).
+__global__ void flip_weights_kernel(const float* __restrict__ w, float* __restrict__ wt, int Cout, int Cin, int KHW) {
+  const int n = Cout * Cin * KHW;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const int tap = i % 9, ci = (i / 9) % Cin, co = i / (9 * Cin);
-    wt[(ci * Cout + co) * 9 + (8 - tap)] = w[i];
+    const int tap = i % KHW, ci = (i / KHW) % Cin, co = i / (KHW * Cin);
+    wt[(ci * Cout + co) * KHW + (KHW - 1 - tap)] = w[i];
   }
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// weight gradient of a 3x3 stride-1 convolution with pad == dilation == d, as a split-K FP32 GEMM:
-//   dw[co][ci*9 + tap] = sum_pos dy[b][co][pos] * x[b][ci][h + (kh-1)d][w + (kw-1)d],   pos = (b, h, w)
-// M = Cout (tile BM), N = Cin * 9 (tile 64), K = B*H*W positions, BK = 16 per stage.  grid (N tiles, splits, M tiles);
-// each block reduces its contiguous share of the positions; partials go to part[split][co][ci*9 + tap] and
+// weight gradient of a convolution (any kernel size, stride, padding, dilation) as a split-K FP32 GEMM:
+//   dw[co][(ci, kh, kw)] = sum_pos dy[b][co][ho][wo] * x[b][ci][ho*sh - ph + kh*dh][wo*sw - pw + kw*dw],   pos = (b, ho, wo)
+// M = Cout (tile BM), N = Cin*KH*KW (tile 64), K = B*Ho*Wo output positions, BK = 16 per stage.  grid (N tiles, splits,
+// M tiles); each block reduces its contiguous share of the positions; partials go to part[split][co][n] and
 // wgrad_reduce_kernel adds them in a fixed order (deterministic).  Both operands are read with the position as the
 // fastest index across a half-warp, i.e. 64-byte segments along w.
 // ---------------------------------------------------------------------------------------------------------------------
@@ -162,33 +163,32 @@ constexpr int WG_BN = 64, WG_BK = 16, WG_THREADS = 256;
 
 template <int BM>
 __global__ void __launch_bounds__(WG_THREADS) wgrad_gemm_kernel(const float* __restrict__ x, const float* __restrict__ dy,
-                                                                float* __restrict__ part, int B, int Cin, int Cout, int H, int W, int d,
-                                                                long long k_per_split) {
+                                                                float* __restrict__ part, ConvGeom g, long long k_per_split) {
   constexpr int TM = BM / 16, TN = 4, LA = BM / 16;            // LA: A loads per thread per stage
   __shared__ float As[WG_BK][BM + 4];
   __shared__ float Bs[WG_BK][WG_BN + 4];
   const int tid = threadIdx.x;
-  const int HW = H * W, N = Cin * 9;
-  const long long K = static_cast<long long>(B) * HW;
+  const int HWo = g.Ho * g.Wo, HWi = g.H * g.W, KHW = g.KH * g.KW, N = g.Cin * KHW, Cout = g.Cout;
+  const long long K = static_cast<long long>(g.B) * HWo;
   const int n0 = blockIdx.x * WG_BN, m0 = blockIdx.z * BM, sp = blockIdx.y;
   const long long k_lo = sp * k_per_split, k_hi = min(K, k_lo + k_per_split);
   // load roles: position kk = tid % 16 of the stage; rows tid / 16 + 16 * i of the tile
   const int kk = tid & 15, row = tid >> 4;
-  // this thread's position (b, h, w), advanced by 16 per stage
+  // this thread's output position (b, ho, wo), advanced by 16 per stage
   long long pos = k_lo + kk;
-  int b = static_cast<int>(pos / HW);
-  int rem = static_cast<int>(pos - static_cast<long long>(b) * HW);
-  int h = rem / W, w = rem - h * W;
-  // B-operand columns of this thread: (ci, dh, dw) for n = n0 + row + 16 * i
+  int b = static_cast<int>(pos / HWo);
+  int rem = static_cast<int>(pos - static_cast<long long>(b) * HWo);
+  int ho = rem / g.Wo, wo = rem - ho * g.Wo;
+  // B-operand columns of this thread: (ci, row offset, column offset) for n = n0 + row + 16 * i
   int b_ci[4], b_dh[4], b_dw[4];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int n = n0 + row + 16 * i;
     if (n < N) {
-      const int ci = n / 9, tap = n - ci * 9;
+      const int ci = n / KHW, tap = n - ci * KHW, kh = tap / g.KW, kw = tap - kh * g.KW;
       b_ci[i] = ci;
-      b_dh[i] = (tap / 3 - 1) * d;
-      b_dw[i] = (tap % 3 - 1) * d;
+      b_dh[i] = kh * g.dh - g.ph;
+      b_dw[i] = kw * g.dw - g.pw;
     } else {
       b_ci[i] = -1; b_dh[i] = 0; b_dw[i] = 0;
     }
@@ -206,13 +206,13 @@ __global__ void __launch_bounds__(WG_THREADS) wgrad_gemm_kernel(const float* __r
 #pragma unroll
     for (int i = 0; i < LA; ++i) {
       const int m = m0 + row + 16 * i;
-      av[i] = (k_ok && m < Cout) ? __ldg(dy + (static_cast<long long>(b) * Cout + m) * HW + h * W + w) : 0.f;
+      av[i] = (k_ok && m < Cout) ? __ldg(dy + (static_cast<long long>(b) * Cout + m) * HWo + ho * g.Wo + wo) : 0.f;
     }
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      const int hh = h + b_dh[i], ww = w + b_dw[i];
-      bv[i] = (k_ok && b_ci[i] >= 0 && hh >= 0 && hh < H && ww >= 0 && ww < W)
-                  ? __ldg(x + (static_cast<long long>(b) * Cin + b_ci[i]) * HW + hh * W + ww) : 0.f;
+      const int hh = ho * g.sh + b_dh[i], ww = wo * g.sw + b_dw[i];
+      bv[i] = (k_ok && b_ci[i] >= 0 && hh >= 0 && hh < g.H && ww >= 0 && ww < g.W)
+                  ? __ldg(x + (static_cast<long long>(b) * g.Cin + b_ci[i]) * HWi + hh * g.W + ww) : 0.f;
     }
     __syncthreads();                       // the previous stage's reads are done
 #pragma unroll
@@ -233,9 +233,9 @@ __global__ void __launch_bounds__(WG_THREADS) wgrad_gemm_kernel(const float* __r
         for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], bb[j], acc[i][j]);
     }
     // advance this thread's position by one stage
-    w += WG_BK;
-    while (w >= W) { w -= W; ++h; }
-    while (h >= H) { h -= H; ++b; }
+    wo += WG_BK;
+    while (wo >= g.Wo) { wo -= g.Wo; ++ho; }
+    while (ho >= g.Ho) { ho -= g.Ho; ++b; }
   }
 #pragma unroll
   for (int i = 0; i < TM; ++i) {
@@ -325,6 +325,116 @@ __global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ g, f
   p[i] = p[i] - lr * grad;
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// cnn-* family (SpeechModel, utils/model.py:123-205): Dropout, MaxPool with argmax, Linear layers
+// ---------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t mix32(uint32_t x) {           // lowbias32 integer hash
+  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+  return x;
+}
+
+// nn.Dropout in training mode: y = x * keep / (1 - p).  keep comes from the caller's mask (uint8, what the parity tests use) or
+// is drawn here (counter-based hash of seed, site and element; the drawn mask is written to `mask` for the backward pass).
+__global__ void dropout_fwd_kernel(const float* __restrict__ x, const unsigned char* __restrict__ user_mask, unsigned char* __restrict__ mask,
+                                   float* __restrict__ y, long long n, float p, float scale, uint32_t seed) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    unsigned char k;
+    if (user_mask) k = user_mask[i] != 0;
+    else k = (mix32(seed ^ mix32(static_cast<uint32_t>(i) + 0x9e3779b9u * static_cast<uint32_t>(i >> 32))) >> 8) * (1.f / 16777216.f) >= p;
+    mask[i] = k;
+    y[i] = k ? x[i] * scale : 0.f;
+  }
+}
+
+// dx = dy * keep / (1 - p), then through the ReLU that produced the dropped tensor when `relu_out` (the ReLU's output) is given
+__global__ void dropout_relu_bwd_kernel(const float* __restrict__ dy, const unsigned char* __restrict__ mask, const float* __restrict__ relu_out,
+                                        float* __restrict__ dx, long long n, float scale) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float g = (!mask || mask[i]) ? dy[i] * scale : 0.f;
+    if (relu_out && !(relu_out[i] > 0.f)) g = 0.f;
+    dx[i] = g;
+  }
+}
+
+// nn.MaxPool2d(kernel = stride, floor mode) with the flat index (within the plane) of the FIRST maximum of each window in
+// scan order, which is the element torch's backward sends the gradient to.
+__global__ void maxpool_fwd_kernel(const float* __restrict__ in, float* __restrict__ out, int* __restrict__ idx, long long total, int H, int W,
+                                   int Ho, int Wo, int kh, int kw) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int wo = static_cast<int>(i % Wo), ho = static_cast<int>((i / Wo) % Ho);
+    const long long bc = i / (static_cast<long long>(Wo) * Ho);
+    const float* pl = in + bc * H * W;
+    int best = (ho * kh) * W + wo * kw;
+    float bv = pl[best];
+    for (int a = 0; a < kh; ++a)
+      for (int b = 0; b < kw; ++b) {
+        const int j = (ho * kh + a) * W + wo * kw + b;
+        const float v = pl[j];
+        if (v > bv || v != v) { bv = v; best = j; }
+      }
+    out[i] = bv;
+    idx[i] = best;
+  }
+}
+
+// one thread per INPUT element: it receives its window's gradient if it is that window's argmax (windows do not overlap)
+__global__ void maxpool_bwd_kernel(const float* __restrict__ dy, const int* __restrict__ idx, float* __restrict__ dx, long long total, int H, int W,
+                                   int Ho, int Wo, int kh, int kw) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int w = static_cast<int>(i % W), h = static_cast<int>((i / W) % H);
+    const long long bc = i / (static_cast<long long>(W) * H);
+    const int ho = h / kh, wo = w / kw;
+    float g = 0.f;
+    if (ho < Ho && wo < Wo) {
+      const long long o = (bc * Ho + ho) * Wo + wo;
+      if (idx[o] == h * W + w) g = dy[o];
+    }
+    dx[i] = g;
+  }
+}
+
+// dx[b][i] = sum_o dy[b][o] * W[o][i]
+__global__ void linear_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ W, float* __restrict__ dx, int B, int In, int Out) {
+  const long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (t >= static_cast<long long>(B) * In) return;
+  const int i = static_cast<int>(t % In), b = static_cast<int>(t / In);
+  float s = 0.f;
+  for (int o = 0; o < Out; ++o) s = fmaf(dy[b * Out + o], W[static_cast<long long>(o) * In + i], s);
+  dx[t] = s;
+}
+
+// dW[o][i] = sum_b dy[b][o] * x[b][i]   (i == In: the bias gradient db[o] = sum_b dy[b][o])
+__global__ void linear_wgrad_full_kernel(const float* __restrict__ dy, const float* __restrict__ x, float* __restrict__ dW, float* __restrict__ db,
+                                         int B, int In, int Out) {
+  const long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (t >= static_cast<long long>(Out) * (In + 1)) return;
+  const int i = static_cast<int>(t % (In + 1)), o = static_cast<int>(t / (In + 1));
+  double s = 0.0;
+  for (int b = 0; b < B; ++b) s += static_cast<double>(dy[b * Out + o]) * (i < In ? x[static_cast<long long>(b) * In + i] : 1.f);
+  if (i < In) dW[static_cast<long long>(o) * In + i] = static_cast<float>(s);
+  else db[o] = static_cast<float>(s);
+}
+
+// db[c] = sum over (b, pos) of dy[b][c][pos] from the partials of chan_sums_kernel(dy, nullptr)
+__global__ void bias_grad_finalize_kernel(const double* __restrict__ partial, int nsplit, float* __restrict__ db, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double s = 0.0;
+  for (int i = 0; i < nsplit; ++i) s += partial[(static_cast<long long>(c) * nsplit + i) * 2];
+  db[c] = static_cast<float>(s);
+}
+
+// in-place ReLU backward for a Linear layer's activation: g = (out > 0) ? g : 0
+__global__ void relu_bwd_kernel(float* __restrict__ g, const float* __restrict__ out, long long n) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x)
+    if (!(out[i] > 0.f)) g[i] = 0.f;
+}
+
+__global__ void relu_fwd_kernel(float* __restrict__ x, long long n) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x)
+    x[i] = fmaxf(x[i], 0.f);
+}
+
 inline int ew_blocks(long long n) { return static_cast<int>(std::min<long long>((n + 255) / 256, 148 * 16)); }
 
 }  // namespace
@@ -353,6 +463,18 @@ struct honk_trainer {
   bool momentum_ready = false;               // false: the next step initialises the momentum buffers with the gradient
   int64_t steps = 0;                         // num_batches_tracked of every BatchNorm layer
   int64_t base_tracked = 0;
+  // cnn-* family: geometry derived from cfg, Dropout settings
+  int C1 = 0, H1 = 0, W1 = 0, H1p = 0, W1p = 0;     // conv1 output, pooled
+  int C2 = 0, H2 = 0, W2 = 0, H2p = 0, W2p = 0;     // conv2 output, pooled (has_conv2)
+  int flat = 0;                                    // features entering the first Linear layer
+  float dropout_p = 0.5f;                          // nn.Dropout(config["dropout_prob"]), model.py:183
+  uint64_t seed = 0x5eed5eedull;
+  const unsigned char* user_mask[4] = {nullptr, nullptr, nullptr, nullptr};   // caller's keep masks for the NEXT step (device, uint8)
+  int pi(const char* name) const {                 // index of a parameter by its state_dict key, -1 when absent
+    for (size_t i = 0; i < params.size(); ++i)
+      if (params[i].name == name) return static_cast<int>(i);
+    return -1;
+  }
 };
 
 namespace {
@@ -379,8 +501,8 @@ struct TrainWs {
 
 int wgrad_bm(int Cout) { return Cout <= 32 ? 32 : 64; }
 
-int wgrad_split(int Cin, int Cout, long long K) {
-  const int tiles = ceil_div(Cin * 9, WG_BN) * ceil_div(Cout, wgrad_bm(Cout));
+int wgrad_split(int n_cols, int Cout, long long K) {          // n_cols = Cin * KH * KW
+  const int tiles = ceil_div(n_cols, WG_BN) * ceil_div(Cout, wgrad_bm(Cout));
   long long s = ceil_div(148 * 6, tiles);
   s = std::max<long long>(1, std::min<long long>(s, std::min<long long>((K + 255) / 256, 1024)));
   return static_cast<int>(s);
@@ -409,22 +531,245 @@ void carve(const honk_trainer* t, int64_t B, Arena& a, TrainWs& w) {
   w.dx = a.take<float>(map);
   w.dc = a.take<float>(big);
   w.dold = a.take<float>(map);
-  w.wsplit_main = wgrad_split(C, C, B * t->Hr * t->Wr);
-  w.wsplit_stem = wgrad_split(1, C, B * t->H0 * t->W0);
+  w.wsplit_main = wgrad_split(C * 9, C, B * t->Hr * t->Wr);
+  w.wsplit_stem = wgrad_split(9, C, B * t->H0 * t->W0);
   w.wpart = a.take<float>(std::max<int64_t>(static_cast<int64_t>(w.wsplit_main) * C * C * 9, static_cast<int64_t>(w.wsplit_stem) * C * 9));
 }
 
-int wgrad(const float* x, const float* dy, float* part, float* dw, int B, int Cin, int Cout, int H, int W, int d, int nsplit, cudaStream_t s) {
-  const long long K = static_cast<long long>(B) * H * W;
+int wgrad(const float* x, const float* dy, float* part, float* dw, const ConvGeom& g, int nsplit, cudaStream_t s) {
+  const long long K = static_cast<long long>(g.B) * g.Ho * g.Wo;
   const long long per = align_up((K + nsplit - 1) / nsplit, WG_BK);
-  const int bm = wgrad_bm(Cout);
-  const dim3 grid(ceil_div(Cin * 9, WG_BN), nsplit, ceil_div(Cout, bm));
-  if (bm == 32) wgrad_gemm_kernel<32><<<grid, WG_THREADS, 0, s>>>(x, dy, part, B, Cin, Cout, H, W, d, per);
-  else wgrad_gemm_kernel<64><<<grid, WG_THREADS, 0, s>>>(x, dy, part, B, Cin, Cout, H, W, d, per);
+  const int bm = wgrad_bm(g.Cout), n = g.Cout * g.Cin * g.KH * g.KW;
+  const dim3 grid(ceil_div(g.Cin * g.KH * g.KW, WG_BN), nsplit, ceil_div(g.Cout, bm));
+  if (bm == 32) wgrad_gemm_kernel<32><<<grid, WG_THREADS, 0, s>>>(x, dy, part, g, per);
+  else wgrad_gemm_kernel<64><<<grid, WG_THREADS, 0, s>>>(x, dy, part, g, per);
   HONK_LAUNCH_CHECK();
-  const int n = Cout * Cin * 9;
   wgrad_reduce_kernel<<<ceil_div(n, 256), 256, 0, s>>>(part, dw, nsplit, n);
   HONK_LAUNCH_CHECK();
+  return HONK_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// cnn-* family: workspace and the step (SpeechModel.forward in training mode, utils/model.py:186-205)
+// ---------------------------------------------------------------------------------------------------------------------
+struct CnnWs {
+  float *a1 = nullptr, *p1 = nullptr, *a2 = nullptr, *p2 = nullptr;      // dropped relu(conv) maps and their pooled versions
+  int *i1 = nullptr, *i2 = nullptr;                                      // argmax of the pool windows
+  unsigned char* mask[4] = {nullptr, nullptr, nullptr, nullptr};
+  float *lin = nullptr, *z1 = nullptr, *e1 = nullptr, *z2 = nullptr, *e2 = nullptr;   // Linear outputs / dropped versions
+  float *logits = nullptr, *dlogits = nullptr, *rowloss = nullptr;
+  float *ga = nullptr, *gb = nullptr;                                    // gradient ping-pong (largest activation)
+  float* wpart = nullptr;
+  int split1 = 1, split2 = 1;
+};
+
+void carve_cnn(const honk_trainer* t, int64_t B, Arena& a, CnnWs& w) {
+  const honk_model_config& c = t->cfg;
+  const int64_t n1 = B * t->C1 * t->H1 * t->W1, n1p = B * t->C1 * t->H1p * t->W1p;
+  const int64_t n2 = c.has_conv2 ? B * t->C2 * t->H2 * t->W2 : 0, n2p = c.has_conv2 ? B * t->C2 * t->H2p * t->W2p : 0;
+  w.a1 = a.take<float>(n1);
+  w.p1 = a.take<float>(n1p);
+  w.i1 = a.take<int>(n1p);
+  w.mask[0] = a.take<unsigned char>(n1);
+  if (c.has_conv2) {
+    w.a2 = a.take<float>(n2);
+    w.p2 = a.take<float>(n2p);
+    w.i2 = a.take<int>(n2p);
+    w.mask[1] = a.take<unsigned char>(n2);
+  }
+  if (!c.tf_variant) w.lin = a.take<float>(B * 32);
+  if (c.dnn1_size > 0) {
+    w.z1 = a.take<float>(B * c.dnn1_size);
+    w.e1 = a.take<float>(B * c.dnn1_size);
+    w.mask[2] = a.take<unsigned char>(B * c.dnn1_size);
+    if (c.dnn2_size > 0) {
+      w.z2 = a.take<float>(B * c.dnn2_size);
+      w.e2 = a.take<float>(B * c.dnn2_size);
+      w.mask[3] = a.take<unsigned char>(B * c.dnn2_size);
+    }
+  }
+  w.logits = a.take<float>(B * c.n_labels);
+  w.dlogits = a.take<float>(B * c.n_labels);
+  w.rowloss = a.take<float>(B);
+  const int64_t big = std::max<int64_t>(std::max(n1, n2), std::max<int64_t>(B * t->flat, 1024));
+  w.ga = a.take<float>(big);
+  w.gb = a.take<float>(big);
+  const int k1 = c.conv1_size[0] * c.conv1_size[1];
+  w.split1 = wgrad_split(k1, t->C1, B * t->H1 * t->W1);
+  int64_t part = static_cast<int64_t>(w.split1) * t->C1 * k1;
+  if (c.has_conv2) {
+    const int k2 = t->C1 * c.conv2_size[0] * c.conv2_size[1];
+    w.split2 = wgrad_split(k2, t->C2, B * t->H2 * t->W2);
+    part = std::max(part, static_cast<int64_t>(w.split2) * t->C2 * k2);
+  }
+  w.wpart = a.take<float>(part);
+}
+
+// y = x W^T + b for a Linear layer stored as parameters (wi, wi + 1)
+int linear_fwd(const honk_trainer* t, int wi, const float* x, float* y, int B, cudaStream_t s) {
+  const TrainParam& W = t->params[wi];
+  const int Out = static_cast<int>(t->params[wi + 1].numel), In = static_cast<int>(W.numel / Out);
+  ConvGeom g{B, In, 1, 1, Out, 1, 1, 1, 1, 0, 0, 1, 1, 1, 1};
+  return conv2d_f32(x, W.p, t->params[wi + 1].p, y, g, false, s);
+}
+
+// gradients of a Linear layer: dW, db always; dx when asked for
+int linear_bwd(honk_trainer* t, int wi, const float* x, const float* dy, float* dx, int B, cudaStream_t s) {
+  TrainParam& W = t->params[wi];
+  const int Out = static_cast<int>(t->params[wi + 1].numel), In = static_cast<int>(W.numel / Out);
+  const long long nw = static_cast<long long>(Out) * (In + 1);
+  linear_wgrad_full_kernel<<<static_cast<unsigned>((nw + 127) / 128), 128, 0, s>>>(dy, x, W.g, t->params[wi + 1].g, B, In, Out);
+  HONK_LAUNCH_CHECK();
+  if (dx) {
+    const long long nx = static_cast<long long>(B) * In;
+    linear_dgrad_kernel<<<static_cast<unsigned>((nx + 127) / 128), 128, 0, s>>>(dy, W.p, dx, B, In, Out);
+    HONK_LAUNCH_CHECK();
+  }
+  return HONK_OK;
+}
+
+int dropout_fwd(honk_trainer* t, int site, const float* x, unsigned char* mask, float* y, long long n, cudaStream_t s) {
+  const float p = t->dropout_p;
+  const uint32_t seed = static_cast<uint32_t>(t->seed) ^ (static_cast<uint32_t>(t->seed >> 32) * 0x9e3779b9u) ^
+                        (static_cast<uint32_t>(t->steps) * 0x85ebca6bu) ^ (static_cast<uint32_t>(site + 1) * 0xc2b2ae35u);
+  dropout_fwd_kernel<<<ew_blocks(n), 256, 0, s>>>(x, t->user_mask[site], mask, y, n, p, 1.f / (1.f - p), seed);
+  HONK_LAUNCH_CHECK();
+  return HONK_OK;
+}
+
+int cnn_step(honk_trainer* t, const float* x, const int64_t* labels, int B, float* d_scores, float* d_loss, CnnWs& w, cudaStream_t s) {
+  const honk_model_config& c = t->cfg;
+  const bool drop = t->dropout_p > 0.f;
+  const float scale = drop ? 1.f / (1.f - t->dropout_p) : 1.f;
+  const int L = c.n_labels;
+  const int i_c1 = t->pi("conv1.weight"), i_c2 = t->pi("conv2.weight"), i_lin = t->pi("lin.weight"), i_d1 = t->pi("dnn1.weight"),
+            i_d2 = t->pi("dnn2.weight"), i_out = t->pi("output.weight");
+  const long long n1 = static_cast<long long>(B) * t->C1 * t->H1 * t->W1, n1p = static_cast<long long>(B) * t->C1 * t->H1p * t->W1p;
+  const long long n2 = c.has_conv2 ? static_cast<long long>(B) * t->C2 * t->H2 * t->W2 : 0;
+  const long long n2p = c.has_conv2 ? static_cast<long long>(B) * t->C2 * t->H2p * t->W2p : 0;
+  ConvGeom g1{B, 1, t->H0, t->W0, t->C1, c.conv1_size[0], c.conv1_size[1], c.conv1_stride[0], c.conv1_stride[1], 0, 0, 1, 1, 0, 0};
+  conv_out_dims(g1);
+  ConvGeom g2{B, t->C1, t->H1p, t->W1p, t->C2, c.conv2_size[0], c.conv2_size[1], 1, 1, 0, 0, 1, 1, 0, 0};
+  if (c.has_conv2) conv_out_dims(g2);
+  const float* flat = nullptr;       // [B, flat] input of the first Linear layer
+  const float* last = nullptr;       // input of the output layer
+  // ---- forward ----------------------------------------------------------------------------------------------------
+  {
+    ProfSpan sp("train_fwd", s);
+    HONK_TRY(conv2d_f32(x, t->params[i_c1].p, t->params[i_c1 + 1].p, w.a1, g1, true, s));
+    if (drop) HONK_TRY(dropout_fwd(t, 0, w.a1, w.mask[0], w.a1, n1, s));
+    maxpool_fwd_kernel<<<ew_blocks(n1p), 256, 0, s>>>(w.a1, w.p1, w.i1, n1p, t->H1, t->W1, t->H1p, t->W1p, c.conv1_pool[0], c.conv1_pool[1]);
+    HONK_LAUNCH_CHECK();
+    flat = w.p1;
+    if (c.has_conv2) {
+      HONK_TRY(conv2d_f32(w.p1, t->params[i_c2].p, t->params[i_c2 + 1].p, w.a2, g2, true, s));
+      if (drop) HONK_TRY(dropout_fwd(t, 1, w.a2, w.mask[1], w.a2, n2, s));
+      maxpool_fwd_kernel<<<ew_blocks(n2p), 256, 0, s>>>(w.a2, w.p2, w.i2, n2p, t->H2, t->W2, t->H2p, t->W2p, c.conv2_pool[0], c.conv2_pool[1]);
+      HONK_LAUNCH_CHECK();
+      flat = w.p2;
+    }
+    last = flat;
+    if (i_lin >= 0) {
+      HONK_TRY(linear_fwd(t, i_lin, last, w.lin, B, s));
+      last = w.lin;
+    }
+    if (i_d1 >= 0) {
+      HONK_TRY(linear_fwd(t, i_d1, last, w.z1, B, s));
+      const long long nz = static_cast<long long>(B) * c.dnn1_size;
+      if (!c.tf_variant) {
+        relu_fwd_kernel<<<ew_blocks(nz), 256, 0, s>>>(w.z1, nz);
+        HONK_LAUNCH_CHECK();
+      }
+      if (drop) HONK_TRY(dropout_fwd(t, 2, w.z1, w.mask[2], w.e1, nz, s));
+      last = drop ? w.e1 : w.z1;
+      if (i_d2 >= 0) {
+        HONK_TRY(linear_fwd(t, i_d2, last, w.z2, B, s));
+        const long long nz2 = static_cast<long long>(B) * c.dnn2_size;
+        if (drop) HONK_TRY(dropout_fwd(t, 3, w.z2, w.mask[3], w.e2, nz2, s));
+        last = drop ? w.e2 : w.z2;
+      }
+    }
+    HONK_TRY(linear_fwd(t, i_out, last, w.logits, B, s));
+    ce_fwd_bwd_kernel<<<ceil_div(B, 128), 128, 0, s>>>(w.logits, reinterpret_cast<const long long*>(labels), w.dlogits, w.rowloss, B, L);
+    HONK_LAUNCH_CHECK();
+    if (d_loss) {
+      loss_mean_kernel<<<1, 256, 0, s>>>(w.rowloss, d_loss, B);
+      HONK_LAUNCH_CHECK();
+    }
+    if (d_scores) HONK_CUDA(cudaMemcpyAsync(d_scores, w.logits, static_cast<size_t>(B) * L * 4, cudaMemcpyDeviceToDevice, s));
+  }
+  // ---- backward ---------------------------------------------------------------------------------------------------
+  {
+    ProfSpan sp("train_bwd", s);
+    float* g = w.ga;                   // gradient at the input of the layer being processed
+    float* g2b = w.gb;
+    HONK_TRY(linear_bwd(t, i_out, last, w.dlogits, g, B, s));
+    if (i_d1 >= 0) {
+      if (i_d2 >= 0) {
+        const long long nz2 = static_cast<long long>(B) * c.dnn2_size;
+        if (drop) {
+          dropout_relu_bwd_kernel<<<ew_blocks(nz2), 256, 0, s>>>(g, w.mask[3], nullptr, g, nz2, scale);
+          HONK_LAUNCH_CHECK();
+        }
+        HONK_TRY(linear_bwd(t, i_d2, drop ? w.e1 : w.z1, g, g2b, B, s));
+        std::swap(g, g2b);
+      }
+      const long long nz = static_cast<long long>(B) * c.dnn1_size;
+      if (drop || !c.tf_variant) {
+        dropout_relu_bwd_kernel<<<ew_blocks(nz), 256, 0, s>>>(g, drop ? w.mask[2] : nullptr, c.tf_variant ? nullptr : w.z1, g, nz, scale);
+        HONK_LAUNCH_CHECK();
+      }
+      HONK_TRY(linear_bwd(t, i_d1, i_lin >= 0 ? w.lin : flat, g, g2b, B, s));
+      std::swap(g, g2b);
+    }
+    if (i_lin >= 0) {
+      HONK_TRY(linear_bwd(t, i_lin, flat, g, g2b, B, s));
+      std::swap(g, g2b);
+    }
+    // g: gradient at the flattened pooled map
+    if (c.has_conv2) {
+      maxpool_bwd_kernel<<<ew_blocks(n2), 256, 0, s>>>(g, w.i2, g2b, n2, t->H2, t->W2, t->H2p, t->W2p, c.conv2_pool[0], c.conv2_pool[1]);
+      HONK_LAUNCH_CHECK();
+      dropout_relu_bwd_kernel<<<ew_blocks(n2), 256, 0, s>>>(g2b, drop ? w.mask[1] : nullptr, w.a2, g2b, n2, scale);
+      HONK_LAUNCH_CHECK();
+      std::swap(g, g2b);               // g = gradient at conv2's output (before bias / ReLU)
+      chan_sums_kernel<<<dim3(t->C2, kStatSplit), 256, 0, s>>>(g, nullptr, t->partial, B, t->C2, t->H2 * t->W2);
+      HONK_LAUNCH_CHECK();
+      bias_grad_finalize_kernel<<<ceil_div(t->C2, 128), 128, 0, s>>>(t->partial, kStatSplit, t->params[i_c2 + 1].g, t->C2);
+      HONK_LAUNCH_CHECK();
+      HONK_TRY(wgrad(w.p1, g, w.wpart, t->params[i_c2].g, g2, w.split2, s));
+      const int khw = g2.KH * g2.KW;
+      flip_weights_kernel<<<ceil_div(t->C2 * t->C1 * khw, 256), 256, 0, s>>>(t->params[i_c2].p, t->wflip, t->C2, t->C1, khw);
+      HONK_LAUNCH_CHECK();
+      ConvGeom gd{B, t->C2, t->H2, t->W2, t->C1, g2.KH, g2.KW, 1, 1, g2.KH - 1, g2.KW - 1, 1, 1, 0, 0};
+      conv_out_dims(gd);               // = H1p x W1p
+      HONK_TRY(conv2d_f32(g, t->wflip, nullptr, g2b, gd, false, s));
+      std::swap(g, g2b);               // g = gradient at the pooled conv1 map
+    }
+    maxpool_bwd_kernel<<<ew_blocks(n1), 256, 0, s>>>(g, w.i1, g2b, n1, t->H1, t->W1, t->H1p, t->W1p, c.conv1_pool[0], c.conv1_pool[1]);
+    HONK_LAUNCH_CHECK();
+    dropout_relu_bwd_kernel<<<ew_blocks(n1), 256, 0, s>>>(g2b, drop ? w.mask[0] : nullptr, w.a1, g2b, n1, scale);
+    HONK_LAUNCH_CHECK();
+    chan_sums_kernel<<<dim3(t->C1, kStatSplit), 256, 0, s>>>(g2b, nullptr, t->partial, B, t->C1, t->H1 * t->W1);
+    HONK_LAUNCH_CHECK();
+    bias_grad_finalize_kernel<<<ceil_div(t->C1, 128), 128, 0, s>>>(t->partial, kStatSplit, t->params[i_c1 + 1].g, t->C1);
+    HONK_LAUNCH_CHECK();
+    HONK_TRY(wgrad(x, g2b, w.wpart, t->params[i_c1].g, g1, w.split1, s));
+  }
+  return HONK_OK;
+}
+
+// torch.optim.SGD.step over every parameter of the handle
+int sgd_apply(honk_trainer* t, const honk_sgd* opt, cudaStream_t s) {
+  ProfSpan sp("train_sgd", s);
+  const int first = t->momentum_ready ? 0 : 1;
+  for (TrainParam& p : t->params) {
+    sgd_kernel<<<ceil_div(static_cast<int>(p.numel), 256), 256, 0, s>>>(p.p, p.g, p.mom, static_cast<int>(p.numel), opt->lr, opt->momentum,
+                                                                       opt->weight_decay, opt->nesterov, first);
+    HONK_LAUNCH_CHECK();
+  }
+  if (opt->momentum != 0.f) t->momentum_ready = true;
+  t->steps += 1;
   return HONK_OK;
 }
 
@@ -436,8 +781,7 @@ int wgrad(const float* x, const float* dy, float* part, float* dw, int B, int Ci
 extern "C" int honk_trainer_create(const honk_model_config* cfg, const honk_tensor* tensors, int32_t n_tensors, int device,
                                    honk_trainer** out) {
   HONK_CHECK(cfg && out && tensors, HONK_ERR_INVALID, "honk_trainer_create: null argument");
-  HONK_CHECK(cfg->family == HONK_FAMILY_RES, HONK_ERR_UNSUPPORTED,
-             "honk_trainer_create: only the res* family trains on the GPU (the cnn-* models draw torch's dropout masks)");
+  HONK_CHECK(cfg->family == HONK_FAMILY_RES || cfg->family == HONK_FAMILY_CNN, HONK_ERR_INVALID, "honk_trainer_create: unknown family");
   // the strict state_dict check (names, shapes) is the model handle's: build one and take its validated host copy
   honk_model* m = nullptr;
   HONK_TRY(honk_model_create(cfg, tensors, n_tensors, device, &m));
@@ -447,7 +791,6 @@ extern "C" int honk_trainer_create(const honk_model_config* cfg, const honk_tens
   t->cfg = *cfg;
   t->device = device;
   t->H0 = m->H0; t->W0 = m->W0; t->Hr = m->Hr; t->Wr = m->Wr;
-  const int C = cfg->n_feature_maps, n = cfg->n_layers;
   auto fail = [&](int rc) {
     for (void* p : t->owned) cudaFree(p);
     return rc;
@@ -464,7 +807,41 @@ extern "C" int honk_trainer_create(const honk_model_config* cfg, const honk_tens
     t->params.push_back(p);
     return HONK_OK;
   };
-  int rc = add_param("conv0.weight");
+  int rc = HONK_OK;
+  if (cfg->family == HONK_FAMILY_CNN) {
+    const honk_model_config& c = *cfg;
+    HONK_CHECK(!c.has_conv2 || (c.conv2_stride[0] == 1 && c.conv2_stride[1] == 1), HONK_ERR_UNSUPPORTED,
+               "honk_trainer_create: conv2 with a stride is not supported (no reference config has one)");
+    t->H0 = c.height; t->W0 = c.width;
+    t->C1 = c.n_feature_maps1;
+    t->H1 = (c.height - c.conv1_size[0]) / c.conv1_stride[0] + 1;
+    t->W1 = (c.width - c.conv1_size[1]) / c.conv1_stride[1] + 1;
+    t->H1p = t->H1 / c.conv1_pool[0]; t->W1p = t->W1 / c.conv1_pool[1];
+    t->flat = t->C1 * t->H1p * t->W1p;
+    if (c.has_conv2) {
+      t->C2 = c.n_feature_maps2;
+      t->H2 = t->H1p - c.conv2_size[0] + 1; t->W2 = t->W1p - c.conv2_size[1] + 1;
+      t->H2p = t->H2 / c.conv2_pool[0]; t->W2p = t->W2 / c.conv2_pool[1];
+      t->flat = t->C2 * t->H2p * t->W2p;
+    }
+    const char* names[] = {"conv1", "conv2", "lin", "dnn1", "dnn2", "output"};
+    for (const char* nm : names) {
+      if (!m->host.count(std::string(nm) + ".weight")) continue;
+      if (rc == HONK_OK) rc = add_param(std::string(nm) + ".weight");
+      if (rc == HONK_OK) rc = add_param(std::string(nm) + ".bias");
+    }
+    if (rc != HONK_OK) return fail(rc);
+    int64_t max_conv_w = t->params[0].numel;
+    if (c.has_conv2) max_conv_w = std::max(max_conv_w, t->params[t->pi("conv2.weight")].numel);
+    const int maxC = std::max(t->C1, t->C2);
+    if (rc == HONK_OK) rc = t_alloc(t.get(), static_cast<int64_t>(maxC) * kStatSplit * 2 * 8, reinterpret_cast<void**>(&t->partial));
+    if (rc == HONK_OK) rc = t_alloc(t.get(), max_conv_w * 4, reinterpret_cast<void**>(&t->wflip));
+    if (rc != HONK_OK) return fail(rc);
+    *out = t.release();
+    return HONK_OK;
+  }
+  const int C = cfg->n_feature_maps, n = cfg->n_layers;
+  rc = add_param("conv0.weight");
   for (int i = 1; rc == HONK_OK && i <= n; ++i) rc = add_param("conv" + std::to_string(i) + ".weight");
   if (rc == HONK_OK) rc = add_param("output.weight");
   if (rc == HONK_OK) rc = add_param("output.bias");
@@ -502,8 +879,13 @@ extern "C" int honk_trainer_destroy(honk_trainer* t) {
 extern "C" int64_t honk_trainer_workspace_bytes(const honk_trainer* t, int64_t n_clips) {
   if (!t || n_clips <= 0) return 0;
   Arena a(nullptr, 0);
-  TrainWs w;
-  carve(t, n_clips, a, w);
+  if (t->cfg.family == HONK_FAMILY_CNN) {
+    CnnWs w;
+    carve_cnn(t, n_clips, a, w);
+  } else {
+    TrainWs w;
+    carve(t, n_clips, a, w);
+  }
   return align_up(a.off, 256);
 }
 
@@ -514,6 +896,20 @@ extern "C" int honk_trainer_reset_optimizer(honk_trainer* t) {
 }
 
 extern "C" int64_t honk_trainer_steps(const honk_trainer* t) { return t ? t->steps : 0; }
+
+extern "C" int honk_trainer_set_dropout(honk_trainer* t, float prob, uint64_t seed) {
+  HONK_CHECK(t, HONK_ERR_INVALID, "honk_trainer_set_dropout: null handle");
+  HONK_CHECK(prob >= 0.f && prob < 1.f, HONK_ERR_INVALID, "honk_trainer_set_dropout: probability %g outside [0, 1)", prob);
+  t->dropout_p = prob;
+  t->seed = seed;
+  return HONK_OK;
+}
+
+extern "C" int honk_trainer_set_dropout_masks(honk_trainer* t, const unsigned char* const* d_masks, int32_t n_masks) {
+  HONK_CHECK(t && (d_masks || n_masks == 0) && n_masks >= 0 && n_masks <= 4, HONK_ERR_INVALID, "honk_trainer_set_dropout_masks: bad argument");
+  for (int i = 0; i < 4; ++i) t->user_mask[i] = i < n_masks ? d_masks[i] : nullptr;
+  return HONK_OK;
+}
 
 // name: a state_dict key ("conv3.weight", "bn2.running_var", "output.bias"), or "grad:<parameter>" / "momentum:<parameter>".
 extern "C" int honk_trainer_read(const honk_trainer* t, const char* name, float* h_out, int64_t numel) {
@@ -550,7 +946,7 @@ extern "C" int honk_trainer_step(honk_trainer* t, const float* d_mfcc, const int
   HONK_CHECK(t && d_mfcc && d_labels && opt, HONK_ERR_INVALID, "honk_trainer_step: null argument");
   HONK_CHECK(height == t->H0 && width == t->W0, HONK_ERR_INVALID, "honk_trainer_step: clips are %d x %d, the model takes %d x %d",
              height, width, t->H0, t->W0);
-  HONK_CHECK(n_clips >= 2 && n_clips <= 65536, HONK_ERR_INVALID,
+  HONK_CHECK(n_clips >= (t->cfg.family == HONK_FAMILY_RES ? 2 : 1) && n_clips <= 65536, HONK_ERR_INVALID,
              "honk_trainer_step: batch of %lld clips (BatchNorm in training mode needs at least 2; at most 65536)",
              static_cast<long long>(n_clips));
   HONK_CHECK(opt->momentum >= 0.f && opt->weight_decay >= 0.f && (!opt->nesterov || opt->momentum > 0.f), HONK_ERR_INVALID,
@@ -558,6 +954,17 @@ extern "C" int honk_trainer_step(honk_trainer* t, const float* d_mfcc, const int
   HONK_CUDA(cudaSetDevice(t->device));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const honk_model_config& c = t->cfg;
+  if (c.family == HONK_FAMILY_CNN) {
+    Arena a(d_workspace, workspace_bytes);
+    CnnWs w;
+    carve_cnn(t, n_clips, a, w);
+    HONK_CHECK(d_workspace && a.ok(), HONK_ERR_WORKSPACE, "honk_trainer_step: workspace of %lld bytes, %lld needed",
+               static_cast<long long>(workspace_bytes), static_cast<long long>(align_up(a.off, 256)));
+    const int rc = cnn_step(t, d_mfcc, d_labels, static_cast<int>(n_clips), d_scores, d_loss, w, s);
+    for (auto& um : t->user_mask) um = nullptr;                   // the caller's masks serve one step
+    HONK_TRY(rc);
+    return sgd_apply(t, opt, s);
+  }
   const int B = static_cast<int>(n_clips), C = c.n_feature_maps, n = c.n_layers, L = c.n_labels;
   const int H0 = t->H0, W0 = t->W0, Hr = t->Hr, Wr = t->Wr, HW = Hr * Wr;
   const bool pooled = c.res_pool[0] > 0;
@@ -635,30 +1042,23 @@ extern "C" int honk_trainer_step(honk_trainer* t, const float* d_mfcc, const int
                                                        (even && have_dold) ? w.dold : nullptr, even ? w.dold : nullptr, w.dc, C, HW, map);
       HONK_LAUNCH_CHECK();
       if (even) have_dold = true;
-      HONK_TRY(wgrad(xin, w.dc, w.wpart, t->params[i].g, B, C, C, Hr, Wr, d, w.wsplit_main, s));
-      flip_weights_kernel<<<ceil_div(C * C * 9, 256), 256, 0, s>>>(t->params[i].p, t->wflip, C, C);
-      HONK_LAUNCH_CHECK();
       ConvGeom gi{B, C, Hr, Wr, C, 3, 3, 1, 1, d, d, d, d, 0, 0};
       conv_out_dims(gi);
+      HONK_TRY(wgrad(xin, w.dc, w.wpart, t->params[i].g, gi, w.wsplit_main, s));
+      flip_weights_kernel<<<ceil_div(C * C * 9, 256), 256, 0, s>>>(t->params[i].p, t->wflip, C, C, 9);
+      HONK_LAUNCH_CHECK();
       HONK_TRY(conv2d_f32(w.dc, t->wflip, nullptr, w.dx, gi, false, s));   // dx now holds the gradient at conv_i's input
     }
     stem_bwd_kernel<<<ew_blocks(big), 256, 0, s>>>(w.dx, have_dold ? w.dold : nullptr, w.y0, w.dc, H0, W0, pooled ? c.res_pool[0] : 1,
                                                   pooled ? c.res_pool[1] : 1, Hr, Wr, big);
     HONK_LAUNCH_CHECK();
-    HONK_TRY(wgrad(d_mfcc, w.dc, w.wpart, P0.g, B, 1, C, H0, W0, 1, w.wsplit_stem, s));
+    {
+      ConvGeom g0{B, 1, H0, W0, C, 3, 3, 1, 1, 1, 1, 1, 1, 0, 0};
+      conv_out_dims(g0);
+      HONK_TRY(wgrad(d_mfcc, w.dc, w.wpart, P0.g, g0, w.wsplit_stem, s));
+    }
   }
 
-  // ---- torch.optim.SGD.step ---------------------------------------------------------------------------------------
-  {
-    ProfSpan sp("train_sgd", s);
-    const int first = t->momentum_ready ? 0 : 1;
-    for (TrainParam& p : t->params) {
-      sgd_kernel<<<ceil_div(static_cast<int>(p.numel), 256), 256, 0, s>>>(p.p, p.g, p.mom, static_cast<int>(p.numel), opt->lr, opt->momentum,
-                                                                         opt->weight_decay, opt->nesterov, first);
-      HONK_LAUNCH_CHECK();
-    }
-    if (opt->momentum != 0.f) t->momentum_ready = true;
-  }
-  t->steps += 1;
+  HONK_TRY(sgd_apply(t, opt, s));
   return HONK_OK;
 }

@@ -289,6 +289,7 @@ class SpeechModel(SerializableModule):
     def __init__(self, config):
         super().__init__()
         self.n_labels = n_labels = int(config["n_labels"])
+        self.dropout_prob = float(config.get("dropout_prob", 0.5))      # nn.Dropout (model.py:183): used by the training step only
         n_featmaps1 = int(config["n_feature_maps1"])
         self.conv1_size = _pair(config["conv1_size"])
         self.conv1_pool = _pair(config["conv1_pool"])

@@ -9,7 +9,8 @@ The training half (train.py:87-163) for the res* family: ``SgdTrainer.step`` rep
 loop (model.train(); scores = model(model_in); loss = criterion(scores, labels); loss.backward(); optimizer.step();
 train.py:127-139) with one native call, ``train`` keeps the loop around it (learning-rate schedule that rebuilds the
 optimiser, dev-set evaluation every ``dev_every`` epochs, best model saved).  Dataset walking (SpeechDataset.splits) stays
-out of scope: the loaders are handed in.  The cnn-* family is refused (its Dropout draws torch's random masks).
+out of scope: the loaders are handed in.  Both families train; the cnn-* family's Dropout masks are drawn by the library
+(reproducible from ``dropout_seed``, not torch's stream) unless the caller hands them in (``step(..., dropout_masks=...)``).
 """
 from __future__ import annotations
 
@@ -87,7 +88,7 @@ class SgdTrainer:
     (``honk_trainer``); ``sync()`` writes the current weights and statistics back into the module (done automatically by
     ``train`` before every evaluation / save), after which ``model.eval()`` inference uses them."""
 
-    def __init__(self, model, lr=0.001, momentum=0.9, weight_decay=0.00001, nesterov=False):
+    def __init__(self, model, lr=0.001, momentum=0.9, weight_decay=0.00001, nesterov=False, dropout_seed=0):
         if not hasattr(model, "_native_config"):
             raise TypeError("SgdTrainer needs a honk_b200 model")
         self.model = model
@@ -102,6 +103,8 @@ class SgdTrainer:
         self.handle = handle.value
         self._ws = None
         self._synced_steps = 0
+        if hasattr(model, "dropout_prob"):                      # SpeechModel: nn.Dropout(config["dropout_prob"])
+            N.check(N.lib().honk_trainer_set_dropout(self.handle, float(model.dropout_prob), int(dropout_seed)))
 
     def __del__(self):
         h, self.handle = getattr(self, "handle", None), None
@@ -124,9 +127,11 @@ class SgdTrainer:
     def steps(self):
         return int(N.lib().honk_trainer_steps(self.handle))
 
-    def step(self, model_in, labels, check_labels=True):
+    def step(self, model_in, labels, check_labels=True, dropout_masks=None):
         """One optimisation step; returns ``(scores [B, n_labels], loss [])`` on the device: the training-mode scores
-        and the batch's mean CrossEntropyLoss before the update, the two things the reference prints (train.py:144)."""
+        and the batch's mean CrossEntropyLoss before the update, the two things the reference prints (train.py:144).
+        ``dropout_masks`` (cnn-* only): up to four keep masks (nonzero = keep) for the Dropout after conv1, conv2, dnn1,
+        dnn2 (``None`` entries are drawn by the library); they replace the library's own draws for this step."""
         m = self.model
         x = torch.as_tensor(model_in)
         y = torch.as_tensor(labels)
@@ -147,6 +152,18 @@ class SgdTrainer:
             self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
         scores = torch.empty((B, m.n_labels), dtype=torch.float32, device=self.device)
         loss = torch.empty((), dtype=torch.float32, device=self.device)
+        keep = []
+        if dropout_masks is not None:
+            ptrs = (C.c_void_p * 4)()
+            for i, mk in enumerate(list(dropout_masks)[:4]):
+                if mk is None:
+                    continue
+                mk = (torch.as_tensor(mk).to(self.device) != 0).to(torch.uint8).contiguous()
+                if mk.shape[0] != B:
+                    raise ValueError("honk_b200: dropout mask %d is for %d clips, the batch has %d" % (i, mk.shape[0], B))
+                keep.append(mk)
+                ptrs[i] = mk.data_ptr()
+            N.check(N.lib().honk_trainer_set_dropout_masks(self.handle, ptrs, 4))
         with torch.cuda.device(self.device):
             N.check(N.lib().honk_trainer_step(self.handle, x.data_ptr(), y.data_ptr(), B, m.height, m.width, C.byref(self.opt),
                                               scores.data_ptr(), loss.data_ptr(), self._ws.data_ptr(), self._ws.numel(),

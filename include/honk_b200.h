@@ -242,8 +242,8 @@ HONK_API int honk_load_audio(const float* d_pcm, int64_t n_clips, int64_t clip_s
  * training loop, utils/train.py:127-139: model.train(), scores = model(model_in), CrossEntropyLoss,
  * loss.backward(), torch.optim.SGD.step()).  FP32 on the CUDA cores; BatchNorm2d(affine=False) in
  * training mode (batch statistics, running statistics moved by momentum 0.1; utils/model.py:98).
- * The cnn-* family is refused with HONK_ERR_UNSUPPORTED: its nn.Dropout draws torch's random masks
- * (utils/model.py:139, 191-200), which no other implementation can reproduce.
+ * cnn-* family (SpeechModel, utils/model.py:123-205): conv + bias + ReLU -> Dropout -> MaxPool (x2), Linear layers with Dropout,
+ * same loss and optimiser; the Dropout keep masks are drawn by the library or handed in (honk_trainer_set_dropout*).
  * ------------------------------------------------------------------------------------------ */
 typedef struct honk_trainer honk_trainer;
 
@@ -270,6 +270,15 @@ HONK_API int honk_trainer_step(honk_trainer* t, const float* d_mfcc, const int64
 /* train.py:141-143 builds a NEW torch.optim.SGD when the learning-rate schedule advances, which drops the momentum
  * buffers; this does the same (the next step initialises them with its gradient). */
 HONK_API int honk_trainer_reset_optimizer(honk_trainer* t);
+/* cnn-* family only: nn.Dropout (utils/model.py:183; applied after conv1, conv2, dnn1 and dnn2, :186-205).  prob is
+ * config["dropout_prob"] (default of a new handle: 0.5); the library draws its keep masks from a counter-based hash of
+ * (seed, step, site, element) - a different stream from torch's, so a run is reproducible here but not bit-comparable with
+ * the reference's.  For a bit-level comparison hand the masks in: honk_trainer_set_dropout_masks gives device pointers to
+ * uint8 keep masks (1 = keep) by site: [0] conv1 [n, C1, H1, W1], [1] conv2 [n, C2, H2, W2], [2] dnn1 [n, dnn1_size],
+ * [3] dnn2 [n, dnn2_size] (entries of absent layers are ignored, NULL or missing entries are drawn by the library); they
+ * serve the NEXT step only. */
+HONK_API int honk_trainer_set_dropout(honk_trainer* t, float prob, uint64_t seed);
+HONK_API int honk_trainer_set_dropout_masks(honk_trainer* t, const unsigned char* const* d_masks, int32_t n_masks);
 /* Steps taken by this handle (what every bn<i>.num_batches_tracked has advanced by). */
 HONK_API int64_t honk_trainer_steps(const honk_trainer* t);
 /* Copies one tensor to the host (synchronises the device): a state_dict key ("conv3.weight", "bn2.running_var",

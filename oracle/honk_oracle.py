@@ -299,14 +299,48 @@ def res_train_logits(params, stats, config, x, momentum=0.1, eps=1e-5):
     return F.linear(x, params["output.weight"], params["output.bias"])
 
 
+def cnn_train_logits(params, config, x, masks=None):
+    """``SpeechModel.forward`` in TRAINING mode (utils/model.py:186-205): ``nn.Dropout(dropout_prob)`` after relu(conv1),
+    relu(conv2), dnn1 and dnn2, each BEFORE the max-pool where there is one.  ``masks``: keep masks (1 = keep) for those four
+    sites in that order (entries of absent layers ignored); the kept values are scaled by 1 / (1 - p) like nn.Dropout does.
+    ``masks=None`` means p = 0 (no dropout)."""
+    import torch.nn.functional as F
+    p = float(config.get("dropout_prob", 0.5)) if masks is not None else 0.0
+
+    def drop(t, site):
+        if masks is None or p == 0.0:
+            return t
+        m = _t(masks[site], t.dtype).reshape(t.shape)
+        return t * m * (1.0 / (1.0 - p))
+
+    x = F.relu(F.conv2d(x.unsqueeze(1), params["conv1.weight"], params["conv1.bias"], tuple(config["conv1_stride"])))
+    x = F.max_pool2d(drop(x, 0), tuple(config["conv1_pool"]))
+    if "conv2.weight" in params:
+        x = F.relu(F.conv2d(x, params["conv2.weight"], params["conv2.bias"], tuple(config["conv2_stride"])))
+        x = F.max_pool2d(drop(x, 1), tuple(config["conv2_pool"]))
+    x = x.reshape(x.size(0), -1)
+    if "lin.weight" in params:
+        x = F.linear(x, params["lin.weight"], params["lin.bias"])
+    if "dnn1.weight" in params:
+        x = F.linear(x, params["dnn1.weight"], params["dnn1.bias"])
+        if not config.get("tf_variant"):
+            x = F.relu(x)
+        x = drop(x, 2)
+    if "dnn2.weight" in params:
+        x = drop(F.linear(x, params["dnn2.weight"], params["dnn2.bias"]), 3)
+    return F.linear(x, params["output.weight"], params["output.bias"])
+
+
 def sgd_train_steps(state, config, batches, lr=0.001, momentum=0.9, weight_decay=0.00001, nesterov=False, dtype=None):
     """The reference's inner training loop (utils/train.py:127-139) for a res* model, restated without nn.Module /
     torch.optim: forward in training mode, mean CrossEntropyLoss (train.py:104), autograd for the gradients, then the
     update rule of ``torch.optim.SGD`` (dampening 0): g += wd * p; buf = g on the first step, else momentum * buf + g;
     g = g + momentum * buf (Nesterov) or buf; p -= lr * g.
 
-    ``state``: numpy state_dict; ``batches``: list of ``(mfcc [B, T, F], labels [B])``.  Returns a dict with the final
-    ``state`` (numpy, num_batches_tracked advanced), per-step ``losses``, ``scores`` and ``grads`` (list of dicts)."""
+    ``state``: numpy state_dict; ``batches``: list of ``(mfcc [B, T, F], labels [B])`` - for a cnn-* model (a state_dict
+    with ``conv1.bias``) optionally ``(mfcc, labels, masks)`` with the Dropout keep masks of ``cnn_train_logits``.
+    Returns a dict with the final ``state`` (numpy, num_batches_tracked advanced), per-step ``losses``, ``scores`` and
+    ``grads`` (list of dicts)."""
     import torch
     import torch.nn.functional as F
     dtype = dtype or torch.float32
@@ -320,10 +354,14 @@ def sgd_train_steps(state, config, batches, lr=0.001, momentum=0.9, weight_decay
             params[k] = _t(v, dtype).clone().requires_grad_()
     bufs = {}
     losses, scores, grads = [], [], []
-    for x, y in batches:
+    for batch in batches:
+        x, y = batch[0], batch[1]
         for p in params.values():
             p.grad = None
-        logits = res_train_logits(params, stats, config, _t(x, dtype))
+        if "conv1.bias" in params:                       # SpeechModel (the res* convolutions have no bias)
+            logits = cnn_train_logits(params, config, _t(x, dtype), batch[2] if len(batch) > 2 else None)
+        else:
+            logits = res_train_logits(params, stats, config, _t(x, dtype))
         loss = F.cross_entropy(logits, torch.as_tensor(np.asarray(y), dtype=torch.int64))
         loss.backward()
         losses.append(float(loss.detach()))

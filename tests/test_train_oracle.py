@@ -9,7 +9,14 @@ import pytest
 
 from oracle import honk_oracle as orc
 
-CASES = ["res8-narrow", "res15-narrow", "res26-narrow", "res8"]
+CASES = ["res8-narrow", "res15-narrow", "res26-narrow", "res8", "cnn-trad-pool2", "cnn-one-stride1", "cnn-tstride4", "cnn-one-fpool3"]
+SUB_MIN, SUB_STEP = 20000, 13          # make_train_golden.py stores large tensors as every 13th element
+
+
+def sub(v):
+    """The view of a tensor that the fixture holds (make_train_golden.subsample)."""
+    v = np.asarray(v)
+    return v.reshape(-1)[::SUB_STEP] if v.size > SUB_MIN else v
 
 
 def load_case(golden_dir, name):
@@ -24,7 +31,19 @@ def load_case(golden_dir, name):
                 case[part][k[len(pfx + part) + 1:]] = g[k]
     steps = len(case["losses"])
     B = len(case["labels"]) // steps
-    case["batches"] = [(case["mfcc"][s * B:(s + 1) * B], case["labels"][s * B:(s + 1) * B]) for s in range(steps)]
+    case["batches"] = [[case["mfcc"][s * B:(s + 1) * B], case["labels"][s * B:(s + 1) * B]] for s in range(steps)]
+    if name.startswith("cnn"):
+        from honk_b200 import synth
+        state = synth.make_state_dict(name, case["config"], seed=11)          # make_train_golden.cnn_init_state
+        case["init"] = {k: (v * np.float32(0.3) if k.endswith("weight") else v) for k, v in state.items()}
+        for s in range(steps):                                                # the reference run's Dropout keep masks
+            masks = [None] * 4
+            for site in range(4):
+                key = pfx + "mask/%d/%d" % (s, site)
+                if key in g.files:
+                    shape = tuple(g[pfx + "maskshape/%d/%d" % (s, site)])
+                    masks[site] = np.unpackbits(g[key])[:int(np.prod(shape))].reshape(shape)
+            case["batches"][s].append(masks)
     return case
 
 
@@ -37,12 +56,12 @@ def test_oracle_training_steps_match_the_reference_run(golden_dir, name):
     for s in range(len(c["losses"])):
         assert np.allclose(o["scores"][s], c["scores"][s], atol=5e-5, rtol=1e-4)
     for k, v in c["grad0"].items():
-        assert np.allclose(o["grads"][0][k], v, atol=1e-6 + 1e-4 * np.abs(v).max(), rtol=0), k
+        assert np.allclose(sub(o["grads"][0][k]), v, atol=1e-6 + 1e-4 * np.abs(v).max(), rtol=0), k
     for k, v in c["final"].items():
         if k.endswith("num_batches_tracked"):
             assert int(o["state"][k]) == int(v) == 100 + len(c["losses"])
         else:
-            assert np.allclose(o["state"][k], v, atol=2e-5, rtol=1e-5), k
+            assert np.allclose(sub(o["state"][k]), v, atol=2e-5, rtol=1e-5), k
 
 
 def test_sgd_rule_weight_decay_momentum_nesterov():

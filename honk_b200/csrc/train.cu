@@ -393,6 +393,31 @@ __global__ void maxpool_bwd_kernel(const float* __restrict__ dy, const int* __re
   }
 }
 
+// y[b][o] = sum_k x[b][k] * W[o][k] + bias[o] for a batch far smaller than the feature count (the cnn-* heads: 26 624 features
+// into 12 labels for cnn-trad-pool2).  grid (Out, ceil(B / 8)): a block reads W's row once against 8 rows of x, k strided
+// over its 256 threads, and reduces in a fixed order.
+constexpr int LF_BT = 8;
+__global__ void __launch_bounds__(256) linear_fwd_kernel(const float* __restrict__ x, const float* __restrict__ W, const float* __restrict__ bias,
+                                                         float* __restrict__ y, int B, int In, int Out) {
+  __shared__ double sh[8];
+  const int o = blockIdx.x, b0 = blockIdx.y * LF_BT;
+  const float* wr = W + static_cast<long long>(o) * In;
+  float acc[LF_BT];
+#pragma unroll
+  for (int j = 0; j < LF_BT; ++j) acc[j] = 0.f;
+  for (int k = threadIdx.x; k < In; k += 256) {
+    const float wv = __ldg(wr + k);
+#pragma unroll
+    for (int j = 0; j < LF_BT; ++j)
+      if (b0 + j < B) acc[j] = fmaf(__ldg(x + static_cast<long long>(b0 + j) * In + k), wv, acc[j]);
+  }
+#pragma unroll
+  for (int j = 0; j < LF_BT; ++j) {
+    const double t = block_sum(static_cast<double>(acc[j]), sh);
+    if (threadIdx.x == 0 && b0 + j < B) y[static_cast<long long>(b0 + j) * Out + o] = static_cast<float>(t + static_cast<double>(bias[o]));
+  }
+}
+
 // dx[b][i] = sum_o dy[b][o] * W[o][i]
 __global__ void linear_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ W, float* __restrict__ dx, int B, int In, int Out) {
   const long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
@@ -609,8 +634,9 @@ void carve_cnn(const honk_trainer* t, int64_t B, Arena& a, CnnWs& w) {
 int linear_fwd(const honk_trainer* t, int wi, const float* x, float* y, int B, cudaStream_t s) {
   const TrainParam& W = t->params[wi];
   const int Out = static_cast<int>(t->params[wi + 1].numel), In = static_cast<int>(W.numel / Out);
-  ConvGeom g{B, In, 1, 1, Out, 1, 1, 1, 1, 0, 0, 1, 1, 1, 1};
-  return conv2d_f32(x, W.p, t->params[wi + 1].p, y, g, false, s);
+  linear_fwd_kernel<<<dim3(Out, ceil_div(B, LF_BT)), 256, 0, s>>>(x, W.p, t->params[wi + 1].p, y, B, In, Out);
+  HONK_LAUNCH_CHECK();
+  return HONK_OK;
 }
 
 // gradients of a Linear layer: dW, db always; dx when asked for

@@ -2,6 +2,8 @@
 // and the softmax/argmax label kernel.  See generic_ops.cuh.
 #include "generic_ops.cuh"
 
+#include <cstdlib>
+
 namespace honk {
 
 namespace {
@@ -91,6 +93,119 @@ __global__ void __launch_bounds__(256) conv_gemm_f32_kernel(const float* __restr
 #pragma unroll
     for (int j = 0; j < TN; ++j) {
       const int n = n0 + tn + j;
+      if (n >= N) continue;
+      float v = acc[i][j] + (bias ? __ldg(bias + n) : 0.f);
+      if (relu) v = fmaxf(v, 0.f);
+      out[(b * N + n) * HWo + pos] = v;
+    }
+  }
+}
+
+// The same GEMM for large problems (training batches, the FP32 reference path at serving batch sizes): 128 x (16 TN) x 16
+// tiles, 8 x TN outputs per thread, the next stage's global loads in flight under the current stage's FMAs (two shared-memory
+// buffers, one barrier per stage).  Every output is still ONE fmaf chain over k in ascending order, so the result is
+// bit-identical to conv_gemm_f32_kernel's.
+constexpr int GB_BM = 128, GB_BK = 16, GB_MAXTAPS = 256;
+
+template <int TN>
+__global__ void __launch_bounds__(256) conv_gemm_f32_big_kernel(const float* __restrict__ in, const float* __restrict__ w,
+                                                                const float* __restrict__ bias, float* __restrict__ out, ConvGeom g, int relu) {
+  constexpr int BNT = 16 * TN;
+  __shared__ __align__(16) float As[2][GB_BK][GB_BM + 4];
+  __shared__ __align__(16) float Bs[2][GB_BK][BNT + 4];
+  __shared__ short2 taps[GB_MAXTAPS];                          // (kh * dh, kw * dw) of tap r = kh * KW + kw
+  const long long M = static_cast<long long>(g.B) * g.Ho * g.Wo;
+  const int N = g.Cout, KHW = g.KH * g.KW, K = g.Cin * KHW;
+  const int tid = threadIdx.x;
+  const long long m0 = static_cast<long long>(blockIdx.x) * GB_BM;
+  const int n0 = blockIdx.y * BNT;
+  for (int r = tid; r < KHW; r += 256) taps[r] = make_short2(static_cast<short>((r / g.KW) * g.dh), static_cast<short>((r % g.KW) * g.dw));
+
+  // A-load role: row la_m of the tile, the 8 consecutive k's [la_k0, la_k0 + 8) of every stage
+  const int la_m = tid & 127, la_k0 = (tid >> 7) * 8;
+  const long long gm = m0 + la_m;
+  const bool m_ok = gm < M;
+  int hi0 = 0, wi0 = 0;
+  const float* in_b = in;
+  if (m_ok) {
+    const int wo = static_cast<int>(gm % g.Wo);
+    const long long r = gm / g.Wo;
+    const int ho = static_cast<int>(r % g.Ho);
+    hi0 = ho * g.sh - g.ph;
+    wi0 = wo * g.sw - g.pw;
+    in_b = in + (r / g.Ho) * g.Cin * g.H * g.W;
+  }
+  int a_ci = la_k0 / KHW, a_r = la_k0 - a_ci * KHW;            // (channel, tap) of this thread's first k of the current stage
+  // B-load role: k = tid % 16, rows tid / 16 + 16 j
+  const int lb_k = tid & 15, lb_n = tid >> 4;
+  // compute role: rows tx*4 + i and 64 + tx*4 + i, columns ty*TN + j
+  const int tx = tid & 15, ty = tid >> 4;
+  float acc[8][TN];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+  float pa[8], pb[TN];
+  auto fetch = [&](int k0) {
+    int ci = a_ci, r = a_r;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float v = 0.f;
+      if (m_ok && k0 + la_k0 + i < K) {
+        const short2 t = taps[r];
+        const int hi = hi0 + t.x, wi = wi0 + t.y;
+        if (hi >= 0 && hi < g.H && wi >= 0 && wi < g.W) v = __ldg(in_b + (static_cast<long long>(ci) * g.H + hi) * g.W + wi);
+      }
+      pa[i] = v;
+      if (++r == KHW) { r = 0; ++ci; }
+    }
+    a_r += GB_BK;                                               // this thread's first k of the NEXT stage
+    while (a_r >= KHW) { a_r -= KHW; ++a_ci; }
+#pragma unroll
+    for (int j = 0; j < TN; ++j) {
+      const int n = n0 + lb_n + 16 * j, k = k0 + lb_k;
+      pb[j] = (n < N && k < K) ? __ldg(w + static_cast<long long>(n) * K + k) : 0.f;
+    }
+  };
+  auto stash = [&](int buf) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) As[buf][la_k0 + i][la_m] = pa[i];
+#pragma unroll
+    for (int j = 0; j < TN; ++j) Bs[buf][lb_k][lb_n + 16 * j] = pb[j];
+  };
+  __syncthreads();                                              // taps
+  fetch(0);
+  stash(0);
+  __syncthreads();
+  const int n_stages = (K + GB_BK - 1) / GB_BK;
+  for (int st = 0; st < n_stages; ++st) {
+    const int buf = st & 1;
+    if (st + 1 < n_stages) fetch((st + 1) * GB_BK);
+#pragma unroll
+    for (int kk = 0; kk < GB_BK; ++kk) {
+      const float4 a0 = *reinterpret_cast<const float4*>(&As[buf][kk][tx * 4]);
+      const float4 a1 = *reinterpret_cast<const float4*>(&As[buf][kk][64 + tx * 4]);
+      const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+      float b[TN];
+#pragma unroll
+      for (int j = 0; j < TN; ++j) b[j] = Bs[buf][kk][ty * TN + j];
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    if (st + 1 < n_stages) stash(buf ^ 1);
+    __syncthreads();
+  }
+  const long long HWo = static_cast<long long>(g.Ho) * g.Wo;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const long long m = m0 + (i < 4 ? tx * 4 + i : 64 + tx * 4 + (i - 4));
+    if (m >= M) continue;
+    const long long b = m / HWo, pos = m - b * HWo;
+#pragma unroll
+    for (int j = 0; j < TN; ++j) {
+      const int n = n0 + ty * TN + j;
       if (n >= N) continue;
       float v = acc[i][j] + (bias ? __ldg(bias + n) : 0.f);
       if (relu) v = fmaxf(v, 0.f);
@@ -260,6 +375,17 @@ int conv2d_f32(const float* in, const float* w, const float* bias, float* out, c
   const long long M = static_cast<long long>(g.B) * g.Ho * g.Wo;
   if (M == 0) return HONK_OK;
   HONK_CHECK(g.Ho > 0 && g.Wo > 0, HONK_ERR_INVALID, "convolution output is empty");
+  static const bool no_big = getenv("HONK_F32_SMALL_TILES") && atoi(getenv("HONK_F32_SMALL_TILES")) != 0;
+  if (!no_big && M >= 8192 && g.Cout >= 16 && g.Cin * g.KH * g.KW >= 16 && g.KH * g.KW <= GB_MAXTAPS && g.KH * g.dh < 32768 &&
+      g.KW * g.dw < 32768) {
+    const int tn = g.Cout > 48 ? 4 : (g.Cout > 32 ? 3 : 2);
+    dim3 gb(static_cast<unsigned>((M + GB_BM - 1) / GB_BM), ceil_div(g.Cout, 16 * tn));
+    if (tn == 4) conv_gemm_f32_big_kernel<4><<<gb, 256, 0, s>>>(in, w, bias, out, g, relu ? 1 : 0);
+    else if (tn == 3) conv_gemm_f32_big_kernel<3><<<gb, 256, 0, s>>>(in, w, bias, out, g, relu ? 1 : 0);
+    else conv_gemm_f32_big_kernel<2><<<gb, 256, 0, s>>>(in, w, bias, out, g, relu ? 1 : 0);
+    HONK_LAUNCH_CHECK();
+    return HONK_OK;
+  }
   dim3 grid(static_cast<unsigned>((M + BM - 1) / BM), ceil_div(g.Cout, BN));
   conv_gemm_f32_kernel<<<grid, 256, 0, s>>>(in, w, bias, out, g, relu ? 1 : 0);
   HONK_LAUNCH_CHECK();

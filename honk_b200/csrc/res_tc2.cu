@@ -108,6 +108,7 @@ struct T2Params {
   int col_bytes;                  // NCG * plane_rows * 16
   int stage_stride, wbytes;       // wbytes = size of one weight buffer (largest layer)
   long long* dbg;                 // optional [gridDim][T2_NDBG] cycle counters (HONK_TC2_DEBUG)
+  int l2hint;                     // 1: evict_first on the x0 stream, evict_last on activation stores and loads
   int mode;                       // debug kernel only (results are garbage): 1 = MMA issue alone (no copies, waits or epilogue),
                                   // 2 = epilogue without its global loads/stores and math, 3 = epilogue without its TMEM loads/stores
   // Per-layer tables live in the kernel parameter (constant) bank so that the MMA warp's descriptor
@@ -131,6 +132,27 @@ __device__ __forceinline__ uint32_t keep(uint32_t x) {
 __device__ __forceinline__ void bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t mbar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
                "l"(src), "r"(bytes), "r"(mbar)
+               : "memory");
+}
+// L2 eviction-priority hints (HONK_TC2_L2HINT, default on): the activation ring (66 MB) is rewritten in place every two layers
+// and should stay resident, while x0 streams through once.
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void bulk_load_hint(uint32_t dst, const void* src, uint32_t bytes, uint32_t mbar, uint64_t pol) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(mbar), "l"(pol)
+               : "memory");
+}
+__device__ __forceinline__ void stcg16_hint(void* p, const uint4& v, uint64_t pol) {
+  asm volatile("st.global.cg.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "l"(pol)
                : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
@@ -328,6 +350,8 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
           }
           const int d = ly.d;
           const bool from_x0 = ly.flags & 4;
+          // x0 and the pooled models' y0 image are read once; the activation ring is re-read by the next layer and rewritten
+          const uint64_t in_pol = (from_x0 || (ly.flags & 8)) ? l2_policy_evict_first() : l2_policy_evict_last();
           const uint32_t bytes = from_x0 ? x0_col_bytes : (NCG - 1) * plane_bytes + (p.H + 2 * d) * 16;
           const long long colb = from_x0 ? x0_col_bytes : p.col_bytes;
           const int nseg = ly.n_seg[rank];
@@ -358,7 +382,8 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
                 }
                 const uint32_t full = a_full + 8 * st;
                 mbar_expect_tx(full, bytes);
-                bulk_load(smem_u32(stages + st * p.stage_stride), in + (r + (jin0 + t) * d) * colb, bytes, full);
+                if (p.l2hint) bulk_load_hint(smem_u32(stages + st * p.stage_stride), in + (r + (jin0 + t) * d) * colb, bytes, full, in_pol);
+                else bulk_load(smem_u32(stages + st * p.stage_stride), in + (r + (jin0 + t) * d) * colb, bytes, full);
               }
             }
           }
@@ -517,6 +542,7 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
     // accumulator columns): a column is drained in 1/NG of the time of a whole-column pass, which is what the 8-slot ring
     // needs.
     constexpr int HC = NCG / NG, HB = HC * 8;
+    const uint64_t st_pol = l2_policy_evict_last();
     const int ew = warp - 2, quad = warp & 3, half = ew >> 2;   // half = this warp's group
     const int cg0 = half * HC;
     const int h = quad * 32 + lane;
@@ -618,7 +644,10 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
                   for (int k = 0; k < 4; ++k)
                     w4[k] = relu_add_h2(pack_h2(__uint_as_float(v[c * 8 + 2 * k]), __uint_as_float(v[c * 8 + 2 * k + 1])), rr[k]);
                   if (c == HC - 1 && half == NG - 1) w4[3] = 0x3C003C00u;   // the two constant-one channels (last channel group)
-                  if (valid) stcg16(outb + off + c * plane_bytes, make_uint4(w4[0], w4[1], w4[2], w4[3]));
+                  if (valid) {
+                    if (p.l2hint) stcg16_hint(outb + off + c * plane_bytes, make_uint4(w4[0], w4[1], w4[2], w4[3]), st_pol);
+                    else stcg16(outb + off + c * plane_bytes, make_uint4(w4[0], w4[1], w4[2], w4[3]));
+                  }
                 }
               } else if (valid) {
 #pragma unroll
@@ -1794,6 +1823,8 @@ int res_tc2_forward(const ResTc2Plan* p, const float* d_mfcc, int64_t n_clips, f
   a.wbytes = p->wbytes;
   a.dbg = nullptr;
   a.mode = 0;
+  static const int l2hint = getenv("HONK_TC2_L2HINT") ? atoi(getenv("HONK_TC2_L2HINT")) : 1;
+  a.l2hint = l2hint;
   static long long* s_dbg = nullptr;
   const char* dbg_env = getenv("HONK_TC2_DEBUG");
   const bool dbg = dbg_env && atoi(dbg_env);

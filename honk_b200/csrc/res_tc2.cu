@@ -350,8 +350,10 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
           }
           const int d = ly.d;
           const bool from_x0 = ly.flags & 4;
-          // x0 and the pooled models' y0 image are read once; the activation ring is re-read by the next layer and rewritten
-          const uint64_t in_pol = (from_x0 || (ly.flags & 8)) ? l2_policy_evict_first() : l2_policy_evict_last();
+          // x0 is read once; the activation ring is re-read by the next layer and rewritten.  The pooled models' y0 image is read
+          // twice (layer 1's input, layer 2's residual) shortly after each other: no hint (evict_first cost 0.6 GB of re-reads)
+          const uint64_t in_pol = from_x0 ? l2_policy_evict_first() : l2_policy_evict_last();
+          const bool hint_in = p.l2hint && !(ly.flags & 8);
           const uint32_t bytes = from_x0 ? x0_col_bytes : (NCG - 1) * plane_bytes + (p.H + 2 * d) * 16;
           const long long colb = from_x0 ? x0_col_bytes : p.col_bytes;
           const int nseg = ly.n_seg[rank];
@@ -382,7 +384,7 @@ __global__ void __launch_bounds__(t2_threads(NCG), 1) tc2_res_kernel(const __gri
                 }
                 const uint32_t full = a_full + 8 * st;
                 mbar_expect_tx(full, bytes);
-                if (p.l2hint) bulk_load_hint(smem_u32(stages + st * p.stage_stride), in + (r + (jin0 + t) * d) * colb, bytes, full, in_pol);
+                if (hint_in) bulk_load_hint(smem_u32(stages + st * p.stage_stride), in + (r + (jin0 + t) * d) * colb, bytes, full, in_pol);
                 else bulk_load(smem_u32(stages + st * p.stage_stride), in + (r + (jin0 + t) * d) * colb, bytes, full);
               }
             }

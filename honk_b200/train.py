@@ -5,7 +5,7 @@ size) but argmax, the label comparison and the CrossEntropyLoss run in one kerne
 (``honk_eval_metrics``), and a loader may hand raw PCM ``[B, 16000]`` instead of MFCCs: the batched front end then
 replaces ``SpeechDataset.collate_fn``'s per-clip ``compute_mfccs`` + ``torch.cat`` (model.py:253-265).
 
-The training half (train.py:87-163) for the res* family: ``SgdTrainer.step`` replaces the body of the reference's inner
+The training half (train.py:87-163): ``SgdTrainer.step`` replaces the body of the reference's inner
 loop (model.train(); scores = model(model_in); loss = criterion(scores, labels); loss.backward(); optimizer.step();
 train.py:127-139) with one native call, ``train`` keeps the loop around it (learning-rate schedule that rebuilds the
 optimiser, dev-set evaluation every ``dev_every`` epochs, best model saved).  Dataset walking (SpeechDataset.splits) stays
@@ -82,7 +82,7 @@ def evaluate(config, model=None, test_loader=None, audio_processor=None):
 
 class SgdTrainer:
     """The reference's ``torch.optim.SGD(model.parameters(), lr, momentum, weight_decay, nesterov)`` plus the
-    forward / loss / backward it is stepped with (train.py:100, 127-139), for a ``SpeechResModel`` on the GPU.
+    forward / loss / backward it is stepped with (train.py:100, 127-139), for a ``SpeechResModel`` or ``SpeechModel`` on the GPU.
 
     The trainer owns device copies of the parameters, gradients, momentum buffers and BatchNorm running statistics
     (``honk_trainer``); ``sync()`` writes the current weights and statistics back into the module (done automatically by

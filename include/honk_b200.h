@@ -238,7 +238,7 @@ HONK_API int honk_load_audio(const float* d_pcm, int64_t n_clips, int64_t clip_s
                     const float* d_bg_noise, int32_t input_length, float* d_out, void* stream);
 
 /* ------------------------------------------------------------------------------------------
- * Training step of the res* family (replaces the body of the reference's
+ * Training step (replaces the body of the reference's
  * training loop, utils/train.py:127-139: model.train(), scores = model(model_in), CrossEntropyLoss,
  * loss.backward(), torch.optim.SGD.step()).  FP32 on the CUDA cores; BatchNorm2d(affine=False) in
  * training mode (batch statistics, running statistics moved by momentum 0.1; utils/model.py:98).

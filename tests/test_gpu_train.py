@@ -125,14 +125,16 @@ def test_batch64_against_oracle_and_schedule_reset():
             assert rel_err(got, t) <= 5 * e_ref + 2e-4, (k, rel_err(got, t), e_ref)
 
 
-def test_training_loss_falls_and_train_loop_runs(tmp_path, capsys):
+@pytest.mark.parametrize("name,lrs,fall,min_acc", [("res8-narrow", [0.1, 0.02], 0.6, 0.5), ("cnn-trad-pool2", [0.002, 0.0005], 0.9, 0.2)])
+def test_training_loss_falls_and_train_loop_runs(tmp_path, capsys, name, lrs, fall, min_acc):
     """train() (train.py:87-163) end to end on the class-structured synthetic clips: loss falls, dev accuracy is
-    printed, the best model is saved in the reference's bare-state_dict format and reloads."""
+    printed, the best model is saved in the reference's bare-state_dict format and reloads.  cnn-trad-pool2 is the
+    reference's default training model (train.py:168); its Dropout masks are the library's own draws here."""
     import honk_b200 as hb
     from honk_b200 import train
-    cfg = dict(hb.find_config("res8-narrow"))
-    cfg.update(n_labels=12, lr=[0.1, 0.02], schedule=[30], n_epochs=4, dev_every=2, momentum=0.9, weight_decay=1e-5,
-               use_nesterov=False, output_file=str(tmp_path / "model.pt"), input_file="", model_class=hb.find_model("res8-narrow"))
+    cfg = dict(hb.find_config(name))
+    cfg.update(n_labels=12, lr=lrs, schedule=[30], n_epochs=4, dev_every=2, momentum=0.9, weight_decay=1e-5,
+               use_nesterov=False, output_file=str(tmp_path / "model.pt"), input_file="", model_class=hb.find_model(name))
     clips, labels = synth.make_clips(12 * 64, start=820000, labelled=True)
     pre = hb.AudioPreprocessor()
     mfcc = pre.compute_mfccs_batch(torch.from_numpy(clips).cuda()).float()
@@ -142,17 +144,17 @@ def test_training_loss_falls_and_train_loop_runs(tmp_path, capsys):
     torch.manual_seed(0)
     best = train.train(cfg, loader, dev_loader=dev)
     out = capsys.readouterr().out
-    assert "changing learning rate to 0.02" in out and "final dev accuracy" in out and "saving best model..." in out
-    first = float(out.split("train step #1 ")[1].split("loss: ")[1].split()[0])
-    last = float(out.split("train step #40 ")[1].split("loss: ")[1].split()[0])
-    assert last < 0.6 * first, (first, last)
+    assert ("changing learning rate to %s" % lrs[1]) in out and "final dev accuracy" in out and "saving best model..." in out
+    losses = [float(out.split("train step #%d " % i)[1].split("loss: ")[1].split()[0]) for i in range(1, 41)]
+    first, last = float(np.mean(losses[:4])), float(np.mean(losses[-4:]))
+    assert last < fall * first, (first, last)
     again = cfg["model_class"](cfg)
     again.load(cfg["output_file"])
     again.cuda().eval()
     best.eval()
     assert torch.allclose(again(dev[0][0]), best(dev[0][0]), atol=1e-5)
     acc = float((best(dev[0][0]).argmax(1).cpu() == dev[0][1]).float().mean())
-    assert acc > 0.5, acc
+    assert acc > min_acc, acc
 
 
 def test_trainer_errors():

@@ -125,7 +125,7 @@ def test_batch64_against_oracle_and_schedule_reset():
             assert rel_err(got, t) <= 5 * e_ref + 2e-4, (k, rel_err(got, t), e_ref)
 
 
-@pytest.mark.parametrize("name,lrs,fall,min_acc", [("res8-narrow", [0.1, 0.02], 0.6, 0.5), ("cnn-trad-pool2", [0.002, 0.0005], 0.9, 0.2)])
+@pytest.mark.parametrize("name,lrs,fall,min_acc", [("res8-narrow", [0.1, 0.02], 0.65, 0.3), ("cnn-trad-pool2", [0.002, 0.0005], 0.5, 0.6)])
 def test_training_loss_falls_and_train_loop_runs(tmp_path, capsys, name, lrs, fall, min_acc):
     """train() (train.py:87-163) end to end on the class-structured synthetic clips: loss falls, dev accuracy is
     printed, the best model is saved in the reference's bare-state_dict format and reloads.  cnn-trad-pool2 is the

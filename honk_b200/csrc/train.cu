@@ -12,6 +12,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <vector>
 
 using namespace honk;
@@ -244,6 +245,105 @@ __global__ void __launch_bounds__(WG_THREADS) wgrad_gemm_kernel(const float* __r
 #pragma unroll
     for (int j = 0; j < TN; ++j) {
       const int n = n0 + tn + j;
+      if (n < N) part[(static_cast<long long>(sp) * Cout + m) * N + n] = acc[i][j];
+    }
+  }
+}
+
+// The same GEMM with (16 TM) x 128 x 16 tiles, TM x 8 outputs per thread and the next stage's loads in flight under the FMAs
+// (two shared-memory buffers, one barrier per stage): used when there are at least 128 (ci, tap) columns.  Each partial sum is
+// still one fmaf chain over the split's positions in ascending order (the number of splits may differ from the small kernel's).
+constexpr int WGB_BN = 128;
+
+template <int TM>
+__global__ void __launch_bounds__(WG_THREADS) wgrad_gemm_big_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                                                                    float* __restrict__ part, ConvGeom g, long long k_per_split) {
+  constexpr int BM = 16 * TM;
+  __shared__ __align__(16) float As[2][WG_BK][BM + 4];
+  __shared__ __align__(16) float Bs[2][WG_BK][WGB_BN + 4];
+  const int tid = threadIdx.x;
+  const int HWo = g.Ho * g.Wo, HWi = g.H * g.W, KHW = g.KH * g.KW, N = g.Cin * KHW, Cout = g.Cout;
+  const long long K = static_cast<long long>(g.B) * HWo;
+  const int n0 = blockIdx.x * WGB_BN, m0 = blockIdx.z * BM, sp = blockIdx.y;
+  const long long k_lo = sp * k_per_split, k_hi = min(K, k_lo + k_per_split);
+  const int kk = tid & 15, row = tid >> 4;                       // load roles: position kk of the stage, rows / columns row + 16 i
+  long long pos = k_lo + kk;
+  int b = static_cast<int>(pos / HWo);
+  int rem = static_cast<int>(pos - static_cast<long long>(b) * HWo);
+  int ho = rem / g.Wo, wo = rem - ho * g.Wo;
+  int b_off[8], b_d[8];                                          // per column: ci * H * W, and (row offset << 16 | column offset + 32768)
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int n = n0 + row + 16 * i;
+    if (n < N) {
+      const int ci = n / KHW, tap = n - ci * KHW, kh = tap / g.KW, kw = tap - kh * g.KW;
+      b_off[i] = ci * HWi;
+      b_d[i] = ((kh * g.dh - g.ph + 16384) << 16) | (kw * g.dw - g.pw + 16384);
+    } else {
+      b_off[i] = -1; b_d[i] = 0;
+    }
+  }
+  const int tx = tid & 15, ty = tid >> 4;                        // compute roles: columns tx*4 + j and 64 + tx*4 + j, rows ty*TM + i
+  float acc[TM][8];
+#pragma unroll
+  for (int i = 0; i < TM; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+  float pa[TM], pb[8];
+  auto fetch = [&](long long k0) {
+    const bool k_ok = k0 + kk < k_hi;
+#pragma unroll
+    for (int i = 0; i < TM; ++i) {
+      const int m = m0 + row + 16 * i;
+      pa[i] = (k_ok && m < Cout) ? __ldg(dy + (static_cast<long long>(b) * Cout + m) * HWo + ho * g.Wo + wo) : 0.f;
+    }
+    const float* xb = x + static_cast<long long>(b) * g.Cin * HWi;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int hh = ho * g.sh + (b_d[i] >> 16) - 16384, ww = wo * g.sw + (b_d[i] & 0xFFFF) - 16384;
+      pb[i] = (k_ok && b_off[i] >= 0 && hh >= 0 && hh < g.H && ww >= 0 && ww < g.W) ? __ldg(xb + b_off[i] + hh * g.W + ww) : 0.f;
+    }
+    wo += WG_BK;                                                 // this thread's position of the NEXT stage
+    while (wo >= g.Wo) { wo -= g.Wo; ++ho; }
+    while (ho >= g.Ho) { ho -= g.Ho; ++b; }
+  };
+  auto stash = [&](int buf) {
+#pragma unroll
+    for (int i = 0; i < TM; ++i) As[buf][kk][row + 16 * i] = pa[i];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) Bs[buf][kk][row + 16 * i] = pb[i];
+  };
+  fetch(k_lo);
+  stash(0);
+  __syncthreads();
+  int st = 0;
+  for (long long k0 = k_lo; k0 < k_hi; k0 += WG_BK, ++st) {
+    const int buf = st & 1;
+    const bool more = k0 + WG_BK < k_hi;
+    if (more) fetch(k0 + WG_BK);
+#pragma unroll
+    for (int q = 0; q < WG_BK; ++q) {
+      const float4 b0 = *reinterpret_cast<const float4*>(&Bs[buf][q][tx * 4]);
+      const float4 b1 = *reinterpret_cast<const float4*>(&Bs[buf][q][64 + tx * 4]);
+      const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+      float a[TM];
+#pragma unroll
+      for (int i = 0; i < TM; ++i) a[i] = As[buf][q][ty * TM + i];
+#pragma unroll
+      for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a[i], bb[j], acc[i][j]);
+    }
+    if (more) stash(buf ^ 1);
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < TM; ++i) {
+    const int m = m0 + ty * TM + i;
+    if (m >= Cout) continue;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int n = n0 + (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
       if (n < N) part[(static_cast<long long>(sp) * Cout + m) * N + n] = acc[i][j];
     }
   }
@@ -527,7 +627,8 @@ struct TrainWs {
 int wgrad_bm(int Cout) { return Cout <= 32 ? 32 : 64; }
 
 int wgrad_split(int n_cols, int Cout, long long K) {          // n_cols = Cin * KH * KW
-  const int tiles = ceil_div(n_cols, WG_BN) * ceil_div(Cout, wgrad_bm(Cout));
+  const int tiles = n_cols >= 128 && Cout > 32 ? ceil_div(n_cols, 128) * ceil_div(Cout, Cout > 48 ? 64 : 48)
+                                                : ceil_div(n_cols, WG_BN) * ceil_div(Cout, wgrad_bm(Cout));
   long long s = ceil_div(148 * 6, tiles);
   s = std::max<long long>(1, std::min<long long>(s, std::min<long long>((K + 255) / 256, 1024)));
   return static_cast<int>(s);
@@ -561,13 +662,28 @@ void carve(const honk_trainer* t, int64_t B, Arena& a, TrainWs& w) {
   w.wpart = a.take<float>(std::max<int64_t>(static_cast<int64_t>(w.wsplit_main) * C * C * 9, static_cast<int64_t>(w.wsplit_stem) * C * 9));
 }
 
+bool wgrad_big(const ConvGeom& g) {
+  static const bool off = getenv("HONK_WGRAD_SMALL_TILES") && atoi(getenv("HONK_WGRAD_SMALL_TILES")) != 0;
+  return !off && g.Cin * g.KH * g.KW >= 128 && g.Cout > 32 && g.KH * g.dh < 16384 && g.KW * g.dw < 16384 && g.ph < 16384 && g.pw < 16384;
+}
+int wgrad_big_tm(int Cout) { return Cout > 48 ? 4 : (Cout > 32 ? 3 : 2); }
+
 int wgrad(const float* x, const float* dy, float* part, float* dw, const ConvGeom& g, int nsplit, cudaStream_t s) {
   const long long K = static_cast<long long>(g.B) * g.Ho * g.Wo;
   const long long per = align_up((K + nsplit - 1) / nsplit, WG_BK);
-  const int bm = wgrad_bm(g.Cout), n = g.Cout * g.Cin * g.KH * g.KW;
-  const dim3 grid(ceil_div(g.Cin * g.KH * g.KW, WG_BN), nsplit, ceil_div(g.Cout, bm));
-  if (bm == 32) wgrad_gemm_kernel<32><<<grid, WG_THREADS, 0, s>>>(x, dy, part, g, per);
-  else wgrad_gemm_kernel<64><<<grid, WG_THREADS, 0, s>>>(x, dy, part, g, per);
+  const int n = g.Cout * g.Cin * g.KH * g.KW;
+  if (wgrad_big(g)) {
+    const int tm = wgrad_big_tm(g.Cout);
+    const dim3 grid(ceil_div(g.Cin * g.KH * g.KW, WGB_BN), nsplit, ceil_div(g.Cout, 16 * tm));
+    if (tm == 4) wgrad_gemm_big_kernel<4><<<grid, WG_THREADS, 0, s>>>(x, dy, part, g, per);
+    else if (tm == 3) wgrad_gemm_big_kernel<3><<<grid, WG_THREADS, 0, s>>>(x, dy, part, g, per);
+    else wgrad_gemm_big_kernel<2><<<grid, WG_THREADS, 0, s>>>(x, dy, part, g, per);
+  } else {
+    const int bm = wgrad_bm(g.Cout);
+    const dim3 grid(ceil_div(g.Cin * g.KH * g.KW, WG_BN), nsplit, ceil_div(g.Cout, bm));
+    if (bm == 32) wgrad_gemm_kernel<32><<<grid, WG_THREADS, 0, s>>>(x, dy, part, g, per);
+    else wgrad_gemm_kernel<64><<<grid, WG_THREADS, 0, s>>>(x, dy, part, g, per);
+  }
   HONK_LAUNCH_CHECK();
   wgrad_reduce_kernel<<<ceil_div(n, 256), 256, 0, s>>>(part, dw, nsplit, n);
   HONK_LAUNCH_CHECK();

@@ -382,3 +382,33 @@ def test_cnn_family_on_tensor_cores(golden_dir, name, monkeypatch):
     import honk_b200 as hb
     yp = build(name, cfg12, sd12, 0).forward_pcm(torch.from_numpy(clips).cuda(), hb.AudioPreprocessor()).cpu().numpy()
     assert np.abs(yp - ref).max() / np.abs(ref).max() <= TOL["tcgen05-f16"]
+
+
+@pytest.mark.parametrize("name,n", [("res15", 8192), ("res8", 16384), ("cnn-trad-pool2", 4096), ("cnn-tpool2", 4096)])
+def test_full_size_batch_properties(name, n):
+    """Size-independent properties at BASELINE.json's batch sizes (where the oracle would take minutes): a clip's logits do
+    not depend on its position in the batch or on its neighbours (permutation equivariance; sub-batch == slice of the
+    batch), duplicated clips give identical rows, and the fused PCM entry equals front end + model.  Sums that go through
+    atomics (the res* global mean, then the folded last BatchNorm's mean - mu cancellation) differ in the last bits from run
+    to run - 2.3e-5 of the logit scale measured - hence 1e-4 of the scale for res* and 1e-5 for cnn-*, not equality."""
+    import honk_b200 as hb
+    cfg = dict(hb.find_config(name))
+    cfg["n_labels"] = 12
+    pre = hb.AudioPreprocessor()
+    base = synth.make_clips(1024, start=500000)
+    mf = pre.compute_mfccs_batch(torch.from_numpy(base[:16]).cuda()).cpu().numpy()
+    m = build(name, cfg, synth.make_state_dict(name, cfg, seed=9, calib_mfcc=mf), 0)
+    clips = np.tile(base, (n // 1024, 1))                                # every clip appears n / 1024 times
+    rng = np.random.default_rng(5)
+    perm = rng.permutation(n)
+    x = torch.from_numpy(clips).cuda()
+    y = m.forward_pcm(x, pre)
+    tol = (1e-4 if name.startswith("res") else 1e-5) * float(y.abs().max())
+    assert torch.isfinite(y).all()
+    yp = m.forward_pcm(x[torch.from_numpy(perm).cuda()], pre)
+    assert float((yp - y[torch.from_numpy(perm).cuda()]).abs().max()) <= tol             # permutation equivariance
+    assert float((y.view(n // 1024, 1024, -1) - y[:1024]).abs().max()) <= tol             # duplicates agree
+    sub = m.forward_pcm(x[1000:1000 + 777], pre)                                         # a ragged sub-batch
+    assert float((sub - y[1000:1000 + 777]).abs().max()) <= tol
+    two_step = m(pre.compute_mfccs_batch(x[:2048]))
+    assert float((two_step - y[:2048]).abs().max()) <= tol

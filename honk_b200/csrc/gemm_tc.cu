@@ -48,6 +48,12 @@ struct GemmTcParams {
   int n_store;                 // columns of C that exist (<= ldc); columns >= n_store are not written
   int relu, out_f32;
   long long n_mtiles;
+  // implicit mode (stride-1 convolutions over a planar activation, no materialised A): A plane (tap, cg) of the tile of clip
+  // `clip` starting at flat input row r0 is the 128 rows [r0 + kh * Wp + kw, +128) of plane cg of that clip's image
+  //   Ap[clip][cg][R_alloc rows][8 halves],   row = h * Wp + w over the (pooled) input map.
+  // Output row r0 + i is output position (ho, wo) = ((r0 + i) / Wp, (r0 + i) % Wp); rows with wo >= Wo or ho >= Ho are junk.
+  const unsigned char* Ap;
+  int imp, NCG, R_alloc, Wp, KW, n_taps, tiles_per_clip, Ho, Wo;
 };
 
 __device__ __forceinline__ uint32_t gt_elect_one() {
@@ -96,21 +102,33 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const __grid_con
 
   if (warp == 0) {
     // ======================================= producer =======================================
-    if (lane == 0) {
-      uint32_t it = 0;
-      for (long long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        const long long mt = t / p.n_ntiles;
-        const int nt = static_cast<int>(t - mt * p.n_ntiles);
-        const unsigned char* At = p.A + mt * (static_cast<long long>(p.KP) * 2048);
-        const unsigned char* Bt = p.B + static_cast<long long>(nt) * p.KP * p.NT * 16;
-        for (int ks = 0; ks < n_ks; ++ks, ++it) {
-          const uint32_t s = it % GT_NSTAGE;
+    // lane 0 arms the stage's barrier and copies B (and A in the materialised mode); in implicit mode lane i copies plane i of
+    // the stage (8 bulk copies of 2 KB issued side by side instead of one lane walking them)
+    uint32_t it = 0;
+    for (long long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+      const long long mt = t / p.n_ntiles;
+      const int nt = static_cast<int>(t - mt * p.n_ntiles);
+      const unsigned char* At = p.A + mt * (static_cast<long long>(p.KP) * 2048);
+      const unsigned char* Bt = p.B + static_cast<long long>(nt) * p.KP * p.NT * 16;
+      const long long clip = p.imp ? mt / p.tiles_per_clip : 0;
+      const unsigned char* Ac = p.imp ? p.Ap + (clip * p.NCG * p.R_alloc + (mt - clip * p.tiles_per_clip) * 128) * 16 : nullptr;
+      for (int ks = 0; ks < n_ks; ++ks, ++it) {
+        const uint32_t s = it % GT_NSTAGE;
+        const int kc = min(GT_KC, p.KP - ks * GT_KC);
+        if (lane == 0) {
           if (it >= GT_NSTAGE) mbar_wait(a_empty + 8 * s, ((it / GT_NSTAGE) & 1) ^ 1);
-          const int kc = min(GT_KC, p.KP - ks * GT_KC);
           mbar_expect_tx(a_full + 8 * s, kc * 2048 + kc * p.NT * 16);
-          gt_bulk_load(smem_u32(gt_smem + s * stage_bytes), At + static_cast<long long>(ks) * GT_KC * 2048, kc * 2048, a_full + 8 * s);
+          if (!p.imp) gt_bulk_load(smem_u32(gt_smem + s * stage_bytes), At + static_cast<long long>(ks) * GT_KC * 2048, kc * 2048, a_full + 8 * s);
           gt_bulk_load(smem_u32(gt_smem + s * stage_bytes + a_stage), Bt + static_cast<long long>(ks) * GT_KC * p.NT * 16, kc * p.NT * 16,
                        a_full + 8 * s);
+        }
+        if (p.imp) {
+          __syncwarp();                                            // the barrier is armed and the stage is free
+          if (lane < kc) {
+            const int kp = ks * GT_KC + lane, tap = kp / p.NCG, cg = kp - tap * p.NCG, kh = tap / p.KW, kw = tap - kh * p.KW;
+            const unsigned char* src = tap < p.n_taps ? Ac + (static_cast<long long>(cg) * p.R_alloc + kh * p.Wp + kw) * 16 : Ac;   // padding plane: zero weights
+            gt_bulk_load(smem_u32(gt_smem + s * stage_bytes + lane * 2048), src, 2048, a_full + 8 * s);
+          }
         }
       }
     }
@@ -156,7 +174,12 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const __grid_con
       const uint32_t ab = c & 1;
       mbar_wait(a_accfull + 8 * ab, (c >> 1) & 1);
       fence_after();
-      const long long m = mt * 128 + row;
+      long long m = mt * 128 + row;
+      if (p.imp) {                                                 // flat input row -> output position; junk rows are not stored
+        const long long clip = mt / p.tiles_per_clip;
+        const int r = static_cast<int>(mt - clip * p.tiles_per_clip) * 128 + row, ho = r / p.Wp, wo = r - ho * p.Wp;
+        m = (ho < p.Ho && wo < p.Wo) ? (clip * p.Ho + ho) * p.Wo + wo : p.M;
+      }
       const int col0 = nt * p.NT;
       for (int c0 = 0; c0 < p.NT; c0 += 16) {
         uint32_t v[16];
@@ -199,6 +222,151 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const __grid_con
   if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
+
+// Implicit-mode convolution with the clip's planar image RESIDENT in shared memory (the stride-1 second convolutions of
+// the two-convolution cnn-* configs).  A persistent CTA takes whole clips: the producer copies the clip's NCG planes
+// (R_alloc rows x 16 B each) once, then streams the layer's B tiles through a ring; the MMA warp runs, for every B stage, the
+// stage's K = 16 steps for EVERY M tile of the clip (all tiles_per_clip accumulators live in TMEM), reading the A operand as
+// tap-shifted windows of the resident image: rows [t * 128 + kh * Wp + kw, +128) of planes (cg, cg + 1).  Per clip the L2 is
+// asked for the image once and the weights once instead of (taps x tiles) shifted copies of the image.
+constexpr int CR_MAXSTEPS = 1024;     // K = 16 steps of a layer (taps x channel-group pairs)
+constexpr int CR_MAXSTAGE = 12;       // B stages in flight: as many as the shared memory left by the image holds (bulk-copy latency)
+
+struct ConvResParams {
+  const unsigned char* Ap;     // [n_clips][NCG][R_alloc][16 B]
+  const unsigned char* B;      // [KP][NT][8 halves], KP = n_taps * NCG
+  const float* bias;
+  __half* C;                   // NHWC f16 [n_clips][Ho][Wo][ldc]
+  int n_clips, NCG, R_alloc, Wp, KW, n_taps, tiles_per_clip, Ho, Wo, NT, ldc, relu, n_stage;
+  int mode;                    // HONK_CR_MODE, timing experiments only (results are garbage): 1 no image reloads, 2 no epilogue math / stores, 4 no MMAs
+};
+
+__global__ void __launch_bounds__(GT_THREADS, 1) conv_res_kernel(const __grid_constant__ ConvResParams p) {
+  extern __shared__ __align__(1024) unsigned char cr_smem[];
+  __shared__ __align__(8) uint64_t bar_bfull[CR_MAXSTAGE], bar_bempty[CR_MAXSTAGE], bar_img[2], bar_acc[2];
+  __shared__ uint32_t a_off[CR_MAXSTEPS];                         // byte offset of every K = 16 step's A window inside the image
+  const uint32_t CR_NSTAGE = p.n_stage;
+  __shared__ uint32_t tmem_base_s;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const int plane_bytes = p.R_alloc * 16, img_bytes = p.NCG * plane_bytes, b_stage = GT_KC * p.NT * 16;
+  unsigned char* ring = cr_smem + (img_bytes + 1023) / 1024 * 1024;
+  const uint32_t a_bfull = smem_u32(&bar_bfull[0]), a_bempty = smem_u32(&bar_bempty[0]);
+  const uint32_t a_imgfull = smem_u32(&bar_img[0]), a_imgempty = smem_u32(&bar_img[1]);
+  const uint32_t a_accfull = smem_u32(&bar_acc[0]), a_accempty = smem_u32(&bar_acc[1]);
+  if (tid == 0) {
+    for (int s = 0; s < CR_MAXSTAGE; ++s) {
+      mbar_init(a_bfull + 8 * s, 1);
+      mbar_init(a_bempty + 8 * s, 1);
+    }
+    mbar_init(a_imgfull, 1);
+    mbar_init(a_imgempty, 1);
+    mbar_init(a_accfull, 1);
+    mbar_init(a_accempty, 4);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(smem_u32(&tmem_base_s), 512);
+  const int KP = p.n_taps * p.NCG, n_ks = (KP + GT_KC - 1) / GT_KC;
+  for (int st = tid; st < KP / 2; st += GT_THREADS) {               // the issuing warp is bound by its own instruction stream:
+    const int tap = (2 * st) / p.NCG, cg = 2 * st - tap * p.NCG, kh = tap / p.KW, kw = tap - kh * p.KW;   // no index arithmetic there
+    a_off[st] = static_cast<uint32_t>(cg * (p.R_alloc * 16) + (kh * p.Wp + kw) * 16);
+  }
+  fence_before();
+  __syncthreads();
+  fence_after();
+  const uint32_t tmem = tmem_base_s;
+
+  if (warp == 0) {
+    // ======================================= producer =======================================
+    if (lane == 0) {
+      uint32_t it = 0, n = 0;
+      for (int clip = blockIdx.x; clip < p.n_clips; clip += gridDim.x, ++n) {
+        if (n > 0) mbar_wait(a_imgempty, (n - 1) & 1);             // the previous clip's MMAs have read the image
+        const bool skip_img = (p.mode & 1) && n > 0;
+        mbar_expect_tx(a_imgfull, skip_img ? plane_bytes : img_bytes);
+        const unsigned char* src = p.Ap + static_cast<long long>(clip) * img_bytes;
+        for (int cg = 0; cg < (skip_img ? 1 : p.NCG); ++cg) gt_bulk_load(smem_u32(cr_smem + cg * plane_bytes), src + static_cast<long long>(cg) * plane_bytes, plane_bytes, a_imgfull);
+        for (int ks = 0; ks < n_ks; ++ks, ++it) {
+          const uint32_t s = it % CR_NSTAGE;
+          if (it >= CR_NSTAGE) mbar_wait(a_bempty + 8 * s, ((it / CR_NSTAGE) & 1) ^ 1);
+          const int kc = min(GT_KC, KP - ks * GT_KC);
+          mbar_expect_tx(a_bfull + 8 * s, kc * p.NT * 16);
+          gt_bulk_load(smem_u32(ring + s * b_stage), p.B + static_cast<long long>(ks) * GT_KC * p.NT * 16, kc * p.NT * 16, a_bfull + 8 * s);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ======================================= MMA issuer =====================================
+    const uint32_t idesc = make_idesc(128, p.NT, 0);
+    const uint64_t a_hi = make_desc(0, plane_bytes, 128) & 0xFFFFFFFFFFFF0000ull;      // LBO = one channel-group plane
+    const uint64_t b_hi = make_desc(0, p.NT * 16, 128) & 0xFFFFFFFFFFFF0000ull;
+    const uint32_t img = smem_u32(cr_smem);
+    uint32_t it = 0, n = 0;
+    for (int clip = blockIdx.x; clip < p.n_clips; clip += gridDim.x, ++n) {
+      mbar_wait(a_imgfull, n & 1);
+      if (n > 0) mbar_wait(a_accempty, (n - 1) & 1);               // the epilogue has drained the previous clip's accumulators
+      fence_after();
+      for (int ks = 0; ks < n_ks; ++ks, ++it) {
+        const uint32_t s = it % CR_NSTAGE;
+        mbar_wait(a_bfull + 8 * s, (it / CR_NSTAGE) & 1);
+        fence_after();
+        const int kc = min(GT_KC, KP - ks * GT_KC);
+        if (gt_elect_one()) {
+          const uint32_t sb = smem_u32(ring + s * b_stage);
+          for (int j = 0; j < kc / 2; ++j) {
+            const uint32_t a0 = img + a_off[ks * (GT_KC / 2) + j];
+            const uint64_t bd = b_hi | ((sb + j * 2 * p.NT * 16) >> 4);
+            for (int t = 0; t < p.tiles_per_clip && !(p.mode & 4); ++t)
+              mma_f16_ss(tmem + t * p.NT, a_hi | ((a0 + t * 2048) >> 4), bd, idesc, (ks > 0 || j > 0) ? 1u : 0u);
+          }
+          commit(a_bempty + 8 * s);
+          if (ks == n_ks - 1) {
+            commit(a_accfull);
+            commit(a_imgempty);
+          }
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // ======================================= epilogue =======================================
+    const int quad = warp & 3, row = quad * 32 + lane;
+    const uint32_t tlane = static_cast<uint32_t>(quad * 32) << 16;
+    uint32_t n = 0;
+    for (int clip = blockIdx.x; clip < p.n_clips; clip += gridDim.x, ++n) {
+      mbar_wait(a_accfull, n & 1);
+      fence_after();
+      for (int t = 0; t < p.tiles_per_clip; ++t) {
+        const int r = t * 128 + row, ho = r / p.Wp, wo = r - ho * p.Wp;
+        const bool valid = ho < p.Ho && wo < p.Wo;
+        __half* dst = p.C + ((static_cast<long long>(clip) * p.Ho + ho) * p.Wo + wo) * p.ldc;
+        for (int c0 = 0; c0 < p.NT; c0 += 16) {
+          uint32_t v[16];
+          tmem_ld16(tmem + tlane + t * p.NT + c0, v);
+          tmem_ld_wait();
+          if (t == p.tiles_per_clip - 1 && c0 + 16 >= p.NT) {      // everything is in registers: hand the accumulators back
+            fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(a_accempty);
+          }
+          if (!valid || c0 >= p.ldc || (p.mode & 2)) continue;
+          float f[16];
+#pragma unroll
+          for (int k = 0; k < 16; ++k) {
+            f[k] = __uint_as_float(v[k]) + __ldg(p.bias + c0 + k);
+            if (p.relu) f[k] = fmaxf(f[k], 0.f);
+          }
+          *reinterpret_cast<uint4*>(dst + c0) = make_uint4(gt_pack_h2(f[0], f[1]), gt_pack_h2(f[2], f[3]), gt_pack_h2(f[4], f[5]), gt_pack_h2(f[6], f[7]));
+          *reinterpret_cast<uint4*>(dst + c0 + 8) =
+              make_uint4(gt_pack_h2(f[8], f[9]), gt_pack_h2(f[10], f[11]), gt_pack_h2(f[12], f[13]), gt_pack_h2(f[14], f[15]));
+        }
+      }
+    }
+  }
+  fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}
 
 // A operand of one layer (see the file comment).  One thread per 16-byte unit (row m, K plane), consecutive threads =
 // consecutive rows of one plane (coalesced 16-byte stores).  The previous layer's MaxPool(ph, pw) (floor mode, model.py:190,193)
@@ -322,6 +490,32 @@ __global__ void __launch_bounds__(256) gemm_pool_kernel(const uint4* __restrict_
   }
 }
 
+// The same MaxPool, written as the PLANAR image the implicit-mode GEMM reads: out[clip][cg][R_alloc rows][8 halves], row =
+// hp * Wp + wp; rows past the map (the tiles' and taps' over-read) are zero.  One thread per 16-byte unit of the output.
+__global__ void __launch_bounds__(256) gemm_pool_planar_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, long long n_units, int Hin,
+                                                               int Win, int cpt, int ph, int pw, int R_alloc) {
+  const int Hp = Hin / ph, Wp = Win / pw;
+  for (long long u = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x; u < n_units; u += static_cast<long long>(gridDim.x) * 256) {
+    const int r = static_cast<int>(u % R_alloc);
+    long long t = u / R_alloc;
+    const int c = static_cast<int>(t % cpt);
+    const long long clip = t / cpt;
+    uint4 o = make_uint4(0, 0, 0, 0);
+    if (r < Hp * Wp) {
+      const int hp = r / Wp, wp = r - hp * Wp;
+      const uint4* src = in + ((clip * Hin + hp * ph) * Win + wp * pw) * cpt + c;
+      o = __ldg(src);
+      for (int i = 0; i < ph; ++i)
+        for (int j = 0; j < pw; ++j) {
+          if (i == 0 && j == 0) continue;
+          const uint4 q = __ldg(src + (i * Win + j) * cpt);
+          o.x = pk_hmax2(o.x, q.x); o.y = pk_hmax2(o.y, q.y); o.z = pk_hmax2(o.z, q.z); o.w = pk_hmax2(o.w, q.w);
+        }
+    }
+    out[u] = o;
+  }
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------------------------------
@@ -331,6 +525,8 @@ struct GemmLayer {
   // geometry
   int in_f32 = 0, Hin = 0, Win = 0, Cs = 1, ph = 1, pw = 1, KH = 1, KW = 1, sh = 1, sw = 1, Ho = 1, Wo = 1;
   int K = 0, KP = 0, N = 0, NT = 16, n_ntiles = 1, relu = 0;
+  int imp = 0, R_alloc = 0, tiles_per_clip = 0;     // implicit mode (stride-1 conv over the pooled planar map): no A operand
+  int res = 0, res_smem = 0, res_stages = 4;        // ... with the clip's image resident in shared memory (conv_res_kernel)
   unsigned char* d_B = nullptr;
   float* d_bias = nullptr;
   int ldc() const { return NT * n_ntiles; }
@@ -434,6 +630,27 @@ int cnn_gemm_plan_create(honk_model* m, CnnGemmPlan** out) {
     HONK_TRY(gt_pack_weights(p.get(), L, Cin, m->host.at("conv2.bias").data, [&](int n, int kh, int kw, int ci) {
       return w.data[((static_cast<size_t>(n) * Cin + ci) * KH + kh) * KW + kw];
     }));
+    // implicit mode: a stride-1 convolution whose input went through a MaxPool reads the pooled map as a planar image by
+    // tap offsets instead of a materialised im2col operand (HONK_GEMM_IMPLICIT=0: the im2col path)
+    static const bool no_imp = getenv("HONK_GEMM_IMPLICIT") && atoi(getenv("HONK_GEMM_IMPLICIT")) == 0;
+    if (!no_imp && L.sh == 1 && L.sw == 1 && L.ph * L.pw > 1 && L.Ho * L.Wo >= 32) {
+      const int Wp = L.Win / L.pw;
+      L.imp = 1;
+      L.tiles_per_clip = ((L.Ho - 1) * Wp + L.Wo + 127) / 128;
+      L.R_alloc = (L.tiles_per_clip * 128 + (L.KH - 1) * Wp + L.KW + 7) / 8 * 8;
+      int max_smem_ = 0;
+      HONK_CUDA(cudaDeviceGetAttribute(&max_smem_, cudaDevAttrMaxSharedMemoryPerBlockOptin, m->device));
+      const int img = ((L.Cs >> 3) * L.R_alloc * 16 + 1023) / 1024 * 1024;
+      const int b_stage = GT_KC * L.NT * 16;
+      L.res_stages = std::max(2, std::min(CR_MAXSTAGE, (max_smem_ - 4096 - img) / b_stage));
+      L.res_smem = img + L.res_stages * b_stage + 1024;
+      static const bool no_res = getenv("HONK_GEMM_RESIDENT") && atoi(getenv("HONK_GEMM_RESIDENT")) == 0;
+      L.res = !no_res && L.n_ntiles == 1 && L.tiles_per_clip * L.NT <= 512 && L.KP / 2 <= CR_MAXSTEPS && L.res_smem + 2048 <= max_smem_ && L.R_alloc < 16384;
+      // measured (profiles/r04_configs.json): the resident kernel wins when a clip has at least two M tiles (cnn-tpool2/3,
+      // tstride2/4: conv2 + its operand 3.1 -> 1.6 ms, 3.3 -> 1.4, 1.5 -> 1.0 per 4096 clips); with a single tile per clip
+      // (cnn-tstride8) every clip streams the whole weight tensor for 160 MMAs and the materialised operand is faster
+      if (!L.res || L.tiles_per_clip < 2) L.imp = L.res = 0;
+    }
     H = L.Ho; W = L.Wo; C = L.N; Cs = L.ldc(); ph = c.conv2_pool[0]; pw = c.conv2_pool[1];
     p->layers.push_back(L);
   }
@@ -466,9 +683,11 @@ int cnn_gemm_plan_create(honk_model* m, CnnGemmPlan** out) {
   }
   // workspace per clip: the largest A operand and the largest activation (two ping-pong buffers)
   for (const GemmLayer& L : p->layers) {
-    p->a_bytes_per_clip = std::max<int64_t>(p->a_bytes_per_clip, static_cast<int64_t>(L.Ho) * L.Wo * L.KP * 16);
+    if (!L.imp) p->a_bytes_per_clip = std::max<int64_t>(p->a_bytes_per_clip, static_cast<int64_t>(L.Ho) * L.Wo * L.KP * 16);
     p->act_bytes_per_clip = std::max<int64_t>(p->act_bytes_per_clip, static_cast<int64_t>(L.Ho) * L.Wo * L.ldc() * 2);
-    if (!L.in_f32 && L.ph * L.pw > 1)
+    if (L.imp)
+      p->pool_bytes_per_clip = std::max<int64_t>(p->pool_bytes_per_clip, static_cast<int64_t>(L.Cs >> 3) * L.R_alloc * 16);
+    else if (!L.in_f32 && L.ph * L.pw > 1)
       p->pool_bytes_per_clip = std::max<int64_t>(p->pool_bytes_per_clip, static_cast<int64_t>(L.Hin / L.ph) * (L.Win / L.pw) * L.Cs * 2);
     if (L.KP > 65535 * 2) return HONK_OK;
   }
@@ -480,13 +699,20 @@ int cnn_gemm_plan_create(honk_model* m, CnnGemmPlan** out) {
   const int smem = GT_NSTAGE * (GT_KC * 2048 + GT_KC * GT_MAXNT * 16) + 1024;
   if (smem + 1024 > max_smem) return HONK_OK;
   HONK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  {
+    int res_smem = 0;
+    for (const GemmLayer& L : p->layers)
+      if (L.res) res_smem = std::max(res_smem, L.res_smem);
+    if (res_smem) HONK_CUDA(cudaFuncSetAttribute(conv_res_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, res_smem));
+  }
   *out = p.release();
   return HONK_OK;
 }
 
 static int64_t gt_a_bytes(const CnnGemmPlan* p, int64_t n) {
   int64_t mx = 0;
-  for (const GemmLayer& L : p->layers) mx = std::max<int64_t>(mx, (n * L.Ho * L.Wo + 127) / 128 * L.KP * 2048);
+  for (const GemmLayer& L : p->layers)
+    if (!L.imp) mx = std::max<int64_t>(mx, (n * L.Ho * L.Wo + 127) / 128 * L.KP * 2048);
   return mx;
 }
 
@@ -520,24 +746,32 @@ int cnn_gemm_forward(const CnnGemmPlan* p, const float* d_mfcc, int64_t n_clips,
       static const char* kPack[] = {"gt_pack0", "gt_pack1", "gt_pack2", "gt_pack3", "gt_pack4", "gt_pack5"};
       static const char* kGemm[] = {"gt_gemm0", "gt_gemm1", "gt_gemm2", "gt_gemm3", "gt_gemm4", "gt_gemm5"};
       int Hin = L.Hin, Win = L.Win;
-      if (!L.in_f32 && L.ph * L.pw > 1) {                    // the previous layer's MaxPool, once, before the im2col reads it many times
-        ProfSpan sp(kPack[std::min<size_t>(li, 5)], s);
-        Hin = L.Hin / L.ph;
-        Win = L.Win / L.pw;
-        const long long units = n * Hin * Win * (L.Cs >> 3);
-        gemm_pool_kernel<<<static_cast<unsigned>(std::min<long long>((units + 255) / 256, 32ll * p->n_sms)), 256, 0, s>>>(
-            static_cast<const uint4*>(in), reinterpret_cast<uint4*>(pooled), units, L.Hin, L.Win, L.Cs >> 3, L.ph, L.pw);
-        HONK_LAUNCH_CHECK();
-        in = pooled;
-      }
       PackParams pk{};
-      pk.in = in; pk.A = A;
       pk.M = n * L.Ho * L.Wo;
-      const long long n_mtiles = (pk.M + 127) / 128;
-      pk.n_units = n_mtiles * L.KP * 128;
-      pk.in_f32 = L.in_f32; pk.Hin = Hin; pk.Win = Win; pk.Cs = L.Cs; pk.ph = 1; pk.pw = 1;
-      pk.KH = L.KH; pk.KW = L.KW; pk.sh = L.sh; pk.sw = L.sw; pk.Ho = L.Ho; pk.Wo = L.Wo; pk.K = L.K; pk.KP = L.KP;
-      {
+      long long n_mtiles = (pk.M + 127) / 128;
+      if (L.imp) {
+        // MaxPool into the planar image the GEMM's producer reads by tap offsets: no A operand for this layer
+        ProfSpan sp(kPack[std::min<size_t>(li, 5)], s);
+        const long long units = n * (L.Cs >> 3) * L.R_alloc;
+        gemm_pool_planar_kernel<<<static_cast<unsigned>(std::min<long long>((units + 255) / 256, 32ll * p->n_sms)), 256, 0, s>>>(
+            static_cast<const uint4*>(in), reinterpret_cast<uint4*>(pooled), units, L.Hin, L.Win, L.Cs >> 3, L.ph, L.pw, L.R_alloc);
+        HONK_LAUNCH_CHECK();
+        n_mtiles = n * L.tiles_per_clip;
+      } else {
+        if (!L.in_f32 && L.ph * L.pw > 1) {                  // the previous layer's MaxPool, once, before the im2col reads it many times
+          ProfSpan sp(kPack[std::min<size_t>(li, 5)], s);
+          Hin = L.Hin / L.ph;
+          Win = L.Win / L.pw;
+          const long long units = n * Hin * Win * (L.Cs >> 3);
+          gemm_pool_kernel<<<static_cast<unsigned>(std::min<long long>((units + 255) / 256, 32ll * p->n_sms)), 256, 0, s>>>(
+              static_cast<const uint4*>(in), reinterpret_cast<uint4*>(pooled), units, L.Hin, L.Win, L.Cs >> 3, L.ph, L.pw);
+          HONK_LAUNCH_CHECK();
+          in = pooled;
+        }
+        pk.in = in; pk.A = A;
+        pk.n_units = n_mtiles * L.KP * 128;
+        pk.in_f32 = L.in_f32; pk.Hin = Hin; pk.Win = Win; pk.Cs = L.Cs; pk.ph = 1; pk.pw = 1;
+        pk.KH = L.KH; pk.KW = L.KW; pk.sh = L.sh; pk.sw = L.sw; pk.Ho = L.Ho; pk.Wo = L.Wo; pk.K = L.K; pk.KP = L.KP;
         ProfSpan sp(kPack[std::min<size_t>(li, 5)], s);
         if (!L.in_f32 && n_mtiles * 128 < 512ll * p->n_sms && L.KP >= 64)
           gemm_pack_units_kernel<<<static_cast<unsigned>(std::min<long long>((pk.n_units + 255) / 256, 32ll * p->n_sms)), 256, 0, s>>>(pk);
@@ -553,9 +787,23 @@ int cnn_gemm_forward(const CnnGemmPlan* p, const float* d_mfcc, int64_t n_clips,
       g.n_store = last ? p->n_labels : L.ldc();
       g.relu = L.relu; g.out_f32 = last ? 1 : 0;
       g.n_mtiles = n_mtiles;
+      if (L.imp) {
+        g.imp = 1; g.Ap = pooled; g.NCG = L.Cs >> 3; g.R_alloc = L.R_alloc; g.Wp = L.Win / L.pw; g.KW = L.KW; g.n_taps = L.KH * L.KW;
+        g.tiles_per_clip = L.tiles_per_clip; g.Ho = L.Ho; g.Wo = L.Wo;
+      }
       const long long n_tiles = n_mtiles * L.n_ntiles;
       const int smem = GT_NSTAGE * (GT_KC * 2048 + GT_KC * L.NT * 16) + 1024;
-      {
+      if (L.res) {
+        ConvResParams r{};
+        r.Ap = pooled; r.B = L.d_B; r.bias = L.d_bias; r.C = reinterpret_cast<__half*>(act[li & 1]);
+        r.n_clips = static_cast<int>(n); r.NCG = L.Cs >> 3; r.R_alloc = L.R_alloc; r.Wp = L.Win / L.pw; r.KW = L.KW; r.n_taps = L.KH * L.KW;
+        r.tiles_per_clip = L.tiles_per_clip; r.Ho = L.Ho; r.Wo = L.Wo; r.NT = L.NT; r.ldc = L.ldc(); r.relu = L.relu; r.n_stage = L.res_stages;
+        static const int cr_mode = getenv("HONK_CR_MODE") ? atoi(getenv("HONK_CR_MODE")) : 0;
+        r.mode = cr_mode;
+        ProfSpan sp(kGemm[std::min<size_t>(li, 5)], s);
+        conv_res_kernel<<<static_cast<unsigned>(std::min<long long>(n, p->n_sms)), GT_THREADS, L.res_smem, s>>>(r);
+        HONK_LAUNCH_CHECK();
+      } else {
         ProfSpan sp(kGemm[std::min<size_t>(li, 5)], s);
         gemm_tc_kernel<<<static_cast<unsigned>(std::min<long long>(n_tiles, p->n_sms)), GT_THREADS, smem, s>>>(g);
         HONK_LAUNCH_CHECK();

@@ -13,7 +13,9 @@ base = synth.make_clips(128, start=500)
 mf0 = pre.compute_mfccs_batch(torch.from_numpy(base).cuda())
 worst = 0.0
 for name, sizes in (("res15", (73, 74, 75, 147, 149, 1111, 2957)), ("res26", (295, 297, 593, 3001)), ("res8", (591, 1185, 4099)),
-                    ("res15-narrow", (223, 1500)), ("cnn-trad-pool2", (147, 149, 1000))):
+                    ("res15-narrow", (223, 1500)), ("cnn-trad-pool2", (147, 149, 1000)),
+                    ("cnn-tpool2", (1, 2, 147, 149, 1000, 4100)), ("cnn-tstride2", (3, 148, 297, 5000)), ("cnn-tstride4", (1, 151, 4097)),
+                    ("cnn-tpool3", (5, 150, 1025)), ("cnn-tstride8", (149, 1000)), ("cnn-one-stride1", (149, 1000))):
     cfg = dict(hb.find_config(name)); cfg["n_labels"] = 12
     sd = synth.make_state_dict(name, cfg, seed=21, calib_mfcc=mf0[:16].cpu().numpy())
     ms = []
@@ -30,6 +32,6 @@ for name, sizes in (("res15", (73, 74, 75, 147, 149, 1111, 2957)), ("res26", (29
             y = ms[0](mf).cpu().numpy()
             err = float(np.abs(y - ref).max() / np.abs(ref).max())
             worst = max(worst, err)
-            assert err < 3e-2, (name, n, rep, err)
+            assert err < 3e-3, (name, n, rep, err)
         print(name, n, "ok", "%.2e" % err, flush=True)
 print("worst relative error %.2e" % worst)

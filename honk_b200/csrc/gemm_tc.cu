@@ -643,6 +643,7 @@ int cnn_gemm_plan_create(honk_model* m, CnnGemmPlan** out) {
       const int img = ((L.Cs >> 3) * L.R_alloc * 16 + 1023) / 1024 * 1024;
       const int b_stage = GT_KC * L.NT * 16;
       L.res_stages = std::max(2, std::min(CR_MAXSTAGE, (max_smem_ - 4096 - img) / b_stage));
+      if (const char* e = getenv("HONK_CR_STAGES")) L.res_stages = std::max(2, std::min(L.res_stages, atoi(e)));
       L.res_smem = img + L.res_stages * b_stage + 1024;
       static const bool no_res = getenv("HONK_GEMM_RESIDENT") && atoi(getenv("HONK_GEMM_RESIDENT")) == 0;
       L.res = !no_res && L.n_ntiles == 1 && L.tiles_per_clip * L.NT <= 512 && L.KP / 2 <= CR_MAXSTEPS && L.res_smem + 2048 <= max_smem_ && L.R_alloc < 16384;

@@ -113,7 +113,7 @@ __global__ void bn_bwd_finalize_kernel(const double* __restrict__ partial, int n
 // dc = dr * (y > 0)  (gradient at the convolution's output, before the ReLU).
 __global__ void bn_relu_bwd_kernel(const float* __restrict__ dx, const float* __restrict__ xhat, const float* __restrict__ y,
                                    const float* __restrict__ sums, const float* __restrict__ invstd,
-                                   const float* __restrict__ dold_in, float* __restrict__ dold_out, float* __restrict__ dc,
+                                   const float* dold_in, float* dold_out /* may be the same buffer */, float* __restrict__ dc,
                                    int C, int HW, long long n) {
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int c = static_cast<int>((i / HW) % C);
@@ -435,8 +435,9 @@ __device__ __forceinline__ uint32_t mix32(uint32_t x) {           // lowbias32 i
 
 // nn.Dropout in training mode: y = x * keep / (1 - p).  keep comes from the caller's mask (uint8, what the parity tests use) or
 // is drawn here (counter-based hash of seed, site and element; the drawn mask is written to `mask` for the backward pass).
-__global__ void dropout_fwd_kernel(const float* __restrict__ x, const unsigned char* __restrict__ user_mask, unsigned char* __restrict__ mask,
-                                   float* __restrict__ y, long long n, float p, float scale, uint32_t seed) {
+// (x and y may be the same buffer: no __restrict__ on them)
+__global__ void dropout_fwd_kernel(const float* x, const unsigned char* __restrict__ user_mask, unsigned char* __restrict__ mask,
+                                   float* y, long long n, float p, float scale, uint32_t seed) {
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x) {
     unsigned char k;
     if (user_mask) k = user_mask[i] != 0;
@@ -447,8 +448,9 @@ __global__ void dropout_fwd_kernel(const float* __restrict__ x, const unsigned c
 }
 
 // dx = dy * keep / (1 - p), then through the ReLU that produced the dropped tensor when `relu_out` (the ReLU's output) is given
-__global__ void dropout_relu_bwd_kernel(const float* __restrict__ dy, const unsigned char* __restrict__ mask, const float* __restrict__ relu_out,
-                                        float* __restrict__ dx, long long n, float scale) {
+// (dy and dx may be the same buffer: no __restrict__ on them)
+__global__ void dropout_relu_bwd_kernel(const float* dy, const unsigned char* __restrict__ mask, const float* __restrict__ relu_out,
+                                        float* dx, long long n, float scale) {
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * blockDim.x) {
     float g = (!mask || mask[i]) ? dy[i] * scale : 0.f;
     if (relu_out && !(relu_out[i] > 0.f)) g = 0.f;

@@ -232,8 +232,9 @@ __global__ void pool2d_f32_kernel(const float* __restrict__ in, float* __restric
   out[i] = is_max ? acc : acc / static_cast<float>(kh * kw);
 }
 
-__global__ void bn_residual_f32_kernel(const float* __restrict__ y, const float* __restrict__ res,
-                                       float* __restrict__ res_out, float* __restrict__ out,
+// (res and res_out are the same buffer when the residual stream is updated in place: no __restrict__ on them)
+__global__ void bn_residual_f32_kernel(const float* __restrict__ y, const float* res,
+                                       float* res_out, float* __restrict__ out,
                                        const float* __restrict__ mean, const float* __restrict__ scale,
                                        long long total, int C, int HW) {
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;

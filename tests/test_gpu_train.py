@@ -216,3 +216,25 @@ def test_cnn_dropout_drawn_by_the_library_is_reproducible_and_has_the_right_rate
     assert rel_err(w0, o["state"]["conv1.weight"].astype(np.float64)) <= 1e-3
     # keep rate of the drawn masks: the first step's scores with p = 0.5 differ from p = 0 but stay finite and of similar scale
     assert np.isfinite(l1).all() and abs(l1[0] - l0[0]) > 1e-4
+
+
+@pytest.mark.parametrize("momentum,wd,nesterov", [(0.0, 0.0, False), (0.0, 1e-3, False), (0.5, 0.0, True)])
+def test_sgd_variants_against_oracle(momentum, wd, nesterov):
+    """Plain SGD (no momentum buffer), weight decay alone, Nesterov without weight decay: two steps against the oracle."""
+    import honk_b200 as hb
+    from honk_b200 import train
+    name = "res8-narrow"
+    cfg = dict(hb.find_config(name))
+    cfg["n_labels"] = 12
+    clips, labels = synth.make_clips(2 * 32, start=840000, labelled=True)
+    pre = hb.AudioPreprocessor()
+    mfcc = pre.compute_mfccs_batch(torch.from_numpy(clips).cuda()).float()
+    state = synth.make_state_dict(name, cfg, seed=6, calib_mfcc=mfcc[:8].cpu().numpy())
+    batches = [(mfcc[i * 32:(i + 1) * 32].cpu().numpy(), labels[i * 32:(i + 1) * 32].astype(np.int64)) for i in range(2)]
+    o = orc.sgd_train_steps(state, cfg, batches, lr=0.05, momentum=momentum, weight_decay=wd, nesterov=nesterov)
+    tr = train.SgdTrainer(make_model(name, cfg, state), lr=0.05, momentum=momentum, weight_decay=wd, nesterov=nesterov)
+    losses = [float(tr.step(torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda())[1]) for x, y in batches]
+    assert np.allclose(losses, o["losses"], atol=1e-4), (losses, o["losses"])
+    for k, v in o["state"].items():
+        if not k.endswith("num_batches_tracked"):
+            assert rel_err(tr.read(k), v.astype(np.float64)) <= 1e-3, k

@@ -368,6 +368,165 @@ __global__ void __launch_bounds__(GT_THREADS, 1) conv_res_kernel(const __grid_co
   if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
+// ------------------------------------------------------------------------------------------
+// conv1 (1 -> C1, KH x 8 kernel, stride (sh, 1)) without an im2col operand.  A pre-pass stores each clip's MFCC image as
+//   x8p[clip][phase p < sh][wx < W - 7][i < Hph][8 halves] = f16(x[i * sh + p][wx .. wx + 7])      (Hph = ceil(H / sh)),
+// i.e. the 8 coefficient taps of one kernel row are one 16-byte unit and, per time phase, time runs fastest.  With output rows
+// numbered r = wo * Hph + ho, kernel row kh of EVERY output row of a tile is the run of 128 units starting at
+// r0 + (kh % sh) * Wx * Hph + kh / sh: the A operand is a window of the image, two kernel rows per K = 16 MMA (their runs are a
+// constant distance apart: 16 bytes for sh = 1, one phase image otherwise).  A persistent CTA keeps the layer's weights and two
+// clips' images resident, walks the clip's M tiles with two TMEM accumulators, and its epilogue stores + bias, ReLU, f16 NHWC.
+// ------------------------------------------------------------------------------------------
+struct Conv1ResParams {
+  const unsigned char* X;      // x8p images, img_bytes per clip (zero padded past the last real row)
+  const unsigned char* B;      // [KP planes][NT][8 halves], plane = kernel row (KP even)
+  const float* bias;
+  __half* C;                   // NHWC f16 [n_clips][Ho][Wo][ldc]
+  int n_clips, img_bytes, KP, NT, ldc, Hph, Ho, Wo, n_tiles, lbo, sh, phase_stride;   // phase_stride = Wx * Hph rows
+};
+
+__global__ void __launch_bounds__(256) x8p_pack_kernel(const float* __restrict__ mfcc, unsigned char* __restrict__ X, int H, int W, int sh, int Hph,
+                                                       int img_units) {
+  const int Wx = W - 7;
+  const float* src = mfcc + static_cast<long long>(blockIdx.x) * H * W;
+  uint4* dst = reinterpret_cast<uint4*>(X) + static_cast<long long>(blockIdx.x) * img_units;
+  for (int u = threadIdx.x; u < img_units; u += blockDim.x) {
+    uint4 o = make_uint4(0, 0, 0, 0);
+    const int i = u % Hph, t = u / Hph, wx = t % Wx, ph = t / Wx;
+    const int h = i * sh + ph;
+    if (ph < sh && h < H) {
+      uint32_t hv[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) hv[e] = __half_as_ushort(__float2half_rn(fminf(fmaxf(__ldg(src + h * W + wx + e), -60000.f), 60000.f)));
+      o = make_uint4(hv[0] | (hv[1] << 16), hv[2] | (hv[3] << 16), hv[4] | (hv[5] << 16), hv[6] | (hv[7] << 16));
+    }
+    dst[u] = o;
+  }
+}
+
+constexpr int C1_THREADS = 10 * 32;      // producer, MMA issuer, 8 epilogue warps (two per TMEM lane quarter, half the channels each)
+
+__global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_constant__ Conv1ResParams p) {
+  extern __shared__ __align__(1024) unsigned char c1_smem[];
+  __shared__ __align__(8) uint64_t bar_w, bar_imgfull[2], bar_imgempty[2], bar_accfull[2], bar_accempty[2];
+  __shared__ __align__(16) float bias_s[GT_MAXNT];
+  __shared__ uint32_t tmem_base_s;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const int img_al = (p.img_bytes + 1023) / 1024 * 1024, w_bytes = p.KP * p.NT * 16;
+  unsigned char* wsm = c1_smem + 2 * img_al;
+  const uint32_t a_w = smem_u32(&bar_w), a_imgfull = smem_u32(&bar_imgfull[0]), a_imgempty = smem_u32(&bar_imgempty[0]);
+  const uint32_t a_accfull = smem_u32(&bar_accfull[0]), a_accempty = smem_u32(&bar_accempty[0]);
+  if (tid == 0) {
+    mbar_init(a_w, 1);
+    for (int k = 0; k < 2; ++k) {
+      mbar_init(a_imgfull + 8 * k, 1);
+      mbar_init(a_imgempty + 8 * k, 1);
+      mbar_init(a_accfull + 8 * k, 1);
+      mbar_init(a_accempty + 8 * k, 8);
+    }
+    fence_mbar_init();
+  }
+  for (int i = tid; i < p.NT; i += C1_THREADS) bias_s[i] = __ldg(p.bias + i);
+  if (warp == 1) tmem_alloc(smem_u32(&tmem_base_s), 512);
+  fence_before();
+  __syncthreads();
+  fence_after();
+  const uint32_t tmem = tmem_base_s;
+
+  if (warp == 0) {
+    // ======================================= producer =======================================
+    if (lane == 0) {
+      mbar_expect_tx(a_w, w_bytes);
+      for (int off = 0; off < w_bytes; off += 32768) gt_bulk_load(smem_u32(wsm + off), p.B + off, min(32768, w_bytes - off), a_w);
+      uint32_t n = 0;
+      for (int clip = blockIdx.x; clip < p.n_clips; clip += gridDim.x, ++n) {
+        const uint32_t ib = n & 1;
+        if (n >= 2) mbar_wait(a_imgempty + 8 * ib, ((n >> 1) & 1) ^ 1);
+        mbar_expect_tx(a_imgfull + 8 * ib, p.img_bytes);
+        const unsigned char* src = p.X + static_cast<long long>(clip) * p.img_bytes;
+        for (int off = 0; off < p.img_bytes; off += 32768)
+          gt_bulk_load(smem_u32(c1_smem + ib * img_al + off), src + off, min(32768, p.img_bytes - off), a_imgfull + 8 * ib);
+      }
+    }
+  } else if (warp == 1) {
+    // ======================================= MMA issuer =====================================
+    const uint32_t idesc = make_idesc(128, p.NT, 0);
+    const uint64_t a_hi = make_desc(0, p.lbo, 128) & 0xFFFFFFFFFFFF0000ull;
+    const uint64_t b_hi = make_desc(0, p.NT * 16, 128) & 0xFFFFFFFFFFFF0000ull;
+    const uint32_t wb = smem_u32(wsm);
+    mbar_wait(a_w, 0);
+    uint32_t n = 0, c = 0;
+    for (int clip = blockIdx.x; clip < p.n_clips; clip += gridDim.x, ++n) {
+      const uint32_t ib = n & 1;
+      mbar_wait(a_imgfull + 8 * ib, (n >> 1) & 1);
+      fence_after();
+      const uint32_t img = smem_u32(c1_smem + ib * img_al);
+      for (int t = 0; t < p.n_tiles; ++t, ++c) {
+        const uint32_t ab = c & 1;
+        if (c >= 2) {
+          mbar_wait(a_accempty + 8 * ab, ((c >> 1) & 1) ^ 1);
+          fence_after();
+        }
+        if (gt_elect_one()) {
+          const uint32_t d = tmem + ab * 256;
+          for (int j = 0; j < p.KP / 2; ++j) {
+            const int kh = 2 * j;                                      // kernel rows (kh, kh + 1): phases kh % sh and the next one
+            const uint32_t a0 = img + (t * 128 + (kh % p.sh) * p.phase_stride + kh / p.sh) * 16;
+            mma_f16_ss(d, a_hi | (a0 >> 4), b_hi | ((wb + j * 2 * p.NT * 16) >> 4), idesc, j > 0 ? 1u : 0u);
+          }
+          commit(a_accfull + 8 * ab);
+          if (t == p.n_tiles - 1) commit(a_imgempty + 8 * ib);
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // ======================================= epilogue =======================================
+    const int quad = warp & 3, row = quad * 32 + lane, half = (warp - 2) >> 2;          // column half of this warp
+    const uint32_t tlane = static_cast<uint32_t>(quad * 32) << 16;
+    const int n16 = p.NT / 16, c_lo = half == 0 ? 0 : (n16 + 1) / 2, c_hi = half == 0 ? (n16 + 1) / 2 : n16;   // 16-column groups
+    uint32_t c = 0;
+    for (int clip = blockIdx.x; clip < p.n_clips; clip += gridDim.x) {
+      for (int t = 0; t < p.n_tiles; ++t, ++c) {
+        const uint32_t ab = c & 1;
+        mbar_wait(a_accfull + 8 * ab, (c >> 1) & 1);
+        fence_after();
+        const int r = t * 128 + row, wo = r / p.Hph, ho = r - wo * p.Hph;
+        const bool valid = ho < p.Ho && wo < p.Wo;
+        __half* dst = p.C + ((static_cast<long long>(clip) * p.Ho + ho) * p.Wo + wo) * p.ldc;
+        for (int g = c_lo; g < c_hi; ++g) {
+          const int c0 = g * 16;
+          uint32_t v[16];
+          tmem_ld16(tmem + tlane + ab * 256 + c0, v);
+          tmem_ld_wait();
+          if (g == c_hi - 1) {                                       // this warp's share of the accumulator is in registers
+            fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(a_accempty + 8 * ab);
+          }
+          if (!valid) continue;
+          float f[16];
+#pragma unroll
+          for (int k = 0; k < 16; k += 4) {
+            const float4 b4 = *reinterpret_cast<const float4*>(&bias_s[c0 + k]);
+            f[k] = fmaxf(__uint_as_float(v[k]) + b4.x, 0.f);
+            f[k + 1] = fmaxf(__uint_as_float(v[k + 1]) + b4.y, 0.f);
+            f[k + 2] = fmaxf(__uint_as_float(v[k + 2]) + b4.z, 0.f);
+            f[k + 3] = fmaxf(__uint_as_float(v[k + 3]) + b4.w, 0.f);
+          }
+          *reinterpret_cast<uint4*>(dst + c0) = make_uint4(gt_pack_h2(f[0], f[1]), gt_pack_h2(f[2], f[3]), gt_pack_h2(f[4], f[5]), gt_pack_h2(f[6], f[7]));
+          *reinterpret_cast<uint4*>(dst + c0 + 8) =
+              make_uint4(gt_pack_h2(f[8], f[9]), gt_pack_h2(f[10], f[11]), gt_pack_h2(f[12], f[13]), gt_pack_h2(f[14], f[15]));
+        }
+      }
+    }
+  }
+  fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
 // A operand of one layer (see the file comment).  One thread per 16-byte unit (row m, K plane), consecutive threads =
 // consecutive rows of one plane (coalesced 16-byte stores).  The previous layer's MaxPool(ph, pw) (floor mode, model.py:190,193)
 // is applied while reading: max over the window of the stored, already ReLU-ed f16 activation (max commutes with the f16 rounding).
@@ -527,6 +686,7 @@ struct GemmLayer {
   int K = 0, KP = 0, N = 0, NT = 16, n_ntiles = 1, relu = 0;
   int imp = 0, R_alloc = 0, tiles_per_clip = 0;     // implicit mode (stride-1 conv over the pooled planar map): no A operand
   int res = 0, res_smem = 0, res_stages = 4;        // ... with the clip's image resident in shared memory (conv_res_kernel)
+  int c1res = 0, c1_units = 0, c1_tiles = 0, c1_hph = 0, c1_smem = 0;   // conv1 over the resident x8p image (conv1_res_kernel)
   unsigned char* d_B = nullptr;
   float* d_bias = nullptr;
   int ldc() const { return NT * n_ntiles; }
@@ -614,6 +774,23 @@ int cnn_gemm_plan_create(honk_model* m, CnnGemmPlan** out) {
     const int KH = L.KH, KW = L.KW;
     HONK_TRY(gt_pack_weights(p.get(), L, 1, m->host.at("conv1.bias").data,
                              [&](int n, int kh, int kw, int) { return w.data[(static_cast<size_t>(n) * KH + kh) * KW + kw]; }));
+    {
+      // conv1 without an im2col operand when it is a real convolution in time (KW = 8 coefficient taps, coefficient stride 1)
+      static const bool no_c1 = getenv("HONK_GEMM_CONV1_RESIDENT") && atoi(getenv("HONK_GEMM_CONV1_RESIDENT")) == 0;
+      int max_smem_ = 0;
+      HONK_CUDA(cudaDeviceGetAttribute(&max_smem_, cudaDevAttrMaxSharedMemoryPerBlockOptin, m->device));
+      const int sh = L.sh, Wx = m->W0 - 7, Hph = (m->H0 + sh - 1) / sh;
+      // measured: time strides 4 and 8 (cnn-tstride4/8) have too few rows per phase image for this to beat the im2col operand
+      if (!no_c1 && L.KW == 8 && L.sw == 1 && L.n_ntiles == 1 && (sh == 1 || sh == 2) && L.Ho * L.Wo >= 256 && L.Wo == Wx) {
+        L.c1_hph = Hph;
+        L.c1_tiles = (Wx * Hph + 127) / 128;
+        L.c1_units = ((sh - 1) * Wx * Hph + L.c1_tiles * 128 + L.KH / sh + 2 + 7) / 8 * 8;
+        L.c1_units = std::max(L.c1_units, sh * Wx * Hph);
+        const int img_al = (L.c1_units * 16 + 1023) / 1024 * 1024;
+        L.c1_smem = 2 * img_al + L.KP * L.NT * 16 + 1024;
+        L.c1res = L.c1_smem + 2048 <= max_smem_ && (sh == 1 ? 16 : Wx * Hph * 16) < (1 << 18);
+      }
+    }
     H = L.Ho; W = L.Wo; C = L.N; Cs = L.ldc(); ph = c.conv1_pool[0]; pw = c.conv1_pool[1];
     p->layers.push_back(L);
   }
@@ -684,7 +861,8 @@ int cnn_gemm_plan_create(honk_model* m, CnnGemmPlan** out) {
   }
   // workspace per clip: the largest A operand and the largest activation (two ping-pong buffers)
   for (const GemmLayer& L : p->layers) {
-    if (!L.imp) p->a_bytes_per_clip = std::max<int64_t>(p->a_bytes_per_clip, static_cast<int64_t>(L.Ho) * L.Wo * L.KP * 16);
+    if (L.c1res) p->a_bytes_per_clip = std::max<int64_t>(p->a_bytes_per_clip, static_cast<int64_t>(L.c1_units) * 16);
+    else if (!L.imp) p->a_bytes_per_clip = std::max<int64_t>(p->a_bytes_per_clip, static_cast<int64_t>(L.Ho) * L.Wo * L.KP * 16);
     p->act_bytes_per_clip = std::max<int64_t>(p->act_bytes_per_clip, static_cast<int64_t>(L.Ho) * L.Wo * L.ldc() * 2);
     if (L.imp)
       p->pool_bytes_per_clip = std::max<int64_t>(p->pool_bytes_per_clip, static_cast<int64_t>(L.Cs >> 3) * L.R_alloc * 16);
@@ -705,6 +883,7 @@ int cnn_gemm_plan_create(honk_model* m, CnnGemmPlan** out) {
     for (const GemmLayer& L : p->layers)
       if (L.res) res_smem = std::max(res_smem, L.res_smem);
     if (res_smem) HONK_CUDA(cudaFuncSetAttribute(conv_res_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, res_smem));
+    if (p->layers[0].c1res) HONK_CUDA(cudaFuncSetAttribute(conv1_res_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, p->layers[0].c1_smem));
   }
   *out = p.release();
   return HONK_OK;
@@ -712,8 +891,10 @@ int cnn_gemm_plan_create(honk_model* m, CnnGemmPlan** out) {
 
 static int64_t gt_a_bytes(const CnnGemmPlan* p, int64_t n) {
   int64_t mx = 0;
-  for (const GemmLayer& L : p->layers)
-    if (!L.imp) mx = std::max<int64_t>(mx, (n * L.Ho * L.Wo + 127) / 128 * L.KP * 2048);
+  for (const GemmLayer& L : p->layers) {
+    if (L.c1res) mx = std::max<int64_t>(mx, n * L.c1_units * 16);
+    else if (!L.imp) mx = std::max<int64_t>(mx, (n * L.Ho * L.Wo + 127) / 128 * L.KP * 2048);
+  }
   return mx;
 }
 
@@ -746,6 +927,25 @@ int cnn_gemm_forward(const CnnGemmPlan* p, const float* d_mfcc, int64_t n_clips,
       const bool last = li + 1 == p->layers.size();
       static const char* kPack[] = {"gt_pack0", "gt_pack1", "gt_pack2", "gt_pack3", "gt_pack4", "gt_pack5"};
       static const char* kGemm[] = {"gt_gemm0", "gt_gemm1", "gt_gemm2", "gt_gemm3", "gt_gemm4", "gt_gemm5"};
+      if (L.c1res) {
+        {
+          ProfSpan sp(kPack[0], s);
+          x8p_pack_kernel<<<static_cast<unsigned>(n), 256, 0, s>>>(static_cast<const float*>(in), A, p->H0, p->W0, L.sh, L.c1_hph, L.c1_units);
+          HONK_LAUNCH_CHECK();
+        }
+        Conv1ResParams r{};
+        r.X = A; r.B = L.d_B; r.bias = L.d_bias; r.C = reinterpret_cast<__half*>(act[li & 1]);
+        r.n_clips = static_cast<int>(n); r.img_bytes = L.c1_units * 16; r.KP = L.KP; r.NT = L.NT; r.ldc = L.ldc(); r.Hph = L.c1_hph;
+        r.Ho = L.Ho; r.Wo = L.Wo; r.n_tiles = L.c1_tiles; r.sh = L.sh; r.phase_stride = (p->W0 - 7) * L.c1_hph;
+        r.lbo = L.sh == 1 ? 16 : r.phase_stride * 16;
+        {
+          ProfSpan sp(kGemm[0], s);
+          conv1_res_kernel<<<static_cast<unsigned>(std::min<long long>(n, p->n_sms)), C1_THREADS, L.c1_smem, s>>>(r);
+          HONK_LAUNCH_CHECK();
+        }
+        in = act[li & 1];
+        continue;
+      }
       int Hin = L.Hin, Win = L.Win;
       PackParams pk{};
       pk.M = n * L.Ho * L.Wo;

@@ -238,3 +238,41 @@ def test_sgd_variants_against_oracle(momentum, wd, nesterov):
     for k, v in o["state"].items():
         if not k.endswith("num_batches_tracked"):
             assert rel_err(tr.read(k), v.astype(np.float64)) <= 1e-3, k
+
+
+@pytest.mark.parametrize("name", ["cnn-trad-pool2", "cnn-tstride4"])
+def test_cnn_batch64_with_supplied_masks_against_oracle(name):
+    """The reference's batch size (train.py:171) for the cnn-* family: two steps with caller-supplied Dropout masks against the
+    float64 oracle, float32's own noise on the case (the float32 oracle) as the yardstick like in the res* test."""
+    import honk_b200 as hb
+    from honk_b200 import train
+    cfg = dict(hb.find_config(name))
+    cfg["n_labels"] = 12
+    B = 64
+    clips, labels = synth.make_clips(2 * B, start=850000, labelled=True)
+    pre = hb.AudioPreprocessor()
+    mfcc = pre.compute_mfccs_batch(torch.from_numpy(clips).cuda()).float()
+    state = synth.make_state_dict(name, cfg, seed=8)
+    state = {k: (v * np.float32(0.3) if k.endswith("weight") else v) for k, v in state.items()}
+    model = make_model(name, cfg, state)
+    rng = np.random.default_rng(17)
+    h1 = (101 - cfg["conv1_size"][0]) // cfg["conv1_stride"][0] + 1
+    w1 = (40 - cfg["conv1_size"][1]) // cfg["conv1_stride"][1] + 1
+    hp, wp = h1 // cfg["conv1_pool"][0], w1 // cfg["conv1_pool"][1]
+    shapes = [(B, cfg["n_feature_maps1"], h1, w1), (B, cfg["n_feature_maps2"], hp - cfg["conv2_size"][0] + 1, wp - cfg["conv2_size"][1] + 1),
+              (B, cfg.get("dnn1_size", 0)), (B, cfg.get("dnn2_size", 0))]
+    batches = []
+    for i in range(2):
+        masks = [rng.integers(0, 2, sh).astype(np.uint8) if sh[-1] > 0 else None for sh in shapes]
+        batches.append((mfcc[i * B:(i + 1) * B].cpu().numpy(), labels[i * B:(i + 1) * B].astype(np.int64), masks))
+    ref = orc.sgd_train_steps(state, cfg, batches, lr=0.002, momentum=0.9, weight_decay=1e-5)
+    truth = orc.sgd_train_steps(state, cfg, batches, lr=0.002, momentum=0.9, weight_decay=1e-5, dtype=torch.float64)
+    tr = train.SgdTrainer(model, lr=0.002, momentum=0.9, weight_decay=1e-5)
+    losses = [float(tr.step(torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda(), dropout_masks=m)[1]) for x, y, m in batches]
+    assert np.allclose(losses, truth["losses"], atol=2e-4, rtol=1e-4), (losses, truth["losses"])
+    noise = max(rel_err(ref["state"][k], t) for k, t in truth["state"].items())
+    for k, t in truth["state"].items():
+        assert rel_err(tr.read(k), t) <= 2 * noise + 2e-4, (k, rel_err(tr.read(k), t), noise)
+    noise_g = max(rel_err(ref["momentum"][k], t) for k, t in truth["momentum"].items())
+    for k, t in truth["momentum"].items():
+        assert rel_err(tr.read("momentum:" + k), t) <= 2 * noise_g + 2e-4, (k, noise_g)

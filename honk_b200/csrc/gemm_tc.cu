@@ -239,8 +239,10 @@ struct ConvResParams {
   __half* C;                   // NHWC f16 [n_clips][Ho][Wo][ldc]
   int n_clips, NCG, R_alloc, Wp, KW, n_taps, tiles_per_clip, Ho, Wo, NT, ldc, relu, n_stage;
   int mode;                    // HONK_CR_MODE, timing experiments only (results are garbage): 1 no image reloads, 2 no epilogue math / stores, 4 no MMAs
+  int G;                       // clips per pass: their images are resident together and share one pass of the weight stream
 };
 
+template <int TPC>       // M tiles per clip as a constant (0: p.tiles_per_clip), so the issuing warp's inner loop unrolls
 __global__ void __launch_bounds__(GT_THREADS, 1) conv_res_kernel(const __grid_constant__ ConvResParams p) {
   extern __shared__ __align__(1024) unsigned char cr_smem[];
   __shared__ __align__(8) uint64_t bar_bfull[CR_MAXSTAGE], bar_bempty[CR_MAXSTAGE], bar_img[2], bar_acc[2];
@@ -250,7 +252,8 @@ __global__ void __launch_bounds__(GT_THREADS, 1) conv_res_kernel(const __grid_co
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   const int plane_bytes = p.R_alloc * 16, img_bytes = p.NCG * plane_bytes, b_stage = GT_KC * p.NT * 16;
-  unsigned char* ring = cr_smem + (img_bytes + 1023) / 1024 * 1024;
+  unsigned char* ring = cr_smem + (p.G * img_bytes + 1023) / 1024 * 1024;
+  const int n_pass = (p.n_clips + p.G - 1) / p.G, tpc = TPC ? TPC : p.tiles_per_clip;
   const uint32_t a_bfull = smem_u32(&bar_bfull[0]), a_bempty = smem_u32(&bar_bempty[0]);
   const uint32_t a_imgfull = smem_u32(&bar_img[0]), a_imgempty = smem_u32(&bar_img[1]);
   const uint32_t a_accfull = smem_u32(&bar_acc[0]), a_accempty = smem_u32(&bar_acc[1]);
@@ -280,12 +283,14 @@ __global__ void __launch_bounds__(GT_THREADS, 1) conv_res_kernel(const __grid_co
     // ======================================= producer =======================================
     if (lane == 0) {
       uint32_t it = 0, n = 0;
-      for (int clip = blockIdx.x; clip < p.n_clips; clip += gridDim.x, ++n) {
-        if (n > 0) mbar_wait(a_imgempty, (n - 1) & 1);             // the previous clip's MMAs have read the image
+      for (int q = blockIdx.x; q < n_pass; q += gridDim.x, ++n) {
+        if (n > 0) mbar_wait(a_imgempty, (n - 1) & 1);             // the previous pass's MMAs have read the images
+        const int n_here = min(p.G, p.n_clips - q * p.G);
         const bool skip_img = (p.mode & 1) && n > 0;
-        mbar_expect_tx(a_imgfull, skip_img ? plane_bytes : img_bytes);
-        const unsigned char* src = p.Ap + static_cast<long long>(clip) * img_bytes;
-        for (int cg = 0; cg < (skip_img ? 1 : p.NCG); ++cg) gt_bulk_load(smem_u32(cr_smem + cg * plane_bytes), src + static_cast<long long>(cg) * plane_bytes, plane_bytes, a_imgfull);
+        mbar_expect_tx(a_imgfull, skip_img ? plane_bytes : n_here * img_bytes);
+        const unsigned char* src = p.Ap + static_cast<long long>(q) * p.G * img_bytes;   // the pass's clips are contiguous
+        for (int pl = 0; pl < (skip_img ? 1 : n_here * p.NCG); ++pl)
+          gt_bulk_load(smem_u32(cr_smem + pl * plane_bytes), src + static_cast<long long>(pl) * plane_bytes, plane_bytes, a_imgfull);
         for (int ks = 0; ks < n_ks; ++ks, ++it) {
           const uint32_t s = it % CR_NSTAGE;
           if (it >= CR_NSTAGE) mbar_wait(a_bempty + 8 * s, ((it / CR_NSTAGE) & 1) ^ 1);
@@ -302,9 +307,10 @@ __global__ void __launch_bounds__(GT_THREADS, 1) conv_res_kernel(const __grid_co
     const uint64_t b_hi = make_desc(0, p.NT * 16, 128) & 0xFFFFFFFFFFFF0000ull;
     const uint32_t img = smem_u32(cr_smem);
     uint32_t it = 0, n = 0;
-    for (int clip = blockIdx.x; clip < p.n_clips; clip += gridDim.x, ++n) {
+    for (int q = blockIdx.x; q < n_pass; q += gridDim.x, ++n) {
+      const int n_g = (p.mode & 4) ? 0 : min(p.G, p.n_clips - q * p.G);
       mbar_wait(a_imgfull, n & 1);
-      if (n > 0) mbar_wait(a_accempty, (n - 1) & 1);               // the epilogue has drained the previous clip's accumulators
+      if (n > 0) mbar_wait(a_accempty, (n - 1) & 1);               // the epilogue has drained the previous pass's accumulators
       fence_after();
       for (int ks = 0; ks < n_ks; ++ks, ++it) {
         const uint32_t s = it % CR_NSTAGE;
@@ -314,10 +320,13 @@ __global__ void __launch_bounds__(GT_THREADS, 1) conv_res_kernel(const __grid_co
         if (gt_elect_one()) {
           const uint32_t sb = smem_u32(ring + s * b_stage);
           for (int j = 0; j < kc / 2; ++j) {
-            const uint32_t a0 = img + a_off[ks * (GT_KC / 2) + j];
+            uint32_t a_g = (img + a_off[ks * (GT_KC / 2) + j]) >> 4, d_g = tmem;
             const uint64_t bd = b_hi | ((sb + j * 2 * p.NT * 16) >> 4);
-            for (int t = 0; t < p.tiles_per_clip && !(p.mode & 4); ++t)
-              mma_f16_ss(tmem + t * p.NT, a_hi | ((a0 + t * 2048) >> 4), bd, idesc, (ks > 0 || j > 0) ? 1u : 0u);
+            const uint32_t acc = (ks > 0 || j > 0) ? 1u : 0u;
+            for (int g = 0; g < n_g; ++g, a_g += img_bytes >> 4, d_g += tpc * p.NT) {
+#pragma unroll
+              for (int t = 0; t < tpc; ++t) mma_f16_ss(d_g + t * p.NT, a_hi | (a_g + t * 128), bd, idesc, acc);
+            }
           }
           commit(a_bempty + 8 * s);
           if (ks == n_ks - 1) {
@@ -333,18 +342,20 @@ __global__ void __launch_bounds__(GT_THREADS, 1) conv_res_kernel(const __grid_co
     const int quad = warp & 3, row = quad * 32 + lane;
     const uint32_t tlane = static_cast<uint32_t>(quad * 32) << 16;
     uint32_t n = 0;
-    for (int clip = blockIdx.x; clip < p.n_clips; clip += gridDim.x, ++n) {
+    for (int q = blockIdx.x; q < n_pass; q += gridDim.x, ++n) {
+      const int n_here = min(p.G, p.n_clips - q * p.G), n_t = n_here * tpc;
       mbar_wait(a_accfull, n & 1);
       fence_after();
-      for (int t = 0; t < p.tiles_per_clip; ++t) {
+      for (int tt = 0, g = 0, t = 0; tt < n_t; ++tt, g += (t == tpc - 1), t = (t == tpc - 1) ? 0 : t + 1) {
+        const long long clip = static_cast<long long>(q) * p.G + g;
         const int r = t * 128 + row, ho = r / p.Wp, wo = r - ho * p.Wp;
         const bool valid = ho < p.Ho && wo < p.Wo;
-        __half* dst = p.C + ((static_cast<long long>(clip) * p.Ho + ho) * p.Wo + wo) * p.ldc;
+        __half* dst = p.C + ((clip * p.Ho + ho) * p.Wo + wo) * p.ldc;
         for (int c0 = 0; c0 < p.NT; c0 += 16) {
           uint32_t v[16];
-          tmem_ld16(tmem + tlane + t * p.NT + c0, v);
+          tmem_ld16(tmem + tlane + tt * p.NT + c0, v);
           tmem_ld_wait();
-          if (t == p.tiles_per_clip - 1 && c0 + 16 >= p.NT) {      // everything is in registers: hand the accumulators back
+          if (tt == n_t - 1 && c0 + 16 >= p.NT) {                  // everything is in registers: hand the accumulators back
             fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(a_accempty);
@@ -685,7 +696,7 @@ struct GemmLayer {
   int in_f32 = 0, Hin = 0, Win = 0, Cs = 1, ph = 1, pw = 1, KH = 1, KW = 1, sh = 1, sw = 1, Ho = 1, Wo = 1;
   int K = 0, KP = 0, N = 0, NT = 16, n_ntiles = 1, relu = 0;
   int imp = 0, R_alloc = 0, tiles_per_clip = 0;     // implicit mode (stride-1 conv over the pooled planar map): no A operand
-  int res = 0, res_smem = 0, res_stages = 4;        // ... with the clip's image resident in shared memory (conv_res_kernel)
+  int res = 0, res_smem = 0, res_stages = 4, res_G = 1;   // ... with the clips' images resident in shared memory (conv_res_kernel)
   int c1res = 0, c1_units = 0, c1_tiles = 0, c1_hph = 0, c1_smem = 0;   // conv1 over the resident x8p image (conv1_res_kernel)
   unsigned char* d_B = nullptr;
   float* d_bias = nullptr;
@@ -817,17 +828,21 @@ int cnn_gemm_plan_create(honk_model* m, CnnGemmPlan** out) {
       L.R_alloc = (L.tiles_per_clip * 128 + (L.KH - 1) * Wp + L.KW + 7) / 8 * 8;
       int max_smem_ = 0;
       HONK_CUDA(cudaDeviceGetAttribute(&max_smem_, cudaDevAttrMaxSharedMemoryPerBlockOptin, m->device));
-      const int img = ((L.Cs >> 3) * L.R_alloc * 16 + 1023) / 1024 * 1024;
-      const int b_stage = GT_KC * L.NT * 16;
-      L.res_stages = std::max(2, std::min(CR_MAXSTAGE, (max_smem_ - 4096 - img) / b_stage));
+      const int img1 = (L.Cs >> 3) * L.R_alloc * 16, b_stage = GT_KC * L.NT * 16;
+      // clips per pass: as many as TMEM (512 columns) and the shared memory next to a 4-stage weight ring hold, at most 4
+      L.res_G = std::max(1, std::min({4, 512 / std::max(1, L.tiles_per_clip * L.NT), (max_smem_ - 6144 - 4 * b_stage) / std::max(1, img1)}));
+      if (const char* e = getenv("HONK_CR_G")) L.res_G = std::max(1, std::min(L.res_G, atoi(e)));
+      const int img = (L.res_G * img1 + 1023) / 1024 * 1024;
+      L.res_stages = std::max(2, std::min(CR_MAXSTAGE, (max_smem_ - 6144 - img) / b_stage));
       if (const char* e = getenv("HONK_CR_STAGES")) L.res_stages = std::max(2, std::min(L.res_stages, atoi(e)));
       L.res_smem = img + L.res_stages * b_stage + 1024;
       static const bool no_res = getenv("HONK_GEMM_RESIDENT") && atoi(getenv("HONK_GEMM_RESIDENT")) == 0;
-      L.res = !no_res && L.n_ntiles == 1 && L.tiles_per_clip * L.NT <= 512 && L.KP / 2 <= CR_MAXSTEPS && L.res_smem + 2048 <= max_smem_ && L.R_alloc < 16384;
-      // measured (profiles/r04_configs.json): the resident kernel wins when a clip has at least two M tiles (cnn-tpool2/3,
-      // tstride2/4: conv2 + its operand 3.1 -> 1.6 ms, 3.3 -> 1.4, 1.5 -> 1.0 per 4096 clips); with a single tile per clip
-      // (cnn-tstride8) every clip streams the whole weight tensor for 160 MMAs and the materialised operand is faster
-      if (!L.res || L.tiles_per_clip < 2) L.imp = L.res = 0;
+      L.res = !no_res && L.n_ntiles == 1 && L.tiles_per_clip * L.NT <= 512 && L.KP / 2 <= CR_MAXSTEPS && L.res_smem + 5120 <= max_smem_ && L.R_alloc < 16384;
+      // measured (profiles/r04_configs.json): the resident kernel wins when a pass over the weight stream feeds at least two M
+      // tiles (cnn-tpool2/3: three tiles of one clip; tstride2/4: two clips of three / two tiles; tstride8: three clips of one
+      // tile; conv2 + its operand 3.1 -> 1.5, 3.3 -> 1.0, 1.5 -> 0.67, 0.66 -> 0.38 ms per 4096 clips); with a single tile per
+      // pass every tile streams the whole weight tensor and the materialised operand is faster
+      if (!L.res || L.tiles_per_clip * L.res_G < 2) L.imp = L.res = 0;
     }
     H = L.Ho; W = L.Wo; C = L.N; Cs = L.ldc(); ph = c.conv2_pool[0]; pw = c.conv2_pool[1];
     p->layers.push_back(L);
@@ -882,7 +897,13 @@ int cnn_gemm_plan_create(honk_model* m, CnnGemmPlan** out) {
     int res_smem = 0;
     for (const GemmLayer& L : p->layers)
       if (L.res) res_smem = std::max(res_smem, L.res_smem);
-    if (res_smem) HONK_CUDA(cudaFuncSetAttribute(conv_res_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, res_smem));
+    if (res_smem) {
+      HONK_CUDA(cudaFuncSetAttribute(conv_res_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, res_smem));
+      HONK_CUDA(cudaFuncSetAttribute(conv_res_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, res_smem));
+      HONK_CUDA(cudaFuncSetAttribute(conv_res_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, res_smem));
+      HONK_CUDA(cudaFuncSetAttribute(conv_res_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, res_smem));
+      HONK_CUDA(cudaFuncSetAttribute(conv_res_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, res_smem));
+    }
     if (p->layers[0].c1res) HONK_CUDA(cudaFuncSetAttribute(conv1_res_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, p->layers[0].c1_smem));
   }
   *out = p.release();
@@ -998,11 +1019,18 @@ int cnn_gemm_forward(const CnnGemmPlan* p, const float* d_mfcc, int64_t n_clips,
         ConvResParams r{};
         r.Ap = pooled; r.B = L.d_B; r.bias = L.d_bias; r.C = reinterpret_cast<__half*>(act[li & 1]);
         r.n_clips = static_cast<int>(n); r.NCG = L.Cs >> 3; r.R_alloc = L.R_alloc; r.Wp = L.Win / L.pw; r.KW = L.KW; r.n_taps = L.KH * L.KW;
-        r.tiles_per_clip = L.tiles_per_clip; r.Ho = L.Ho; r.Wo = L.Wo; r.NT = L.NT; r.ldc = L.ldc(); r.relu = L.relu; r.n_stage = L.res_stages;
+        r.tiles_per_clip = L.tiles_per_clip; r.Ho = L.Ho; r.Wo = L.Wo; r.NT = L.NT; r.ldc = L.ldc(); r.relu = L.relu; r.n_stage = L.res_stages; r.G = L.res_G;
         static const int cr_mode = getenv("HONK_CR_MODE") ? atoi(getenv("HONK_CR_MODE")) : 0;
         r.mode = cr_mode;
         ProfSpan sp(kGemm[std::min<size_t>(li, 5)], s);
-        conv_res_kernel<<<static_cast<unsigned>(std::min<long long>(n, p->n_sms)), GT_THREADS, L.res_smem, s>>>(r);
+        const unsigned grid = static_cast<unsigned>(std::min<long long>((n + L.res_G - 1) / L.res_G, p->n_sms));
+        switch (L.tiles_per_clip) {
+          case 1: conv_res_kernel<1><<<grid, GT_THREADS, L.res_smem, s>>>(r); break;
+          case 2: conv_res_kernel<2><<<grid, GT_THREADS, L.res_smem, s>>>(r); break;
+          case 3: conv_res_kernel<3><<<grid, GT_THREADS, L.res_smem, s>>>(r); break;
+          case 4: conv_res_kernel<4><<<grid, GT_THREADS, L.res_smem, s>>>(r); break;
+          default: conv_res_kernel<0><<<grid, GT_THREADS, L.res_smem, s>>>(r); break;
+        }
         HONK_LAUNCH_CHECK();
       } else {
         ProfSpan sp(kGemm[std::min<size_t>(li, 5)], s);

@@ -394,6 +394,11 @@ struct Conv1ResParams {
   const float* bias;
   __half* C;                   // NHWC f16 [n_clips][Ho][Wo][ldc]
   int n_clips, img_bytes, KP, NT, ldc, Hph, Ho, Wo, n_tiles, lbo, sh, phase_stride;   // phase_stride = Wx * Hph rows
+  int mode;                    // HONK_C1_MODE, timing experiments only (results are garbage): 2 no epilogue stores, 4 no MMAs
+  // fused MaxPool(ph, pw) (model.py:190): Hph = 128, so tile t is coefficient column wo = t and a thread keeps ONE time row in
+  // every tile; the epilogue writes the pooled map as the next layer's planar image P[clip][cg][R_alloc rows][8 halves]
+  int fuse, ph, pw, Hp, Wp, R_alloc, cpt;
+  unsigned char* P;
 };
 
 __global__ void __launch_bounds__(256) x8p_pack_kernel(const float* __restrict__ mfcc, unsigned char* __restrict__ X, int H, int W, int sh, int Hph,
@@ -415,17 +420,31 @@ __global__ void __launch_bounds__(256) x8p_pack_kernel(const float* __restrict__
   }
 }
 
+__device__ __forceinline__ uint32_t pk_hmax2(uint32_t a, uint32_t b) {
+  uint32_t o;
+  asm("max.f16x2 %0, %1, %2;" : "=r"(o) : "r"(a), "r"(b));
+  return o;
+}
+
+constexpr int C1_FUSE_MAXNT = 128;       // fused pool: the column maxima of a warp's half of the channels stay in registers
+constexpr int C1_MAXSTEPS = 64;          // kernel-row pairs of conv1 (KH <= 128)
 constexpr int C1_THREADS = 10 * 32;      // producer, MMA issuer, 8 epilogue warps (two per TMEM lane quarter, half the channels each)
 
 __global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_constant__ Conv1ResParams p) {
   extern __shared__ __align__(1024) unsigned char c1_smem[];
   __shared__ __align__(8) uint64_t bar_w, bar_imgfull[2], bar_imgempty[2], bar_accfull[2], bar_accempty[2];
   __shared__ __align__(16) float bias_s[GT_MAXNT];
+  __shared__ uint32_t c1_aoff[C1_MAXSTEPS];                       // A window of every K = 16 step (a kernel-row pair), bytes from the tile's first unit
   __shared__ uint32_t tmem_base_s;
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   const int img_al = (p.img_bytes + 1023) / 1024 * 1024, w_bytes = p.KP * p.NT * 16;
+  for (int j = tid; j < p.KP / 2; j += C1_THREADS) {               // no index arithmetic in the issuing warp's loop
+    const int kh = 2 * j;                                          // kernel rows (kh, kh + 1): phases kh % sh and the next one
+    c1_aoff[j] = static_cast<uint32_t>(((kh % p.sh) * p.phase_stride + kh / p.sh) * 16);
+  }
   unsigned char* wsm = c1_smem + 2 * img_al;
+  unsigned char* xch = wsm + (w_bytes + 1023) / 1024 * 1024;      // fused pool: two [Hp * ph rows][NT halves + 16 bytes] exchange buffers
   const uint32_t a_w = smem_u32(&bar_w), a_imgfull = smem_u32(&bar_imgfull[0]), a_imgempty = smem_u32(&bar_imgempty[0]);
   const uint32_t a_accfull = smem_u32(&bar_accfull[0]), a_accempty = smem_u32(&bar_accempty[0]);
   if (tid == 0) {
@@ -481,11 +500,10 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_c
         }
         if (gt_elect_one()) {
           const uint32_t d = tmem + ab * 256;
-          for (int j = 0; j < p.KP / 2; ++j) {
-            const int kh = 2 * j;                                      // kernel rows (kh, kh + 1): phases kh % sh and the next one
-            const uint32_t a0 = img + (t * 128 + (kh % p.sh) * p.phase_stride + kh / p.sh) * 16;
-            mma_f16_ss(d, a_hi | (a0 >> 4), b_hi | ((wb + j * 2 * p.NT * 16) >> 4), idesc, j > 0 ? 1u : 0u);
-          }
+          const uint32_t a_t = img + t * 2048, n_j = (p.mode & 4) ? 0 : p.KP / 2;
+          uint32_t bd = wb >> 4;
+          for (uint32_t j = 0; j < n_j; ++j, bd += 2 * p.NT)
+            mma_f16_ss(d, a_hi | ((a_t + c1_aoff[j]) >> 4), b_hi | bd, idesc, j > 0 ? 1u : 0u);
           commit(a_accfull + 8 * ab);
           if (t == p.n_tiles - 1) commit(a_imgempty + 8 * ib);
         }
@@ -498,6 +516,70 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_c
     const uint32_t tlane = static_cast<uint32_t>(quad * 32) << 16;
     const int n16 = p.NT / 16, c_lo = half == 0 ? 0 : (n16 + 1) / 2, c_hi = half == 0 ? (n16 + 1) / 2 : n16;   // 16-column groups
     uint32_t c = 0;
+    if (p.fuse) {
+      // max over the pw coefficient columns in registers (tile = column, thread = time row), then bias + ReLU + f16 (all monotonic,
+      // so the order against the reference's conv -> ReLU -> pool does not change a bit), max over ph time rows through shared memory
+      constexpr int MAXG = C1_FUSE_MAXNT / 32;
+      float rm[MAXG][16];
+      const int n_g = c_hi - c_lo, xrow = p.NT * 2 + 16, etid = tid - 64, rows_p = p.Hp * p.ph;
+      uint32_t xb = 0;
+      for (int clip = blockIdx.x; clip < p.n_clips; clip += gridDim.x) {
+        for (int t = 0, wq = 0, wp = 0; t < p.n_tiles; ++t, ++c) {
+          const uint32_t ab = c & 1;
+          mbar_wait(a_accfull + 8 * ab, (c >> 1) & 1);
+          fence_after();
+#pragma unroll
+          for (int gi = 0; gi < MAXG; ++gi) {
+            if (gi >= n_g) break;
+            uint32_t v[16];
+            tmem_ld16(tmem + tlane + ab * 256 + (c_lo + gi) * 16, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int k = 0; k < 16; ++k) rm[gi][k] = wq == 0 ? __uint_as_float(v[k]) : fmaxf(rm[gi][k], __uint_as_float(v[k]));
+          }
+          fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(a_accempty + 8 * ab);
+          if (++wq < p.pw) continue;
+          wq = 0;
+          if (wp >= p.Wp) continue;                                  // floor mode: the last Wo % pw columns are dropped
+          unsigned char* xs = xch + xb * (rows_p * xrow);
+          if (row < rows_p && !(p.mode & 2)) {
+#pragma unroll
+            for (int gi = 0; gi < MAXG; ++gi) {
+              if (gi >= n_g) break;
+              const int c0 = (c_lo + gi) * 16;
+              float f[16];
+#pragma unroll
+              for (int k = 0; k < 16; k += 4) {
+                const float4 b4 = *reinterpret_cast<const float4*>(&bias_s[c0 + k]);
+                f[k] = fmaxf(rm[gi][k] + b4.x, 0.f);
+                f[k + 1] = fmaxf(rm[gi][k + 1] + b4.y, 0.f);
+                f[k + 2] = fmaxf(rm[gi][k + 2] + b4.z, 0.f);
+                f[k + 3] = fmaxf(rm[gi][k + 3] + b4.w, 0.f);
+              }
+              uint4* d = reinterpret_cast<uint4*>(xs + row * xrow + c0 * 2);
+              d[0] = make_uint4(gt_pack_h2(f[0], f[1]), gt_pack_h2(f[2], f[3]), gt_pack_h2(f[4], f[5]), gt_pack_h2(f[6], f[7]));
+              d[1] = make_uint4(gt_pack_h2(f[8], f[9]), gt_pack_h2(f[10], f[11]), gt_pack_h2(f[12], f[13]), gt_pack_h2(f[14], f[15]));
+            }
+          }
+          asm volatile("bar.sync 1, 256;" ::: "memory");             // the 8 epilogue warps: the column block is staged
+          uint4* P = reinterpret_cast<uint4*>(p.P) + static_cast<long long>(clip) * p.cpt * p.R_alloc;
+          for (int u = etid; u < p.Hp * p.cpt && !(p.mode & 2); u += 256) {
+            const int hp = u / p.cpt, cg = u - hp * p.cpt;
+            const unsigned char* src = xs + (hp * p.ph) * xrow + cg * 16;
+            uint4 o = *reinterpret_cast<const uint4*>(src);
+            for (int i = 1; i < p.ph; ++i) {
+              const uint4 q = *reinterpret_cast<const uint4*>(src + i * xrow);
+              o.x = pk_hmax2(o.x, q.x); o.y = pk_hmax2(o.y, q.y); o.z = pk_hmax2(o.z, q.z); o.w = pk_hmax2(o.w, q.w);
+            }
+            P[static_cast<long long>(cg) * p.R_alloc + hp * p.Wp + wp] = o;
+          }
+          xb ^= 1;                                                   // the other buffer is two barriers away from its readers
+          ++wp;
+        }
+      }
+    } else
     for (int clip = blockIdx.x; clip < p.n_clips; clip += gridDim.x) {
       for (int t = 0; t < p.n_tiles; ++t, ++c) {
         const uint32_t ab = c & 1;
@@ -516,7 +598,7 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_c
             __syncwarp();
             if (lane == 0) mbar_arrive(a_accempty + 8 * ab);
           }
-          if (!valid) continue;
+          if (!valid || (p.mode & 2)) continue;
           float f[16];
 #pragma unroll
           for (int k = 0; k < 16; k += 4) {
@@ -550,12 +632,6 @@ struct PackParams {
   int KH, KW, sh, sw, Ho, Wo;  // kernel over the POOLED map, strides, output map
   int K, KP;                   // real K = KH * KW * Cs and planes (multiple of 2)
 };
-
-__device__ __forceinline__ uint32_t pk_hmax2(uint32_t a, uint32_t b) {
-  uint32_t o;
-  asm("max.f16x2 %0, %1, %2;" : "=r"(o) : "r"(a), "r"(b));
-  return o;
-}
 
 // One thread per ROW m of A: (clip, ho, wo) is decoded once, then the thread walks the K planes of its row.  Consecutive threads
 // are consecutive rows, so every plane step of a warp is 32 adjacent 16-byte stores, and neighbouring rows read overlapping
@@ -698,6 +774,8 @@ struct GemmLayer {
   int imp = 0, R_alloc = 0, tiles_per_clip = 0;     // implicit mode (stride-1 conv over the pooled planar map): no A operand
   int res = 0, res_smem = 0, res_stages = 4, res_G = 1;   // ... with the clips' images resident in shared memory (conv_res_kernel)
   int c1res = 0, c1_units = 0, c1_tiles = 0, c1_hph = 0, c1_smem = 0;   // conv1 over the resident x8p image (conv1_res_kernel)
+  int c1_fuse = 0;             // ... whose epilogue applies the MaxPool and writes the next layer's planar image
+  int planar_in = 0;           // the previous layer wrote this layer's planar image (no gemm_pool_planar_kernel pass)
   unsigned char* d_B = nullptr;
   float* d_bias = nullptr;
   int ldc() const { return NT * n_ntiles; }
@@ -792,14 +870,15 @@ int cnn_gemm_plan_create(honk_model* m, CnnGemmPlan** out) {
       HONK_CUDA(cudaDeviceGetAttribute(&max_smem_, cudaDevAttrMaxSharedMemoryPerBlockOptin, m->device));
       const int sh = L.sh, Wx = m->W0 - 7, Hph = (m->H0 + sh - 1) / sh;
       // measured: time strides 4 and 8 (cnn-tstride4/8) have too few rows per phase image for this to beat the im2col operand
-      if (!no_c1 && L.KW == 8 && L.sw == 1 && L.n_ntiles == 1 && (sh == 1 || sh == 2) && L.Ho * L.Wo >= 256 && L.Wo == Wx) {
+      static const int c1_maxsh = getenv("HONK_C1_MAXSH") ? atoi(getenv("HONK_C1_MAXSH")) : 2;
+      if (!no_c1 && L.KW == 8 && L.sw == 1 && L.n_ntiles == 1 && (sh == 1 || (sh % 2 == 0 && sh <= c1_maxsh)) && L.Ho * L.Wo >= 256 && L.Wo == Wx) {
         L.c1_hph = Hph;
         L.c1_tiles = (Wx * Hph + 127) / 128;
         L.c1_units = ((sh - 1) * Wx * Hph + L.c1_tiles * 128 + L.KH / sh + 2 + 7) / 8 * 8;
         L.c1_units = std::max(L.c1_units, sh * Wx * Hph);
         const int img_al = (L.c1_units * 16 + 1023) / 1024 * 1024;
         L.c1_smem = 2 * img_al + L.KP * L.NT * 16 + 1024;
-        L.c1res = L.c1_smem + 2048 <= max_smem_ && (sh == 1 ? 16 : Wx * Hph * 16) < (1 << 18);
+        L.c1res = L.c1_smem + 2048 <= max_smem_ && L.KP / 2 <= C1_MAXSTEPS && (sh == 1 ? 16 : Wx * Hph * 16) < (1 << 18);
       }
     }
     H = L.Ho; W = L.Wo; C = L.N; Cs = L.ldc(); ph = c.conv1_pool[0]; pw = c.conv1_pool[1];
@@ -843,6 +922,19 @@ int cnn_gemm_plan_create(honk_model* m, CnnGemmPlan** out) {
       // tile; conv2 + its operand 3.1 -> 1.5, 3.3 -> 1.0, 1.5 -> 0.67, 0.66 -> 0.38 ms per 4096 clips); with a single tile per
       // pass every tile streams the whole weight tensor and the materialised operand is faster
       if (!L.res || L.tiles_per_clip * L.res_G < 2) L.imp = L.res = 0;
+      // conv1's epilogue can do the MaxPool and write this image itself when a thread keeps one time row across the
+      // coefficient columns (column stride 128 in the x8p image) and the column maxima fit its registers
+      GemmLayer& L1 = p->layers[0];
+      static const bool no_fuse = getenv("HONK_C1_FUSE") && atoi(getenv("HONK_C1_FUSE")) == 0;
+      if (!no_fuse && L.res && L1.c1res && L1.sh == 1 && m->H0 <= 128 && L1.NT <= C1_FUSE_MAXNT && L.pw <= L1.Wo && L.ph <= L1.Ho) {
+        const int Wx = m->W0 - 7, units = (Wx * 128 + L1.KH + 2 + 7) / 8 * 8, img_al = (units * 16 + 1023) / 1024 * 1024;
+        const int w_al = (L1.KP * L1.NT * 16 + 1023) / 1024 * 1024, xch = 2 * (L.Hin / L.ph) * L.ph * (L1.NT * 2 + 16);
+        const int smem = 2 * img_al + w_al + xch + 1024;
+        if (smem + 2048 <= max_smem_) {
+          L1.c1_fuse = 1; L1.c1_hph = 128; L1.c1_tiles = Wx; L1.c1_units = units; L1.c1_smem = smem;
+          L.planar_in = 1;
+        }
+      }
     }
     H = L.Ho; W = L.Wo; C = L.N; Cs = L.ldc(); ph = c.conv2_pool[0]; pw = c.conv2_pool[1];
     p->layers.push_back(L);
@@ -959,6 +1051,13 @@ int cnn_gemm_forward(const CnnGemmPlan* p, const float* d_mfcc, int64_t n_clips,
         r.n_clips = static_cast<int>(n); r.img_bytes = L.c1_units * 16; r.KP = L.KP; r.NT = L.NT; r.ldc = L.ldc(); r.Hph = L.c1_hph;
         r.Ho = L.Ho; r.Wo = L.Wo; r.n_tiles = L.c1_tiles; r.sh = L.sh; r.phase_stride = (p->W0 - 7) * L.c1_hph;
         r.lbo = L.sh == 1 ? 16 : r.phase_stride * 16;
+        if (L.c1_fuse) {
+          const GemmLayer& L2 = p->layers[1];
+          r.fuse = 1; r.ph = L2.ph; r.pw = L2.pw; r.Hp = L2.Hin / L2.ph; r.Wp = L2.Win / L2.pw; r.R_alloc = L2.R_alloc; r.cpt = L2.Cs >> 3;
+          r.P = pooled;
+        }
+        static const int c1_mode = getenv("HONK_C1_MODE") ? atoi(getenv("HONK_C1_MODE")) : 0;
+        r.mode = c1_mode;
         {
           ProfSpan sp(kGemm[0], s);
           conv1_res_kernel<<<static_cast<unsigned>(std::min<long long>(n, p->n_sms)), C1_THREADS, L.c1_smem, s>>>(r);
@@ -971,7 +1070,9 @@ int cnn_gemm_forward(const CnnGemmPlan* p, const float* d_mfcc, int64_t n_clips,
       PackParams pk{};
       pk.M = n * L.Ho * L.Wo;
       long long n_mtiles = (pk.M + 127) / 128;
-      if (L.imp) {
+      if (L.imp && L.planar_in) {
+        n_mtiles = n * L.tiles_per_clip;                   // conv1's epilogue wrote the pooled planar image
+      } else if (L.imp) {
         // MaxPool into the planar image the GEMM's producer reads by tap offsets: no A operand for this layer
         ProfSpan sp(kPack[std::min<size_t>(li, 5)], s);
         const long long units = n * (L.Cs >> 3) * L.R_alloc;

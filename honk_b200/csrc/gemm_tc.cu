@@ -397,7 +397,9 @@ struct Conv1ResParams {
   int mode;                    // HONK_C1_MODE, timing experiments only (results are garbage): 2 no epilogue stores, 4 no MMAs
   // fused MaxPool(ph, pw) (model.py:190): Hph = 128, so tile t is coefficient column wo = t and a thread keeps ONE time row in
   // every tile; the epilogue writes the pooled map as the next layer's planar image P[clip][cg][R_alloc rows][8 halves]
-  int fuse, ph, pw, Hp, Wp, R_alloc, cpt;
+  // fuse = 2 (time stride > 1): column stride Hc = 1 << hc_shift <= 64 rows, several columns per tile; the ReLU-ed f16 rows go to a
+  // ring of n_cols columns in shared memory and every complete block of pw columns is pooled from there
+  int fuse, ph, pw, Hp, Wp, R_alloc, cpt, hc_shift, n_cols;
   unsigned char* P;
 };
 
@@ -426,9 +428,52 @@ __device__ __forceinline__ uint32_t pk_hmax2(uint32_t a, uint32_t b) {
   return o;
 }
 
+// The same image for the 40-coefficient geometry, one thread per TIME ROW: the row's 40 values are read once (contiguous), kept as 20
+// packed words, and the 33 units of the row (sliding windows of 8 halves) go out with consecutive threads = consecutive time rows of
+// one coefficient column, i.e. coalesced 16-byte stores.  Rows are numbered phase-major like the image (row = phase * Hph + i).
+__global__ void __launch_bounds__(128) x8p_pack_rows40_kernel(const float* __restrict__ mfcc, unsigned char* __restrict__ X, int H, int sh, int Hph,
+                                                              int img_units) {
+  constexpr int W = 40, Wx = 33;
+  const float* src = mfcc + static_cast<long long>(blockIdx.x) * H * W;
+  uint4* dst = reinterpret_cast<uint4*>(X) + static_cast<long long>(blockIdx.x) * img_units;
+  for (int row = threadIdx.x; row < sh * Hph; row += blockDim.x) {
+    const int ph = row / Hph, i = row - ph * Hph, h = i * sh + ph;
+    uint32_t w[W / 2 + 1];
+    if (h < H) {
+      const float4* s4 = reinterpret_cast<const float4*>(src + h * W);                 // clips and rows are multiples of 16 bytes
+#pragma unroll
+      for (int k = 0; k < W / 4; ++k) {
+        const float4 q = __ldg(s4 + k);
+        w[2 * k] = gt_pack_h2(fminf(fmaxf(q.x, -60000.f), 60000.f), fminf(fmaxf(q.y, -60000.f), 60000.f));
+        w[2 * k + 1] = gt_pack_h2(fminf(fmaxf(q.z, -60000.f), 60000.f), fminf(fmaxf(q.w, -60000.f), 60000.f));
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < W / 2; ++k) w[k] = 0;
+    }
+    w[W / 2] = 0;
+    uint4* d = dst + static_cast<long long>(ph) * Wx * Hph + i;
+#pragma unroll
+    for (int wx = 0; wx < Wx; ++wx) {
+      const int k = wx >> 1;
+      uint4 o;
+      if (wx & 1) {
+        o = make_uint4(__funnelshift_r(w[k], w[k + 1], 16), __funnelshift_r(w[k + 1], w[k + 2], 16), __funnelshift_r(w[k + 2], w[k + 3], 16),
+                       __funnelshift_r(w[k + 3], w[k + 4], 16));
+      } else {
+        o = make_uint4(w[k], w[k + 1], w[k + 2], w[k + 3]);
+      }
+      d[static_cast<long long>(wx) * Hph] = o;
+    }
+  }
+  for (int u = sh * Wx * Hph + threadIdx.x; u < img_units; u += blockDim.x) dst[u] = make_uint4(0, 0, 0, 0);   // the tiles' over-read
+}
+
 constexpr int C1_FUSE_MAXNT = 128;       // fused pool: the column maxima of a warp's half of the channels stay in registers
 constexpr int C1_MAXSTEPS = 64;          // kernel-row pairs of conv1 (KH <= 128)
-constexpr int C1_THREADS = 10 * 32;      // producer, MMA issuer, 8 epilogue warps (two per TMEM lane quarter, half the channels each)
+constexpr int C1_EPI = 16;               // epilogue warps: four per TMEM lane quarter, a quarter of the channels each (their dependent
+                                         // instruction chains, not issue slots, bound the kernel: 8 warps measured 25-35 % slower)
+constexpr int C1_THREADS = (2 + C1_EPI) * 32;      // producer, MMA issuer, epilogue
 
 __global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_constant__ Conv1ResParams p) {
   extern __shared__ __align__(1024) unsigned char c1_smem[];
@@ -453,7 +498,7 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_c
       mbar_init(a_imgfull + 8 * k, 1);
       mbar_init(a_imgempty + 8 * k, 1);
       mbar_init(a_accfull + 8 * k, 1);
-      mbar_init(a_accempty + 8 * k, 8);
+      mbar_init(a_accempty + 8 * k, C1_EPI);
     }
     fence_mbar_init();
   }
@@ -512,16 +557,17 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_c
     }
   } else {
     // ======================================= epilogue =======================================
-    const int quad = warp & 3, row = quad * 32 + lane, half = (warp - 2) >> 2;          // column half of this warp
+    const int quad = warp & 3, row = quad * 32 + lane, part = (warp - 2) >> 2;          // column part of this warp
     const uint32_t tlane = static_cast<uint32_t>(quad * 32) << 16;
-    const int n16 = p.NT / 16, c_lo = half == 0 ? 0 : (n16 + 1) / 2, c_hi = half == 0 ? (n16 + 1) / 2 : n16;   // 16-column groups
+    const int n16 = p.NT / 16, c_lo = part * n16 / (C1_EPI / 4), c_hi = (part + 1) * n16 / (C1_EPI / 4);   // 16-column groups
     uint32_t c = 0;
-    if (p.fuse) {
+    if (p.fuse == 1) {
       // max over the pw coefficient columns in registers (tile = column, thread = time row), then bias + ReLU + f16 (all monotonic,
       // so the order against the reference's conv -> ReLU -> pool does not change a bit), max over ph time rows through shared memory
-      constexpr int MAXG = C1_FUSE_MAXNT / 32;
+      constexpr int MAXG = (C1_FUSE_MAXNT / 16 + C1_EPI / 4 - 1) / (C1_EPI / 4);
       float rm[MAXG][16];
-      const int n_g = c_hi - c_lo, xrow = p.NT * 2 + 16, etid = tid - 64, rows_p = p.Hp * p.ph;
+      const int n_g = c_hi - c_lo, xrow = p.NT * 2 + 16, etid = tid - 64, rows_p = p.Hp * p.ph, upc = p.Hp * p.cpt;
+      const int hp0 = etid / p.cpt, cg0 = etid - hp0 * p.cpt, d_hp = C1_EPI * 32 / p.cpt, d_cg = C1_EPI * 32 - d_hp * p.cpt;   // this thread's pooled units
       uint32_t xb = 0;
       for (int clip = blockIdx.x; clip < p.n_clips; clip += gridDim.x) {
         for (int t = 0, wq = 0, wp = 0; t < p.n_tiles; ++t, ++c) {
@@ -563,10 +609,9 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_c
               d[1] = make_uint4(gt_pack_h2(f[8], f[9]), gt_pack_h2(f[10], f[11]), gt_pack_h2(f[12], f[13]), gt_pack_h2(f[14], f[15]));
             }
           }
-          asm volatile("bar.sync 1, 256;" ::: "memory");             // the 8 epilogue warps: the column block is staged
+          asm volatile("bar.sync 1, %0;" ::"n"(C1_EPI * 32) : "memory");             // the 8 epilogue warps: the column block is staged
           uint4* P = reinterpret_cast<uint4*>(p.P) + static_cast<long long>(clip) * p.cpt * p.R_alloc;
-          for (int u = etid; u < p.Hp * p.cpt && !(p.mode & 2); u += 256) {
-            const int hp = u / p.cpt, cg = u - hp * p.cpt;
+          for (int u = etid, hp = hp0, cg = cg0; u < upc && !(p.mode & 2); u += C1_EPI * 32) {
             const unsigned char* src = xs + (hp * p.ph) * xrow + cg * 16;
             uint4 o = *reinterpret_cast<const uint4*>(src);
             for (int i = 1; i < p.ph; ++i) {
@@ -574,10 +619,87 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_c
               o.x = pk_hmax2(o.x, q.x); o.y = pk_hmax2(o.y, q.y); o.z = pk_hmax2(o.z, q.z); o.w = pk_hmax2(o.w, q.w);
             }
             P[static_cast<long long>(cg) * p.R_alloc + hp * p.Wp + wp] = o;
+            hp += d_hp;                                              // the unit one stride further on, without a division
+            cg += d_cg;
+            if (cg >= p.cpt) {
+              cg -= p.cpt;
+              ++hp;
+            }
           }
           xb ^= 1;                                                   // the other buffer is two barriers away from its readers
           ++wp;
         }
+      }
+    } else if (p.fuse == 2) {
+      const int xrow = p.NT * 2 + 16, etid = tid - 64, rows_p = p.Hp * p.ph, col_bytes = rows_p * xrow, upc = p.Hp * p.cpt;
+      const int col_in_tile = row >> p.hc_shift, ho = row & ((1 << p.hc_shift) - 1);      // this thread's place in every tile
+      const int hp0 = etid / p.cpt, cg0 = etid - hp0 * p.cpt, d_hp = C1_EPI * 32 / p.cpt, d_cg = C1_EPI * 32 - d_hp * p.cpt;   // its pooled units
+      for (int clip = blockIdx.x; clip < p.n_clips; clip += gridDim.x) {
+        uint4* P = reinterpret_cast<uint4*>(p.P) + static_cast<long long>(clip) * p.cpt * p.R_alloc;
+        for (int t = 0, wp_done = 0, pslot = 0, tslot = 0; t < p.n_tiles; ++t, ++c) {   // ring slots of the next column block / tile
+          const uint32_t ab = c & 1;
+          mbar_wait(a_accfull + 8 * ab, (c >> 1) & 1);
+          fence_after();
+          const int col = (t << (7 - p.hc_shift)) + col_in_tile;
+          const bool valid = ho < rows_p && col < p.Wp * p.pw && !(p.mode & 2);
+          int slot = tslot + col_in_tile;
+          if (slot >= p.n_cols) slot -= p.n_cols;
+          unsigned char* xs = xch + slot * col_bytes + ho * xrow;
+          tslot += 1 << (7 - p.hc_shift);
+          if (tslot >= p.n_cols) tslot -= p.n_cols;
+          if (c_lo == c_hi && lane == 0) mbar_arrive(a_accempty + 8 * ab);       // fewer column groups than parts
+          for (int g = c_lo; g < c_hi; ++g) {
+            const int c0 = g * 16;
+            uint32_t v[16];
+            tmem_ld16(tmem + tlane + ab * 256 + c0, v);
+            tmem_ld_wait();
+            if (g == c_hi - 1) {
+              fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(a_accempty + 8 * ab);
+            }
+            if (!valid) continue;
+            float f[16];
+#pragma unroll
+            for (int k = 0; k < 16; k += 4) {
+              const float4 b4 = *reinterpret_cast<const float4*>(&bias_s[c0 + k]);
+              f[k] = fmaxf(__uint_as_float(v[k]) + b4.x, 0.f);
+              f[k + 1] = fmaxf(__uint_as_float(v[k + 1]) + b4.y, 0.f);
+              f[k + 2] = fmaxf(__uint_as_float(v[k + 2]) + b4.z, 0.f);
+              f[k + 3] = fmaxf(__uint_as_float(v[k + 3]) + b4.w, 0.f);
+            }
+            uint4* d = reinterpret_cast<uint4*>(xs + c0 * 2);
+            d[0] = make_uint4(gt_pack_h2(f[0], f[1]), gt_pack_h2(f[2], f[3]), gt_pack_h2(f[4], f[5]), gt_pack_h2(f[6], f[7]));
+            d[1] = make_uint4(gt_pack_h2(f[8], f[9]), gt_pack_h2(f[10], f[11]), gt_pack_h2(f[12], f[13]), gt_pack_h2(f[14], f[15]));
+          }
+          asm volatile("bar.sync 1, %0;" ::"n"(C1_EPI * 32) : "memory");             // the 8 epilogue warps: the tile's columns are staged
+          const int wp_end = min(p.Wp, min(p.Wo, ((t + 1) * 128) >> p.hc_shift) / p.pw);
+          for (int wp = wp_done; wp < wp_end && !(p.mode & 2); ++wp) {
+            for (int u = etid, hp = hp0, cg = cg0; u < upc; u += C1_EPI * 32) {
+              const unsigned char* base = xch + (hp * p.ph) * xrow + cg * 16;
+              uint4 o = make_uint4(0, 0, 0, 0);                      // the staged values are ReLU-ed: 0 is the identity of the max
+              for (int j = 0, sj = pslot; j < p.pw; ++j) {
+                const unsigned char* src = base + sj * col_bytes;
+                for (int i = 0; i < p.ph; ++i) {
+                  const uint4 q = *reinterpret_cast<const uint4*>(src + i * xrow);
+                  o.x = pk_hmax2(o.x, q.x); o.y = pk_hmax2(o.y, q.y); o.z = pk_hmax2(o.z, q.z); o.w = pk_hmax2(o.w, q.w);
+                }
+                if (++sj == p.n_cols) sj = 0;
+              }
+              P[static_cast<long long>(cg) * p.R_alloc + hp * p.Wp + wp] = o;
+              hp += d_hp;                                            // the unit one stride further on, without a division
+              cg += d_cg;
+              if (cg >= p.cpt) {
+                cg -= p.cpt;
+                ++hp;
+              }
+            }
+            pslot += p.pw;
+            if (pslot >= p.n_cols) pslot -= p.n_cols;
+          }
+          wp_done = wp_end;
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(C1_EPI * 32) : "memory");               // the ring restarts at column 0 with the next clip
       }
     } else
     for (int clip = blockIdx.x; clip < p.n_clips; clip += gridDim.x) {
@@ -588,6 +710,7 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_c
         const int r = t * 128 + row, wo = r / p.Hph, ho = r - wo * p.Hph;
         const bool valid = ho < p.Ho && wo < p.Wo;
         __half* dst = p.C + ((static_cast<long long>(clip) * p.Ho + ho) * p.Wo + wo) * p.ldc;
+        if (c_lo == c_hi && lane == 0) mbar_arrive(a_accempty + 8 * ab);         // fewer column groups than parts
         for (int g = c_lo; g < c_hi; ++g) {
           const int c0 = g * 16;
           uint32_t v[16];
@@ -774,7 +897,7 @@ struct GemmLayer {
   int imp = 0, R_alloc = 0, tiles_per_clip = 0;     // implicit mode (stride-1 conv over the pooled planar map): no A operand
   int res = 0, res_smem = 0, res_stages = 4, res_G = 1;   // ... with the clips' images resident in shared memory (conv_res_kernel)
   int c1res = 0, c1_units = 0, c1_tiles = 0, c1_hph = 0, c1_smem = 0;   // conv1 over the resident x8p image (conv1_res_kernel)
-  int c1_fuse = 0;             // ... whose epilogue applies the MaxPool and writes the next layer's planar image
+  int c1_fuse = 0, c1_cols = 0, c1_shift = 0;   // ... whose epilogue applies the MaxPool and writes the next layer's planar image (1: columns in registers, 2: staged)
   int planar_in = 0;           // the previous layer wrote this layer's planar image (no gemm_pool_planar_kernel pass)
   unsigned char* d_B = nullptr;
   float* d_bias = nullptr;
@@ -869,8 +992,9 @@ int cnn_gemm_plan_create(honk_model* m, CnnGemmPlan** out) {
       int max_smem_ = 0;
       HONK_CUDA(cudaDeviceGetAttribute(&max_smem_, cudaDevAttrMaxSharedMemoryPerBlockOptin, m->device));
       const int sh = L.sh, Wx = m->W0 - 7, Hph = (m->H0 + sh - 1) / sh;
-      // measured: time strides 4 and 8 (cnn-tstride4/8) have too few rows per phase image for this to beat the im2col operand
-      static const int c1_maxsh = getenv("HONK_C1_MAXSH") ? atoi(getenv("HONK_C1_MAXSH")) : 2;
+      // time strides 4 and 8 (cnn-tstride4/8): too few rows per phase image to beat the im2col operand on its own (measured); kept
+      // only if the epilogue can also take over the MaxPool (decided below, once conv2's operand is known)
+      static const int c1_maxsh = getenv("HONK_C1_MAXSH") ? atoi(getenv("HONK_C1_MAXSH")) : 8;
       if (!no_c1 && L.KW == 8 && L.sw == 1 && L.n_ntiles == 1 && (sh == 1 || (sh % 2 == 0 && sh <= c1_maxsh)) && L.Ho * L.Wo >= 256 && L.Wo == Wx) {
         L.c1_hph = Hph;
         L.c1_tiles = (Wx * Hph + 127) / 128;
@@ -926,19 +1050,32 @@ int cnn_gemm_plan_create(honk_model* m, CnnGemmPlan** out) {
       // coefficient columns (column stride 128 in the x8p image) and the column maxima fit its registers
       GemmLayer& L1 = p->layers[0];
       static const bool no_fuse = getenv("HONK_C1_FUSE") && atoi(getenv("HONK_C1_FUSE")) == 0;
+      const int Wx = m->W0 - 7, w_al = (L1.KP * L1.NT * 16 + 1023) / 1024 * 1024, rows_p = (L.Hin / L.ph) * L.ph;
       if (!no_fuse && L.res && L1.c1res && L1.sh == 1 && m->H0 <= 128 && L1.NT <= C1_FUSE_MAXNT && L.pw <= L1.Wo && L.ph <= L1.Ho) {
-        const int Wx = m->W0 - 7, units = (Wx * 128 + L1.KH + 2 + 7) / 8 * 8, img_al = (units * 16 + 1023) / 1024 * 1024;
-        const int w_al = (L1.KP * L1.NT * 16 + 1023) / 1024 * 1024, xch = 2 * (L.Hin / L.ph) * L.ph * (L1.NT * 2 + 16);
-        const int smem = 2 * img_al + w_al + xch + 1024;
+        const int units = (Wx * 128 + L1.KH + 2 + 7) / 8 * 8, img_al = (units * 16 + 1023) / 1024 * 1024;
+        const int smem = 2 * img_al + w_al + 2 * rows_p * (L1.NT * 2 + 16) + 1024;
         if (smem + 2048 <= max_smem_) {
           L1.c1_fuse = 1; L1.c1_hph = 128; L1.c1_tiles = Wx; L1.c1_units = units; L1.c1_smem = smem;
           L.planar_in = 1;
+        }
+      } else if (!no_fuse && L.res && L1.c1res && L1.sh > 1 && L1.c1_hph <= 64 && L.pw <= L1.Wo && L.ph <= L1.Ho) {
+        int shift = 0;
+        while ((1 << shift) < L1.c1_hph) ++shift;
+        const int Hc = 1 << shift, tiles = (Wx * Hc + 127) / 128, n_cols = 2 * (128 / Hc) + L.pw - 1;
+        const int units = ((L1.sh - 1) * Wx * Hc + tiles * 128 + L1.KH / L1.sh + 2 + 7) / 8 * 8, img_al = (units * 16 + 1023) / 1024 * 1024;
+        const int smem = 2 * img_al + w_al + n_cols * rows_p * (L1.NT * 2 + 16) + 1024;
+        if (smem + 2048 <= max_smem_ && Wx * Hc * 16 < (1 << 18)) {
+          L1.c1_fuse = 2; L1.c1_hph = Hc; L1.c1_tiles = tiles; L1.c1_units = std::max(units, L1.sh * Wx * Hc); L1.c1_smem = smem;
+          L1.c1_cols = n_cols; L1.c1_shift = shift;
+          L.planar_in = 1;
+          if (getenv("HONK_C1_FUSE") && atoi(getenv("HONK_C1_FUSE")) == 3) L1.c1_fuse = 0, L.planar_in = 0, L1.c1_smem = 2 * img_al + L1.KP * L1.NT * 16 + 1024;   // geometry only
         }
       }
     }
     H = L.Ho; W = L.Wo; C = L.N; Cs = L.ldc(); ph = c.conv2_pool[0]; pw = c.conv2_pool[1];
     p->layers.push_back(L);
   }
+  if (p->layers[0].c1res && p->layers[0].sh > 2 && !p->layers[0].c1_fuse) p->layers[0].c1res = 0;   // see conv1 above
   // ---- linear layers (model.py:195-205): the first one is a convolution whose kernel covers the whole pooled map, with the
   // weights permuted from the reference's (C, H, W) flatten order; the others are 1 x 1 over a 1 x 1 map
   std::vector<std::pair<std::string, int>> fcs;       // (name, relu)
@@ -1043,7 +1180,11 @@ int cnn_gemm_forward(const CnnGemmPlan* p, const float* d_mfcc, int64_t n_clips,
       if (L.c1res) {
         {
           ProfSpan sp(kPack[0], s);
-          x8p_pack_kernel<<<static_cast<unsigned>(n), 256, 0, s>>>(static_cast<const float*>(in), A, p->H0, p->W0, L.sh, L.c1_hph, L.c1_units);
+          static const bool pack_units = getenv("HONK_C1_PACK_UNITS") && atoi(getenv("HONK_C1_PACK_UNITS")) != 0;
+          if (p->W0 == 40 && !pack_units)
+            x8p_pack_rows40_kernel<<<static_cast<unsigned>(n), 128, 0, s>>>(static_cast<const float*>(in), A, p->H0, L.sh, L.c1_hph, L.c1_units);
+          else
+            x8p_pack_kernel<<<static_cast<unsigned>(n), 256, 0, s>>>(static_cast<const float*>(in), A, p->H0, p->W0, L.sh, L.c1_hph, L.c1_units);
           HONK_LAUNCH_CHECK();
         }
         Conv1ResParams r{};
@@ -1053,7 +1194,7 @@ int cnn_gemm_forward(const CnnGemmPlan* p, const float* d_mfcc, int64_t n_clips,
         r.lbo = L.sh == 1 ? 16 : r.phase_stride * 16;
         if (L.c1_fuse) {
           const GemmLayer& L2 = p->layers[1];
-          r.fuse = 1; r.ph = L2.ph; r.pw = L2.pw; r.Hp = L2.Hin / L2.ph; r.Wp = L2.Win / L2.pw; r.R_alloc = L2.R_alloc; r.cpt = L2.Cs >> 3;
+          r.fuse = L.c1_fuse; r.hc_shift = L.c1_shift; r.n_cols = L.c1_cols; r.ph = L2.ph; r.pw = L2.pw; r.Hp = L2.Hin / L2.ph; r.Wp = L2.Win / L2.pw; r.R_alloc = L2.R_alloc; r.cpt = L2.Cs >> 3;
           r.P = pooled;
         }
         static const int c1_mode = getenv("HONK_C1_MODE") ? atoi(getenv("HONK_C1_MODE")) : 0;

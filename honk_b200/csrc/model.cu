@@ -282,7 +282,8 @@ extern "C" int honk_model_create(const honk_model_config* cfg, const honk_tensor
       if (m->tc || m->tc2) m->path = "tcgen05-f16";
     }
   } else if (cfg->precision == 0) {
-    HONK_TRY(cnn_tc_plan_create(m.get(), &m->ctc));
+    static const bool no_ctc = getenv("HONK_DISABLE_CNN_TC") && atoi(getenv("HONK_DISABLE_CNN_TC")) != 0;   // A/B: the per-layer kernels
+    if (!no_ctc) HONK_TRY(cnn_tc_plan_create(m.get(), &m->ctc));
     if (!m->ctc) HONK_TRY(cnn_gemm_plan_create(m.get(), &m->cgm));
     if (m->ctc || m->cgm) m->path = "tcgen05-f16";
   }

@@ -394,7 +394,7 @@ struct Conv1ResParams {
   const float* bias;
   __half* C;                   // NHWC f16 [n_clips][Ho][Wo][ldc]
   int n_clips, img_bytes, KP, NT, ldc, Hph, Ho, Wo, n_tiles, lbo, sh, phase_stride;   // phase_stride = Wx * Hph rows
-  int mode;                    // HONK_C1_MODE, timing experiments only (results are garbage): 2 no epilogue stores, 4 no MMAs
+  int mode;                    // HONK_C1_MODE, timing experiments only (2, 4: results are garbage): 2 no epilogue stores, 4 no MMAs, 8 two accumulators
   // fused MaxPool(ph, pw) (model.py:190): Hph = 128, so tile t is coefficient column wo = t and a thread keeps ONE time row in
   // every tile; the epilogue writes the pooled map as the next layer's planar image P[clip][cg][R_alloc rows][8 halves]
   // fuse = 2 (time stride > 1): column stride Hc = 1 << hc_shift <= 64 rows, several columns per tile; the ReLU-ed f16 rows go to a
@@ -470,20 +470,27 @@ __global__ void __launch_bounds__(128) x8p_pack_rows40_kernel(const float* __res
 }
 
 constexpr int C1_FUSE_MAXNT = 128;       // fused pool: the column maxima of a warp's half of the channels stay in registers
+constexpr int C1_UNROLL = 12;            // kernel-row pairs issued from registers (KH <= 24: every reference config)
 constexpr int C1_MAXSTEPS = 64;          // kernel-row pairs of conv1 (KH <= 128)
 constexpr int C1_EPI = 16;               // epilogue warps: four per TMEM lane quarter, a quarter of the channels each (their dependent
                                          // instruction chains, not issue slots, bound the kernel: 8 warps measured 25-35 % slower)
-constexpr int C1_THREADS = (2 + C1_EPI) * 32;      // producer, MMA issuer, epilogue
+constexpr int C1_ISSUERS = 2;            // MMA-issuing warps, one per TMEM accumulator (alternate tiles): a lone issuer needs ~97 clk per
+                                         // MMA of its own instruction stream (ncu, profiles/r05_conv1_res_ncu.txt) against 56 clk of tensor time
+constexpr int C1_EPI0 = 1 + C1_ISSUERS;  // first epilogue warp
+constexpr int C1_THREADS = (C1_EPI0 + C1_EPI) * 32;      // producer, MMA issuers, epilogue
 
 __global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_constant__ Conv1ResParams p) {
   extern __shared__ __align__(1024) unsigned char c1_smem[];
-  __shared__ __align__(8) uint64_t bar_w, bar_imgfull[2], bar_imgempty[2], bar_accfull[2], bar_accempty[2];
+  __shared__ __align__(8) uint64_t bar_w, bar_imgfull[2], bar_imgempty[2], bar_accfull[4], bar_accempty[4];
   __shared__ __align__(16) float bias_s[GT_MAXNT];
   __shared__ uint32_t c1_aoff[C1_MAXSTEPS];                       // A window of every K = 16 step (a kernel-row pair), bytes from the tile's first unit
   __shared__ uint32_t tmem_base_s;
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   const int img_al = (p.img_bytes + 1023) / 1024 * 1024, w_bytes = p.KP * p.NT * 16;
+  // TMEM accumulators in flight: four of 128 columns when the layer fits them, else two of 256.  The commit -> epilogue load ->
+  // hand-back round trip is ~1700 clk (measured with MMAs and stores switched off), so two accumulators cap a tile at ~860 clk
+  const uint32_t acc_shift = (p.NT <= 128 && !(p.mode & 8)) ? 2 : 1, acc_mask = (1u << acc_shift) - 1, acc_stride = 512u >> acc_shift;
   for (int j = tid; j < p.KP / 2; j += C1_THREADS) {               // no index arithmetic in the issuing warp's loop
     const int kh = 2 * j;                                          // kernel rows (kh, kh + 1): phases kh % sh and the next one
     c1_aoff[j] = static_cast<uint32_t>(((kh % p.sh) * p.phase_stride + kh / p.sh) * 16);
@@ -496,7 +503,9 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_c
     mbar_init(a_w, 1);
     for (int k = 0; k < 2; ++k) {
       mbar_init(a_imgfull + 8 * k, 1);
-      mbar_init(a_imgempty + 8 * k, 1);
+      mbar_init(a_imgempty + 8 * k, C1_ISSUERS);
+    }
+    for (int k = 0; k < 4; ++k) {
       mbar_init(a_accfull + 8 * k, 1);
       mbar_init(a_accempty + 8 * k, C1_EPI);
     }
@@ -524,12 +533,16 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_c
           gt_bulk_load(smem_u32(c1_smem + ib * img_al + off), src + off, min(32768, p.img_bytes - off), a_imgfull + 8 * ib);
       }
     }
-  } else if (warp == 1) {
-    // ======================================= MMA issuer =====================================
+  } else if (warp < C1_EPI0) {
+    // ======================================= MMA issuers ====================================
+    const uint32_t me = warp - 1;                                  // this warp's accumulator = the tiles it issues (c & 1 == me)
     const uint32_t idesc = make_idesc(128, p.NT, 0);
     const uint64_t a_hi = make_desc(0, p.lbo, 128) & 0xFFFFFFFFFFFF0000ull;
     const uint64_t b_hi = make_desc(0, p.NT * 16, 128) & 0xFFFFFFFFFFFF0000ull;
     const uint32_t wb = smem_u32(wsm);
+    uint32_t aoff_r[C1_UNROLL];
+#pragma unroll
+    for (int j = 0; j < C1_UNROLL; ++j) aoff_r[j] = c1_aoff[min(j, C1_MAXSTEPS - 1)] >> 4;
     mbar_wait(a_w, 0);
     uint32_t n = 0, c = 0;
     for (int clip = blockIdx.x; clip < p.n_clips; clip += gridDim.x, ++n) {
@@ -538,26 +551,29 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_c
       fence_after();
       const uint32_t img = smem_u32(c1_smem + ib * img_al);
       for (int t = 0; t < p.n_tiles; ++t, ++c) {
-        const uint32_t ab = c & 1;
-        if (c >= 2) {
-          mbar_wait(a_accempty + 8 * ab, ((c >> 1) & 1) ^ 1);
+        const uint32_t ab = c & acc_mask;
+        if (C1_ISSUERS == 2 && (c & 1) != me) continue;
+        if (c > acc_mask) {
+          mbar_wait(a_accempty + 8 * ab, ((c >> acc_shift) & 1) ^ 1);
           fence_after();
         }
         if (gt_elect_one()) {
-          const uint32_t d = tmem + ab * 256;
-          const uint32_t a_t = img + t * 2048, n_j = (p.mode & 4) ? 0 : p.KP / 2;
-          uint32_t bd = wb >> 4;
-          for (uint32_t j = 0; j < n_j; ++j, bd += 2 * p.NT)
-            mma_f16_ss(d, a_hi | ((a_t + c1_aoff[j]) >> 4), b_hi | bd, idesc, j > 0 ? 1u : 0u);
+          const uint32_t d = tmem + ab * acc_stride;
+          const uint32_t a_t = (img + t * 2048) >> 4, n_j = (p.mode & 4) ? 0 : p.KP / 2;
+#pragma unroll
+          for (uint32_t j = 0; j < C1_UNROLL; ++j)                     // offsets in registers: no load in front of an MMA
+            if (j < n_j) mma_f16_ss(d, a_hi | (a_t + aoff_r[j]), b_hi | ((wb >> 4) + j * 2 * p.NT), idesc, j > 0 ? 1u : 0u);
+          for (uint32_t j = C1_UNROLL; j < n_j; ++j)
+            mma_f16_ss(d, a_hi | (a_t + (c1_aoff[j] >> 4)), b_hi | ((wb >> 4) + j * 2 * p.NT), idesc, 1u);
           commit(a_accfull + 8 * ab);
-          if (t == p.n_tiles - 1) commit(a_imgempty + 8 * ib);
+          if (t + C1_ISSUERS >= p.n_tiles) commit(a_imgempty + 8 * ib);   // this warp's last tile of the clip (n_tiles >= 2)
         }
         __syncwarp();
       }
     }
   } else {
     // ======================================= epilogue =======================================
-    const int quad = warp & 3, row = quad * 32 + lane, part = (warp - 2) >> 2;          // column part of this warp
+    const int quad = warp & 3, row = quad * 32 + lane, part = (warp - C1_EPI0) >> 2;          // column part of this warp
     const uint32_t tlane = static_cast<uint32_t>(quad * 32) << 16;
     const int n16 = p.NT / 16, c_lo = part * n16 / (C1_EPI / 4), c_hi = (part + 1) * n16 / (C1_EPI / 4);   // 16-column groups
     uint32_t c = 0;
@@ -566,19 +582,19 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_c
       // so the order against the reference's conv -> ReLU -> pool does not change a bit), max over ph time rows through shared memory
       constexpr int MAXG = (C1_FUSE_MAXNT / 16 + C1_EPI / 4 - 1) / (C1_EPI / 4);
       float rm[MAXG][16];
-      const int n_g = c_hi - c_lo, xrow = p.NT * 2 + 16, etid = tid - 64, rows_p = p.Hp * p.ph, upc = p.Hp * p.cpt;
+      const int n_g = c_hi - c_lo, xrow = p.NT * 2 + 16, etid = tid - C1_EPI0 * 32, rows_p = p.Hp * p.ph, upc = p.Hp * p.cpt;
       const int hp0 = etid / p.cpt, cg0 = etid - hp0 * p.cpt, d_hp = C1_EPI * 32 / p.cpt, d_cg = C1_EPI * 32 - d_hp * p.cpt;   // this thread's pooled units
       uint32_t xb = 0;
       for (int clip = blockIdx.x; clip < p.n_clips; clip += gridDim.x) {
         for (int t = 0, wq = 0, wp = 0; t < p.n_tiles; ++t, ++c) {
-          const uint32_t ab = c & 1;
-          mbar_wait(a_accfull + 8 * ab, (c >> 1) & 1);
+          const uint32_t ab = c & acc_mask;
+          mbar_wait(a_accfull + 8 * ab, (c >> acc_shift) & 1);
           fence_after();
 #pragma unroll
           for (int gi = 0; gi < MAXG; ++gi) {
             if (gi >= n_g) break;
             uint32_t v[16];
-            tmem_ld16(tmem + tlane + ab * 256 + (c_lo + gi) * 16, v);
+            tmem_ld16(tmem + tlane + ab * acc_stride + (c_lo + gi) * 16, v);
             tmem_ld_wait();
 #pragma unroll
             for (int k = 0; k < 16; ++k) rm[gi][k] = wq == 0 ? __uint_as_float(v[k]) : fmaxf(rm[gi][k], __uint_as_float(v[k]));
@@ -631,14 +647,14 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_c
         }
       }
     } else if (p.fuse == 2) {
-      const int xrow = p.NT * 2 + 16, etid = tid - 64, rows_p = p.Hp * p.ph, col_bytes = rows_p * xrow, upc = p.Hp * p.cpt;
+      const int xrow = p.NT * 2 + 16, etid = tid - C1_EPI0 * 32, rows_p = p.Hp * p.ph, col_bytes = rows_p * xrow, upc = p.Hp * p.cpt;
       const int col_in_tile = row >> p.hc_shift, ho = row & ((1 << p.hc_shift) - 1);      // this thread's place in every tile
       const int hp0 = etid / p.cpt, cg0 = etid - hp0 * p.cpt, d_hp = C1_EPI * 32 / p.cpt, d_cg = C1_EPI * 32 - d_hp * p.cpt;   // its pooled units
       for (int clip = blockIdx.x; clip < p.n_clips; clip += gridDim.x) {
         uint4* P = reinterpret_cast<uint4*>(p.P) + static_cast<long long>(clip) * p.cpt * p.R_alloc;
         for (int t = 0, wp_done = 0, pslot = 0, tslot = 0; t < p.n_tiles; ++t, ++c) {   // ring slots of the next column block / tile
-          const uint32_t ab = c & 1;
-          mbar_wait(a_accfull + 8 * ab, (c >> 1) & 1);
+          const uint32_t ab = c & acc_mask;
+          mbar_wait(a_accfull + 8 * ab, (c >> acc_shift) & 1);
           fence_after();
           const int col = (t << (7 - p.hc_shift)) + col_in_tile;
           const bool valid = ho < rows_p && col < p.Wp * p.pw && !(p.mode & 2);
@@ -651,7 +667,7 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_c
           for (int g = c_lo; g < c_hi; ++g) {
             const int c0 = g * 16;
             uint32_t v[16];
-            tmem_ld16(tmem + tlane + ab * 256 + c0, v);
+            tmem_ld16(tmem + tlane + ab * acc_stride + c0, v);
             tmem_ld_wait();
             if (g == c_hi - 1) {
               fence_before();
@@ -704,8 +720,8 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_c
     } else
     for (int clip = blockIdx.x; clip < p.n_clips; clip += gridDim.x) {
       for (int t = 0; t < p.n_tiles; ++t, ++c) {
-        const uint32_t ab = c & 1;
-        mbar_wait(a_accfull + 8 * ab, (c >> 1) & 1);
+        const uint32_t ab = c & acc_mask;
+        mbar_wait(a_accfull + 8 * ab, (c >> acc_shift) & 1);
         fence_after();
         const int r = t * 128 + row, wo = r / p.Hph, ho = r - wo * p.Hph;
         const bool valid = ho < p.Ho && wo < p.Wo;
@@ -714,7 +730,7 @@ __global__ void __launch_bounds__(C1_THREADS, 1) conv1_res_kernel(const __grid_c
         for (int g = c_lo; g < c_hi; ++g) {
           const int c0 = g * 16;
           uint32_t v[16];
-          tmem_ld16(tmem + tlane + ab * 256 + c0, v);
+          tmem_ld16(tmem + tlane + ab * acc_stride + c0, v);
           tmem_ld_wait();
           if (g == c_hi - 1) {                                       // this warp's share of the accumulator is in registers
             fence_before();

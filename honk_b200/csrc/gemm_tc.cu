@@ -229,6 +229,8 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const __grid_con
 // stage's K = 16 steps for EVERY M tile of the clip (all tiles_per_clip accumulators live in TMEM), reading the A operand as
 // tap-shifted windows of the resident image: rows [t * 128 + kh * Wp + kw, +128) of planes (cg, cg + 1).  Per clip the L2 is
 // asked for the image once and the weights once instead of (taps x tiles) shifted copies of the image.
+constexpr int CR_EPI = 16;               // epilogue warps: four per TMEM lane quarter, a quarter of the channels each
+constexpr int CR_THREADS = (2 + CR_EPI) * 32;
 constexpr int CR_MAXSTEPS = 1024;     // K = 16 steps of a layer (taps x channel-group pairs)
 constexpr int CR_MAXSTAGE = 12;       // B stages in flight: as many as the shared memory left by the image holds (bulk-copy latency)
 
@@ -243,7 +245,7 @@ struct ConvResParams {
 };
 
 template <int TPC>       // M tiles per clip as a constant (0: p.tiles_per_clip), so the issuing warp's inner loop unrolls
-__global__ void __launch_bounds__(GT_THREADS, 1) conv_res_kernel(const __grid_constant__ ConvResParams p) {
+__global__ void __launch_bounds__(CR_THREADS, 1) conv_res_kernel(const __grid_constant__ ConvResParams p) {
   extern __shared__ __align__(1024) unsigned char cr_smem[];
   __shared__ __align__(8) uint64_t bar_bfull[CR_MAXSTAGE], bar_bempty[CR_MAXSTAGE], bar_img[2], bar_acc[2];
   __shared__ uint32_t a_off[CR_MAXSTEPS];                         // byte offset of every K = 16 step's A window inside the image
@@ -265,12 +267,12 @@ __global__ void __launch_bounds__(GT_THREADS, 1) conv_res_kernel(const __grid_co
     mbar_init(a_imgfull, 1);
     mbar_init(a_imgempty, 1);
     mbar_init(a_accfull, 1);
-    mbar_init(a_accempty, 4);
+    mbar_init(a_accempty, CR_EPI);
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(smem_u32(&tmem_base_s), 512);
   const int KP = p.n_taps * p.NCG, n_ks = (KP + GT_KC - 1) / GT_KC;
-  for (int st = tid; st < KP / 2; st += GT_THREADS) {               // the issuing warp is bound by its own instruction stream:
+  for (int st = tid; st < KP / 2; st += CR_THREADS) {               // the issuing warp is bound by its own instruction stream:
     const int tap = (2 * st) / p.NCG, cg = 2 * st - tap * p.NCG, kh = tap / p.KW, kw = tap - kh * p.KW;   // no index arithmetic there
     a_off[st] = static_cast<uint32_t>(cg * (p.R_alloc * 16) + (kh * p.Wp + kw) * 16);
   }
@@ -339,23 +341,25 @@ __global__ void __launch_bounds__(GT_THREADS, 1) conv_res_kernel(const __grid_co
     }
   } else {
     // ======================================= epilogue =======================================
-    const int quad = warp & 3, row = quad * 32 + lane;
+    const int quad = warp & 3, row = quad * 32 + lane, part = (warp - 2) >> 2;          // TMEM lane quarter, column part
     const uint32_t tlane = static_cast<uint32_t>(quad * 32) << 16;
+    const int n16 = p.NT / 16, g_lo = part * n16 / (CR_EPI / 4), g_hi = (part + 1) * n16 / (CR_EPI / 4);   // 16-column groups of this warp
     uint32_t n = 0;
     for (int q = blockIdx.x; q < n_pass; q += gridDim.x, ++n) {
       const int n_here = min(p.G, p.n_clips - q * p.G), n_t = n_here * tpc;
       mbar_wait(a_accfull, n & 1);
       fence_after();
+      if (g_lo == g_hi && lane == 0) mbar_arrive(a_accempty);        // fewer column groups than parts
       for (int tt = 0, g = 0, t = 0; tt < n_t; ++tt, g += (t == tpc - 1), t = (t == tpc - 1) ? 0 : t + 1) {
         const long long clip = static_cast<long long>(q) * p.G + g;
         const int r = t * 128 + row, ho = r / p.Wp, wo = r - ho * p.Wp;
         const bool valid = ho < p.Ho && wo < p.Wo;
         __half* dst = p.C + ((clip * p.Ho + ho) * p.Wo + wo) * p.ldc;
-        for (int c0 = 0; c0 < p.NT; c0 += 16) {
+        for (int c0 = g_lo * 16; c0 < g_hi * 16; c0 += 16) {
           uint32_t v[16];
           tmem_ld16(tmem + tlane + tt * p.NT + c0, v);
           tmem_ld_wait();
-          if (tt == n_t - 1 && c0 + 16 >= p.NT) {                  // everything is in registers: hand the accumulators back
+          if (tt == n_t - 1 && c0 + 16 >= g_hi * 16) {                  // everything is in registers: hand the accumulators back
             fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(a_accempty);
@@ -1283,11 +1287,11 @@ int cnn_gemm_forward(const CnnGemmPlan* p, const float* d_mfcc, int64_t n_clips,
         ProfSpan sp(kGemm[std::min<size_t>(li, 5)], s);
         const unsigned grid = static_cast<unsigned>(std::min<long long>((n + L.res_G - 1) / L.res_G, p->n_sms));
         switch (L.tiles_per_clip) {
-          case 1: conv_res_kernel<1><<<grid, GT_THREADS, L.res_smem, s>>>(r); break;
-          case 2: conv_res_kernel<2><<<grid, GT_THREADS, L.res_smem, s>>>(r); break;
-          case 3: conv_res_kernel<3><<<grid, GT_THREADS, L.res_smem, s>>>(r); break;
-          case 4: conv_res_kernel<4><<<grid, GT_THREADS, L.res_smem, s>>>(r); break;
-          default: conv_res_kernel<0><<<grid, GT_THREADS, L.res_smem, s>>>(r); break;
+          case 1: conv_res_kernel<1><<<grid, CR_THREADS, L.res_smem, s>>>(r); break;
+          case 2: conv_res_kernel<2><<<grid, CR_THREADS, L.res_smem, s>>>(r); break;
+          case 3: conv_res_kernel<3><<<grid, CR_THREADS, L.res_smem, s>>>(r); break;
+          case 4: conv_res_kernel<4><<<grid, CR_THREADS, L.res_smem, s>>>(r); break;
+          default: conv_res_kernel<0><<<grid, CR_THREADS, L.res_smem, s>>>(r); break;
         }
         HONK_LAUNCH_CHECK();
       } else {
